@@ -1,0 +1,156 @@
+"""Pin the CPU oracle against fixtures produced by the reference's own Python
+(oracle/make_golden.py).  CPU only."""
+import numpy as np
+import torch
+
+from oracle import gla, swa
+
+T = torch.from_numpy
+
+
+def close(a, b, atol, rtol=0.0):
+    a, b = torch.as_tensor(a).float(), torch.as_tensor(b).float()
+    assert a.shape == b.shape, (a.shape, b.shape)
+    err = (a - b).abs().max().item()
+    assert torch.allclose(a, b, atol=atol, rtol=rtol), f"max err {err}"
+
+
+def test_gla_recurrence_vs_fla_naive(golden):
+    g = golden("gla_naive.npz")
+    for tag in ("7b", "70b"):
+        q, k, v, gg, S0 = (T(g[f"{tag}_{n}"]) for n in ("q", "k", "v", "g", "S0"))
+        o, S = gla.gla_recurrent(q, k, v, gg, S0)
+        close(o, g[f"{tag}_o"], 2e-5, 1e-5)
+        close(S, g[f"{tag}_S"], 2e-5, 1e-5)
+        # compact (per-kv-head) initial state is the same thing when the group shares it
+        o2, S2 = gla.gla_chunked(q, k, v, gg, S0, chunk=16)
+        close(o2, g[f"{tag}_o"], 1e-4, 1e-4)
+        close(S2, g[f"{tag}_S"], 1e-4, 1e-4)
+
+
+def test_swa_dense_vs_reference_naive(golden):
+    g = golden("swa_naive.npz")
+    for tag in ("prefill", "suffix", "decode", "full"):
+        W = int(g[f"{tag}_W"])
+        # reference mask is (q_id - k_id) < W  ==  window_left = W - 1
+        wl = W - 1 if W < (1 << 29) else -1
+        q2 = T(g[f"{tag}_q2"]) if f"{tag}_q2" in g else None
+        o, om = swa.swa_meta_dense(T(g[f"{tag}_q1"]), T(g[f"{tag}_k1"]), T(g[f"{tag}_v1"]), q2,
+                                   T(g[f"{tag}_k2"]), T(g[f"{tag}_v2"]), wl)
+        ref = g[f"{tag}_o"]                       # reference returns real-then-meta
+        Lq = o.shape[0]
+        close(o, ref[:Lq], 2e-6, 1e-5)
+        if q2 is not None:
+            close(om, ref[Lq:], 2e-6, 1e-5)
+        two = swa.swa_meta_two_pass(T(g[f"{tag}_q1"]), T(g[f"{tag}_k1"]), T(g[f"{tag}_v1"]),
+                                    T(g[f"{tag}_k2"]), T(g[f"{tag}_v2"]), wl)
+        close(two, ref[:Lq], 5e-6, 1e-5)
+
+
+def test_merge_vs_reference_torchscript(golden):
+    g = golden("merge.npz")
+    o, l = swa.merge_out_lse(T(g["out"]), T(g["lse"]), T(g["bout"]), T(g["blse"]))
+    close(o, g["o"], 1e-6)
+    close(l, g["l"], 1e-6)
+
+
+def test_gate_7b_vs_hf_module(golden):
+    g = golden("hf7b_gla_module.npz")
+    H, Hkv, D = 4, 2, 128
+    q_raw = T(g["q_raw"]).view(-1, H, D)
+    k_raw = T(g["k_raw"]).view(-1, Hkv, D)
+    v_raw = T(g["v_raw"]).view(-1, Hkv, D)
+    gk_raw = T(g["gk_raw"]).view(-1, Hkv, D)
+    q, k, gk = gla.gate_7b(q_raw, k_raw, gk_raw)
+    # module tensors are head-first [H,T,D] and already repeat_kv'ed
+    close(q.transpose(0, 1), g["q"], 1e-6)
+    close(gla._expand_heads(k, H).transpose(0, 1), g["k"], 1e-6)
+    close(gla._expand_heads(gk, H).transpose(0, 1), g["gk"], 1e-6)
+    o, S = gla.gla_recurrent(q, k, v_raw, gk)
+    close(o.transpose(0, 1), g["o"], 2e-5, 1e-5)
+    close(S, g["h"], 2e-5, 1e-5)
+    y = gla.rms_norm_head(o, T(g["g_norm_w"]), 1e-5).reshape(o.shape[0], -1) @ T(g["o_proj_w"]).T
+    close(y, g["y"], 1e-4, 1e-4)
+
+
+def test_gate_70b_vs_hf_module(golden):
+    g = golden("hf70b_linear_module.npz")
+    H, Hkv, D = 4, 2, 128
+    for tag in ("first", "lb", "nolb"):
+        q_raw = T(g[f"{tag}_q_raw"]).view(-1, H, D)
+        k_raw = T(g[f"{tag}_k_raw"]).view(-1, Hkv, D)
+        v_raw = T(g[f"{tag}_v_raw"]).view(-1, Hkv, D)
+        lb = T(g[f"{tag}_lb"]) if f"{tag}_lb" in g else None
+        # HF applies the gate after repeat_kv (lower bound is per q-head)
+        k_rep = gla._expand_heads(k_raw, H)
+        q, k, gg = gla.gate_70b(q_raw, k_rep, v_raw, lower_bound=lb,
+                                layer_idx=int(g[f"{tag}_layer"]), num_heads=H, rule="hf")
+        close(q.transpose(0, 1), g[f"{tag}_q"], 1e-6)
+        close(k.transpose(0, 1), g[f"{tag}_k"], 2e-6)
+        close(gg.transpose(0, 1), g[f"{tag}_g"], 1e-5, 1e-5)
+        o, _ = gla.gla_recurrent(q, k, v_raw, gg)
+        close(o.transpose(0, 1), g[f"{tag}_o"], 2e-5, 1e-5)
+
+
+def test_rope_vs_hf(golden):
+    g = golden("rope.npz")
+    pos = T(g["pos"])
+    qe = swa.rope_neox(T(g["q"]).transpose(0, 1), pos)
+    ke = swa.rope_neox(T(g["k"]).transpose(0, 1), pos)
+    close(qe.transpose(0, 1), g["qe"], 1e-5)
+    close(ke.transpose(0, 1), g["ke"], 1e-5)
+
+
+def test_decode_step_matches_recurrence():
+    """Faithful (bf16-rounding) decode steps track the fp32 recurrence (SURVEY 8c drift)."""
+    torch.manual_seed(0)
+    Tn, H, Hkv, D = 64, 4, 2, 128
+    q, k, v, gg = gla.synth_gla_inputs(Tn, H, Hkv, D, "70b", seed=4)
+    o_ref, S_ref = gla.gla_recurrent(q, k, v, gg)
+    cache = torch.zeros(3, Hkv, D, D, dtype=torch.bfloat16)
+    slot = torch.tensor([1], dtype=torch.int32)
+    outs = [gla.gla_decode_step(q[t:t + 1], k[t:t + 1], v[t:t + 1], gg[t:t + 1], cache, slot)
+            for t in range(Tn)]
+    o = torch.cat(outs).float()
+    assert (o - o_ref).abs().max() < 2 ** -6 * o_ref.abs().max()
+    assert (cache[1].float() - S_ref[::2]).abs().max() < 0.05
+    assert cache[0].abs().max() == 0 and cache[2].abs().max() == 0
+    # PAD slot leaves everything untouched
+    before = cache.clone()
+    z = gla.gla_decode_step(q[:1], k[:1], v[:1], gg[:1], cache, torch.tensor([-1]))
+    assert torch.equal(before, cache) and z.abs().max() == 0
+
+
+def test_paged_decode_equals_dense_and_kv_write_bit_exact():
+    torch.manual_seed(1)
+    H, Hkv, D, M, bs = 4, 2, 64, 8, 16
+    lens = [5, 37, 16, 64]
+    nb = 16
+    k_cache = torch.zeros(nb, bs, Hkv, D, dtype=torch.bfloat16)
+    v_cache = torch.zeros_like(k_cache)
+    perm = torch.randperm(nb).tolist()
+    tables, slot_map, keys, vals = [], [], [], []
+    it = iter(perm)
+    for L in lens:
+        row = [next(it) for _ in range((L + bs - 1) // bs)]
+        tables.append(row + [0] * (4 - len(row)))
+        slot_map += [row[p // bs] * bs + p % bs for p in range(L)]
+        keys.append(torch.randn(L, Hkv, D).bfloat16())
+        vals.append(torch.randn(L, Hkv, D).bfloat16())
+    key, val = torch.cat(keys), torch.cat(vals)
+    slot_map[3] = -1                                   # a padded token is skipped
+    swa.kv_write_paged(key, val, k_cache, v_cache, slot_map)
+    slot_map[3] = tables[0][0] * bs + 3
+    swa.kv_write_paged(key[3:4], val[3:4], k_cache, v_cache, slot_map[3:4])
+    off = 0
+    for i, L in enumerate(lens):
+        got = swa.gather_paged(k_cache, tables[i], 0, L)
+        assert torch.equal(got, keys[i])
+        off += L
+    q = torch.randn(len(lens), H, D).bfloat16()
+    k2, v2 = torch.randn(M, Hkv, D).bfloat16(), torch.randn(M, Hkv, D).bfloat16()
+    for wl in (-1, 7, 20):
+        out = swa.swa_meta_decode_paged(q, k_cache, v_cache, tables, lens, k2, v2, wl, out_dtype=torch.float32)
+        for i, L in enumerate(lens):
+            ref, _ = swa.swa_meta_dense(q[i:i + 1], keys[i], vals[i], None, k2, v2, wl)
+            close(out[i], ref[0], 1e-6)
