@@ -1,0 +1,177 @@
+/*
+ * hymeta_b200.h -- C ABI of the B200 (sm_100a) Hymeta hybrid-attention kernels.
+ *
+ * The reference (FAndromedA/vllm-hymeta) is pure Python and defines no FFI; its
+ * kernel boundary is a set of Python functions (Triton / flash-attn / fla
+ * wrappers).  Each entry point below replaces one of them and is what the
+ * reference-side Python stub binds with ctypes.  Citations
+ * are file:line relative to the reference root.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless stated; the caller owns all memory
+ *   - activations / KV / state are bf16 (uint16 storage); gates are fp32 or bf16
+ *   - strides are in ELEMENTS; the innermost (head_dim) stride is always 1
+ *   - `stream` is a cudaStream_t passed as void*
+ *   - no allocation, no synchronisation, no global state: every call only
+ *     enqueues kernels on `stream` and is CUDA-graph-capture safe
+ *   - return 0 on success, a negative hymeta_status otherwise
+ *   - head_dim (D) must be 128 (the only geometry the reference models use,
+ *     SURVEY F2)
+ */
+#ifndef HYMETA_B200_H
+#define HYMETA_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define HYMETA_ABI_VERSION 1
+
+typedef enum {
+  HYMETA_OK = 0,
+  HYMETA_ERR_INVALID_ARG = -1,   /* null pointer / negative size / bad stride          -> ValueError        */
+  HYMETA_ERR_UNSUPPORTED = -2,   /* head size / group size / block size not supported  -> ValueError        */
+  HYMETA_ERR_WORKSPACE = -3,     /* workspace too small                                -> ValueError        */
+  HYMETA_ERR_CUDA = -4,          /* launch failed; see hymeta_last_cuda_error()        -> RuntimeError      */
+  HYMETA_ERR_NO_DEVICE = -5      /* no sm_100 device / driver entry point missing      -> RuntimeError      */
+} hymeta_status;
+
+int hymeta_abi_version(void);
+const char* hymeta_status_string(int status);
+/* cudaError_t of the last failed launch on this thread (0 if none). */
+int hymeta_last_cuda_error(void);
+/* Number of kernels launched by this library in this process (bench.py's gpu_launches). */
+int64_t hymeta_launch_count(void);
+
+/* ------------------------------------------------------------------------------------------------
+ * a2  GLA decode -- replaces my_fused_recurrent_gla / my_fused_recurrent_fwd_kernel
+ *     (vllm_hymeta/models/my_fused_recurrent_gla.py:8-23, my_fused_recurrent.py:8-135;
+ *      7B twin vllm_hymeta/model_for_7B/my_fused_recurrent.py:8-153).
+ *
+ * One recurrent step for B requests, state updated IN PLACE:
+ *     S <- bf16(k (x) v) + exp(g)[:,None] * S ;  o = (q*scale)^T S   (fp32 math, bf16 stores)
+ * q,o: [B, H, D].  k,v,g: [B, Hk, D].  state: [slots, Hs, D, D] (row = d_k, col = d_v).
+ * Hs is the number of states per request: Hs == H reproduces the reference layout
+ * (one state per q-head, k/v/g already repeat_kv'ed or not), Hs == Hkv stores one state
+ * per kv-head (the 7 q-heads of a GQA group share a bit-identical state -- SURVEY F7).
+ * Requires H % Hs == 0 and Hs % Hk == 0.  slot_idx[b] == -1 skips the request
+ * (my_fused_recurrent.py:31-35); its output row is written as zeros.
+ * ---------------------------------------------------------------------------------------------- */
+int hymeta_gla_decode(const void* q, const void* k, const void* v, const void* g, void* o,
+                      void* state, const int32_t* slot_idx,
+                      int B, int H, int Hk, int Hs, int D,
+                      int64_t q_sb, int64_t q_sh, int64_t k_sb, int64_t k_sh,
+                      int64_t v_sb, int64_t v_sh, int64_t g_sb, int64_t g_sh,
+                      int64_t o_sb, int64_t o_sh, int64_t st_ss, int64_t st_sh,
+                      int g_is_fp32, float scale, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * a3  GLA chunked prefill, varlen -- replaces the per-request fused_chunk_gla loop
+ *     (vllm_hymeta/models/modeling_hymeta.py:441-549 incl. the meta pass :447-467;
+ *      vllm_hymeta/model_for_7B/gla_attention.py:179-221).
+ *
+ * q,o: [T, H, D].  k,v,g: [T, Hk, D].  Sequence n covers tokens [cu_seqlens[n], cu_seqlens[n+1]).
+ * init_mode[n]: 0 = zero state, 1 = state[slot_idx[n]], 2 = meta_state ([Hs, D, D], may be null
+ * if unused).  If write_state != 0 and slot_idx[n] >= 0 the final state is stored (bf16) to
+ * state[slot_idx[n]].  No host synchronisation (replaces the isnan()/context_len host syncs,
+ * modeling_hymeta.py:489,501).  max_seqlen is an upper bound used for grid sizing only.
+ * ---------------------------------------------------------------------------------------------- */
+int hymeta_gla_prefill_varlen(const void* q, const void* k, const void* v, const void* g, void* o,
+                              void* state, const void* meta_state,
+                              const int32_t* cu_seqlens, const int32_t* slot_idx,
+                              const int32_t* init_mode,
+                              int N, int T, int H, int Hk, int Hs, int D,
+                              int64_t q_st, int64_t q_sh, int64_t k_st, int64_t k_sh,
+                              int64_t v_st, int64_t v_sh, int64_t g_st, int64_t g_sh,
+                              int64_t o_st, int64_t o_sh, int64_t st_ss, int64_t st_sh,
+                              int64_t meta_sh, int g_is_fp32, float scale, int write_state,
+                              int max_seqlen, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * a9  Paged-KV write -- replaces torch.ops._C_cache_ops.reshape_and_cache_flash
+ *     (vllm_hymeta/attention/meta_attention.py:790-799).  Bit-exact copy:
+ *     cache[slot / block_size, slot % block_size, h, :] = key|value[t, h, :]   for slot >= 0.
+ * key,value: [T, Hkv, D].  k_cache,v_cache: [num_blocks, block_size, Hkv, D].
+ * ---------------------------------------------------------------------------------------------- */
+int hymeta_kv_write_paged(const void* key, const void* value, void* k_cache, void* v_cache,
+                          const int64_t* slot_mapping, int T, int Hkv, int D, int block_size,
+                          int64_t key_st, int64_t key_sh, int64_t val_st, int64_t val_sh,
+                          int64_t kc_sblk, int64_t kc_stok, int64_t kc_sh,
+                          int64_t vc_sblk, int64_t vc_stok, int64_t vc_sh, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * a8  SWA + meta-prefix paged decode -- replaces metatoken_flash_attn_with_kvcache
+ *     (vllm_hymeta/attention/fa_kernel_metatoken.py:287-326 -> :124-194 -> :26-106,
+ *      i.e. flash_attn fwd_kvcache + meta pass + _update_out_and_lse in ONE pass).
+ *
+ * q,out: [B, H, D].  Request b attends to [meta_k/meta_v (M rows, always visible) |
+ * cached keys at logical positions max(0, L-1-window_left) .. L-1], L = cache_seqlens[b]
+ * (window_left < 0: all positions).  Logical position p lives at
+ * cache[block_tables[b, p / block_size], p % block_size].  meta_k/meta_v: [M, Hkv, D] or null
+ * when M == 0.  workspace: hymeta_swa_decode_workspace_bytes(...) bytes, any contents.
+ * ---------------------------------------------------------------------------------------------- */
+size_t hymeta_swa_decode_workspace_bytes(int B, int H, int Hkv, int D, int max_blocks,
+                                         int block_size, int window_left, int M);
+int hymeta_swa_meta_decode_paged(const void* q, const void* k_cache, const void* v_cache,
+                                 const int32_t* block_tables, const int32_t* cache_seqlens,
+                                 const void* meta_k, const void* meta_v, void* out,
+                                 void* workspace, size_t workspace_bytes,
+                                 int B, int H, int Hkv, int D, int M, int block_size,
+                                 int max_blocks, int64_t bt_stride, int window_left, float scale,
+                                 int64_t q_sb, int64_t q_sh, int64_t o_sb, int64_t o_sh,
+                                 int64_t kc_sblk, int64_t kc_stok, int64_t kc_sh,
+                                 int64_t vc_sblk, int64_t vc_stok, int64_t vc_sh,
+                                 int64_t mk_st, int64_t mk_sh, int64_t mv_st, int64_t mv_sh,
+                                 void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * a7  SWA + meta-prefix varlen prefill -- replaces metatoken_flash_attn_varlen_func
+ *     (vllm_hymeta/attention/fa_kernel_metatoken.py:329-374 -> :198-285: two flash-attn
+ *      launches + TorchScript LSE merge + concat, in ONE kernel).
+ *
+ * q1: [Tq, H, D] packed queries, k1,v1: [Tk, Hkv, D] packed keys; sequence n has queries
+ * [cu_q[n], cu_q[n+1]) and keys [cu_k[n], cu_k[n+1]); queries are aligned to the END of the keys
+ * (flash-attn bottom-right causal).  Real query at key-position i sees the M meta keys plus real
+ * keys j <= i with i - j <= window_left (window_left < 0: unbounded).
+ * q2: [M, H, D] meta queries or null; when given they attend to the meta keys only,
+ * bidirectionally (:261-275), and their rows come FIRST in `out` (:283):
+ * out: [(M if q2) + Tq, H, D].
+ * If block_tables != null the keys are read from the paged cache instead (prefix/chunked
+ * prefill, meta_attention.py:886-919): k1,v1 are then [num_blocks, block_size, Hkv, D] caches
+ * addressed like the decode entry point and cu_k holds cumulative seq_lens.
+ * ---------------------------------------------------------------------------------------------- */
+int hymeta_swa_meta_prefill_varlen(const void* q1, const void* k1, const void* v1, const void* q2,
+                                   const void* meta_k, const void* meta_v, void* out,
+                                   const int32_t* cu_q, const int32_t* cu_k,
+                                   const int32_t* block_tables, int64_t bt_stride, int block_size,
+                                   int N, int Tq, int Tk, int H, int Hkv, int D, int M,
+                                   int max_seqlen_q, int window_left, float scale,
+                                   int64_t q_st, int64_t q_sh, int64_t k_st, int64_t k_sh,
+                                   int64_t v_st, int64_t v_sh, int64_t q2_st, int64_t q2_sh,
+                                   int64_t mk_st, int64_t mk_sh, int64_t mv_st, int64_t mv_sh,
+                                   int64_t o_st, int64_t o_sh, int64_t kc_sblk, int64_t vc_sblk,
+                                   void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * a5  Slot-state maintenance -- replaces the advanced-index zero fill
+ *     `hymeta_cache[:, slots, ...] = 0` (modeling_hymeta.py:1202-1227) and
+ *     HymetaCacheManager._copy_cache (models/hymeta_cache.py:46-50) with one launch each.
+ * state: [L, slots, Hs, D, D] bf16, contiguous per (layer, slot).
+ * ---------------------------------------------------------------------------------------------- */
+int hymeta_state_zero_slots(void* state, const int32_t* slots, int n, int L,
+                            int64_t st_sl, int64_t st_ss, int64_t slot_elems, void* stream);
+int hymeta_state_copy_slot(void* state, int from_slot, int to_slot, int L,
+                           int64_t st_sl, int64_t st_ss, int64_t slot_elems, void* stream);
+
+/* Built-in self test of the tcgen05 / TMA building blocks (descriptor encodings, swizzles).
+ * Runs small GEMMs on the current device and compares with a CUDA-core result.
+ * Returns 0 if all pass, else the (positive) index of the first failing case. */
+int hymeta_selftest_umma(float* max_err_out /* host pointer, may be null */);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HYMETA_B200_H */

@@ -1,0 +1,68 @@
+"""ctypes binding of the C-ABI kernel library (include/hymeta_b200.h).
+
+There is no fallback: if ``csrc/libhymeta_b200.so`` is missing the import of any
+op raises, and every op raises if the library reports an error.  Build it with
+``python -c "import __graft_entry__ as g; g.build()"`` (nvcc, sm_100a).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "csrc", "libhymeta_b200.so")
+
+_i, _i64, _f, _p, _sz = C.c_int, C.c_int64, C.c_float, C.c_void_p, C.c_size_t
+
+# name -> (restype, argtypes); mirrors include/hymeta_b200.h one to one
+SIGNATURES = {
+    "hymeta_abi_version": (_i, []),
+    "hymeta_status_string": (C.c_char_p, [_i]),
+    "hymeta_last_cuda_error": (_i, []),
+    "hymeta_launch_count": (_i64, []),
+    "hymeta_gla_decode": (_i, [_p] * 7 + [_i] * 5 + [_i64] * 12 + [_i, _f, _p]),
+    "hymeta_gla_prefill_varlen": (_i, [_p] * 10 + [_i] * 6 + [_i64] * 13 + [_i, _f, _i, _i, _p]),
+    "hymeta_kv_write_paged": (_i, [_p] * 5 + [_i] * 4 + [_i64] * 10 + [_p]),
+    "hymeta_swa_decode_workspace_bytes": (_sz, [_i] * 8),
+    "hymeta_swa_meta_decode_paged": (_i, [_p] * 9 + [_sz] + [_i] * 7 + [_i64, _i, _f] + [_i64] * 14 + [_p]),
+    "hymeta_swa_meta_prefill_varlen": (_i, [_p] * 10 + [_i64, _i] + [_i] * 9 + [_f] + [_i64] * 16 + [_p]),
+    "hymeta_state_zero_slots": (_i, [_p, _p, _i, _i, _i64, _i64, _i64, _p]),
+    "hymeta_state_copy_slot": (_i, [_p, _i, _i, _i, _i64, _i64, _i64, _p]),
+    "hymeta_selftest_umma": (_i, [_p]),
+}
+
+_lib = None
+
+
+class HymetaKernelError(RuntimeError):
+    pass
+
+
+def lib() -> C.CDLL:
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise ImportError(
+                f"{LIB_PATH} not found: the sm_100a kernel library is not built and there is no "
+                "fallback path. Run `python -c 'import __graft_entry__ as g; g.build()'`.")
+        h = C.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(h, name)      # AttributeError if the library lacks a declared symbol
+            fn.restype, fn.argtypes = res, args
+        if h.hymeta_abi_version() != 1:
+            raise ImportError("hymeta_b200 ABI version mismatch")
+        _lib = h
+    return _lib
+
+
+def check(status: int, what: str) -> None:
+    """Map a hymeta_status to the exception types of the reference boundary
+    (SURVEY 8b): bad arguments -> ValueError, launch failures -> RuntimeError."""
+    if status == 0:
+        return
+    msg = f"{what}: {lib().hymeta_status_string(status).decode()} (status {status})"
+    if status in (-1, -2, -3):
+        raise ValueError(msg)
+    if status == -4:
+        msg += f", cudaError {lib().hymeta_last_cuda_error()}"
+    raise HymetaKernelError(msg)

@@ -1,0 +1,244 @@
+"""Torch-facing wrappers over the C-ABI kernels.  PyTorch is plumbing only: device
+memory, the current stream and dtype/shape checks.  Every function enqueues on
+``torch.cuda.current_stream()`` and never synchronises (CUDA-graph safe).
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+
+from ._lib import check, lib
+
+INIT_ZERO, INIT_SLOT, INIT_META = 0, 1, 2
+
+_workspaces: dict = {}
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+def _req(t: torch.Tensor, name: str, dtype=None):
+    if not t.is_cuda:
+        raise ValueError(f"{name} must be a CUDA tensor (there is no CPU path)")
+    if dtype is not None and t.dtype != dtype:
+        raise ValueError(f"{name} must be {dtype}, got {t.dtype}")
+    if t.stride(-1) != 1:
+        raise ValueError(f"{name} must be contiguous in its last dimension")
+
+
+def launch_count() -> int:
+    """Kernels launched by the library so far in this process."""
+    return int(lib().hymeta_launch_count())
+
+
+# ----------------------------------------------------------------------------------- a2
+def gla_decode(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, g: torch.Tensor,
+               state: torch.Tensor, slot_idx: torch.Tensor, scale: Optional[float] = None,
+               out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """q [B,H,D]; k,v,g [B,Hk,D]; state [slots,Hs,D,D] bf16 (updated in place);
+    slot_idx [B] int32 (-1 = skip).  Returns o [B,H,D] bf16."""
+    B, H, D = q.shape
+    Hk, Hs = k.shape[1], state.shape[1]
+    for n, t in (("q", q), ("k", k), ("v", v), ("state", state)):
+        _req(t, n, torch.bfloat16)
+    _req(g, "g")
+    if g.dtype not in (torch.float32, torch.bfloat16):
+        raise ValueError("g must be float32 or bfloat16")
+    _req(slot_idx, "slot_idx", torch.int32)
+    if state.stride(2) != D or state.shape[2] != D or state.shape[3] != D:
+        raise ValueError("state must be [slots, Hs, D, D] with contiguous [D, D] tiles")
+    if out is None:
+        out = torch.empty(B, H, D, dtype=q.dtype, device=q.device)
+    if scale is None:
+        scale = D ** -0.5
+    check(lib().hymeta_gla_decode(
+        _ptr(q), _ptr(k), _ptr(v), _ptr(g), _ptr(out), _ptr(state), _ptr(slot_idx),
+        B, H, Hk, Hs, D, q.stride(0), q.stride(1), k.stride(0), k.stride(1), v.stride(0), v.stride(1),
+        g.stride(0), g.stride(1), out.stride(0), out.stride(1), state.stride(0), state.stride(1),
+        int(g.dtype == torch.float32), float(scale), _stream()), "hymeta_gla_decode")
+    return out
+
+
+# ----------------------------------------------------------------------------------- a3
+def gla_prefill_varlen(q, k, v, g, state, cu_seqlens, slot_idx, init_mode,
+                       meta_state: Optional[torch.Tensor] = None, scale: Optional[float] = None,
+                       write_state: bool = True, max_seqlen: Optional[int] = None,
+                       out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """q [T,H,D]; k,v,g [T,Hk,D]; state [slots,Hs,D,D]; cu_seqlens [N+1], slot_idx [N],
+    init_mode [N] int32 device tensors.  Returns o [T,H,D] bf16; writes final states."""
+    T, H, D = q.shape
+    Hk, Hs = k.shape[1], state.shape[1]
+    N = cu_seqlens.numel() - 1
+    for n, t in (("q", q), ("k", k), ("v", v), ("state", state)):
+        _req(t, n, torch.bfloat16)
+    _req(g, "g")
+    for n, t in (("cu_seqlens", cu_seqlens), ("slot_idx", slot_idx), ("init_mode", init_mode)):
+        _req(t, n, torch.int32)
+    if meta_state is not None:
+        _req(meta_state, "meta_state", torch.bfloat16)
+    if out is None:
+        out = torch.empty(T, H, D, dtype=q.dtype, device=q.device)
+    if scale is None:
+        scale = D ** -0.5
+    check(lib().hymeta_gla_prefill_varlen(
+        _ptr(q), _ptr(k), _ptr(v), _ptr(g), _ptr(out), _ptr(state), _ptr(meta_state),
+        _ptr(cu_seqlens), _ptr(slot_idx), _ptr(init_mode), N, T, H, Hk, Hs, D,
+        q.stride(0), q.stride(1), k.stride(0), k.stride(1), v.stride(0), v.stride(1),
+        g.stride(0), g.stride(1), out.stride(0), out.stride(1), state.stride(0), state.stride(1),
+        0 if meta_state is None else meta_state.stride(0),
+        int(g.dtype == torch.float32), float(scale), int(write_state),
+        int(max_seqlen if max_seqlen is not None else T), _stream()), "hymeta_gla_prefill_varlen")
+    return out
+
+
+# ----------------------------------------------------------------------------------- a9
+def kv_write_paged(key, value, k_cache, v_cache, slot_mapping) -> None:
+    """key,value [T,Hkv,D]; caches [nb,bs,Hkv,D]; slot_mapping [T] int64 (<0 = skip)."""
+    T, Hkv, D = key.shape
+    for n, t in (("key", key), ("value", value), ("k_cache", k_cache), ("v_cache", v_cache)):
+        _req(t, n, torch.bfloat16)
+    _req(slot_mapping, "slot_mapping", torch.int64)
+    if slot_mapping.numel() < T:
+        raise ValueError("slot_mapping shorter than the number of tokens")
+    check(lib().hymeta_kv_write_paged(
+        _ptr(key), _ptr(value), _ptr(k_cache), _ptr(v_cache), _ptr(slot_mapping), T, Hkv, D,
+        k_cache.shape[1], key.stride(0), key.stride(1), value.stride(0), value.stride(1),
+        k_cache.stride(0), k_cache.stride(1), k_cache.stride(2),
+        v_cache.stride(0), v_cache.stride(1), v_cache.stride(2), _stream()), "hymeta_kv_write_paged")
+
+
+# ----------------------------------------------------------------------------------- a8
+def _workspace(nbytes: int, device) -> torch.Tensor:
+    key = (device.index, torch.cuda.current_stream().cuda_stream)
+    ws = _workspaces.get(key)
+    if ws is None or ws.numel() < nbytes:
+        if torch.cuda.is_current_stream_capturing():
+            raise RuntimeError("workspace must be sized before CUDA-graph capture "
+                               "(run one eager step first)")
+        ws = torch.empty(max(nbytes, 1 << 20), dtype=torch.uint8, device=device)
+        _workspaces[key] = ws
+    return ws
+
+
+def swa_meta_decode_paged(q, k_cache, v_cache, block_tables, cache_seqlens, meta_k, meta_v,
+                          window_left: int, scale: Optional[float] = None,
+                          out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """q [B,H,D]; caches [nb,bs,Hkv,D]; block_tables [B,max_blocks] int32; cache_seqlens [B]
+    int32; meta_k/meta_v [M,Hkv,D] or None.  Returns out [B,H,D]."""
+    B, H, D = q.shape
+    Hkv, bs = k_cache.shape[2], k_cache.shape[1]
+    M = 0 if meta_k is None else meta_k.shape[0]
+    for n, t in (("q", q), ("k_cache", k_cache), ("v_cache", v_cache)):
+        _req(t, n, torch.bfloat16)
+    _req(block_tables, "block_tables", torch.int32)
+    _req(cache_seqlens, "cache_seqlens", torch.int32)
+    if M:
+        _req(meta_k, "meta_k", torch.bfloat16)
+        _req(meta_v, "meta_v", torch.bfloat16)
+    if out is None:
+        out = torch.empty(B, H, D, dtype=q.dtype, device=q.device)
+    if scale is None:
+        scale = D ** -0.5
+    max_blocks = block_tables.shape[1]
+    nbytes = lib().hymeta_swa_decode_workspace_bytes(B, H, Hkv, D, max_blocks, bs, window_left, M)
+    ws = _workspace(nbytes, q.device)
+    check(lib().hymeta_swa_meta_decode_paged(
+        _ptr(q), _ptr(k_cache), _ptr(v_cache), _ptr(block_tables), _ptr(cache_seqlens),
+        _ptr(meta_k), _ptr(meta_v), _ptr(out), _ptr(ws), ws.numel(),
+        B, H, Hkv, D, M, bs, max_blocks, block_tables.stride(0), int(window_left), float(scale),
+        q.stride(0), q.stride(1), out.stride(0), out.stride(1),
+        k_cache.stride(0), k_cache.stride(1), k_cache.stride(2),
+        v_cache.stride(0), v_cache.stride(1), v_cache.stride(2),
+        meta_k.stride(0) if M else 0, meta_k.stride(1) if M else 0,
+        meta_v.stride(0) if M else 0, meta_v.stride(1) if M else 0, _stream()),
+        "hymeta_swa_meta_decode_paged")
+    return out
+
+
+# ----------------------------------------------------------------------------------- a7
+def swa_meta_prefill_varlen(q1, k1, v1, q2, meta_k, meta_v, cu_seqlens_q, cu_seqlens_k,
+                            max_seqlen_q: int, window_left: int, scale: Optional[float] = None,
+                            block_tables: Optional[torch.Tensor] = None,
+                            out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """q1 [Tq,H,D]; k1,v1 [Tk,Hkv,D] (or paged caches [nb,bs,Hkv,D] with block_tables);
+    q2 [M,H,D] or None; meta_k/meta_v [M,Hkv,D] or None.  Returns [(M if q2)+Tq, H, D], meta
+    rows first."""
+    Tq, H, D = q1.shape
+    paged = block_tables is not None
+    Hkv = k1.shape[-2]
+    M = 0 if meta_k is None else meta_k.shape[0]
+    for n, t in (("q1", q1), ("k1", k1), ("v1", v1)):
+        _req(t, n, torch.bfloat16)
+    _req(cu_seqlens_q, "cu_seqlens_q", torch.int32)
+    _req(cu_seqlens_k, "cu_seqlens_k", torch.int32)
+    if q2 is not None:
+        _req(q2, "q2", torch.bfloat16)
+        if M == 0 or q2.shape[0] != M:
+            raise ValueError("q2 requires meta keys with the same number of rows")
+    if M:
+        _req(meta_k, "meta_k", torch.bfloat16)
+        _req(meta_v, "meta_v", torch.bfloat16)
+    N = cu_seqlens_q.numel() - 1
+    rows = Tq + (M if q2 is not None else 0)
+    if out is None:
+        out = torch.empty(rows, H, D, dtype=q1.dtype, device=q1.device)
+    if scale is None:
+        scale = D ** -0.5
+    if paged:
+        _req(block_tables, "block_tables", torch.int32)
+        Tk, bs = 0, k1.shape[1]
+        k_st, k_sh, v_st, v_sh = k1.stride(1), k1.stride(2), v1.stride(1), v1.stride(2)
+        kc_sblk, vc_sblk, bt_stride = k1.stride(0), v1.stride(0), block_tables.stride(0)
+    else:
+        Tk, bs = k1.shape[0], 0
+        k_st, k_sh, v_st, v_sh = k1.stride(0), k1.stride(1), v1.stride(0), v1.stride(1)
+        kc_sblk = vc_sblk = bt_stride = 0
+    check(lib().hymeta_swa_meta_prefill_varlen(
+        _ptr(q1), _ptr(k1), _ptr(v1), _ptr(q2), _ptr(meta_k), _ptr(meta_v), _ptr(out),
+        _ptr(cu_seqlens_q), _ptr(cu_seqlens_k), _ptr(block_tables), bt_stride, bs,
+        N, Tq, Tk, H, Hkv, D, M, int(max_seqlen_q), int(window_left), float(scale),
+        q1.stride(0), q1.stride(1), k_st, k_sh, v_st, v_sh,
+        q2.stride(0) if q2 is not None else 0, q2.stride(1) if q2 is not None else 0,
+        meta_k.stride(0) if M else 0, meta_k.stride(1) if M else 0,
+        meta_v.stride(0) if M else 0, meta_v.stride(1) if M else 0,
+        out.stride(0), out.stride(1), kc_sblk, vc_sblk, _stream()),
+        "hymeta_swa_meta_prefill_varlen")
+    return out
+
+
+# ----------------------------------------------------------------------------------- a5
+def state_zero_slots(state: torch.Tensor, slots: torch.Tensor) -> None:
+    """state [L, slots, Hs, D, D] bf16; zero state[:, slots[i]] for every i (slots int32, <0 skipped)."""
+    _req(state, "state", torch.bfloat16)
+    _req(slots, "slots", torch.int32)
+    L = state.shape[0]
+    slot_elems = state[0, 0].numel()
+    if not state[0, 0].is_contiguous():
+        raise ValueError("each (layer, slot) state block must be contiguous")
+    check(lib().hymeta_state_zero_slots(_ptr(state), _ptr(slots), slots.numel(), L,
+                                        state.stride(0), state.stride(1), slot_elems, _stream()),
+          "hymeta_state_zero_slots")
+
+
+def state_copy_slot(state: torch.Tensor, from_slot: int, to_slot: int) -> None:
+    _req(state, "state", torch.bfloat16)
+    L = state.shape[0]
+    slot_elems = state[0, 0].numel()
+    check(lib().hymeta_state_copy_slot(_ptr(state), int(from_slot), int(to_slot), L,
+                                       state.stride(0), state.stride(1), slot_elems, _stream()),
+          "hymeta_state_copy_slot")
+
+
+def selftest_umma() -> float:
+    import ctypes as C
+    err = C.c_float(0.0)
+    rc = lib().hymeta_selftest_umma(C.addressof(err))
+    if rc != 0:
+        raise RuntimeError(f"tcgen05/TMA self test failed at case {rc} (max err {err.value})")
+    return err.value
