@@ -1,0 +1,107 @@
+"""Per-kernel micro-benchmarks at the BASELINE config shapes (CUDA events, L2 flushed between
+iterations).  Development aid; bench.py is the contract benchmark."""
+import argparse
+import json
+import os
+import sys
+
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from vllm_hymeta_b200 import ops  # noqa: E402
+
+PEAK = 6524.6
+try:
+    PEAK = json.load(open(os.path.join(os.path.dirname(__file__), "..", "MEASURED_PEAKS.json")))["hbm_gbs"]
+except Exception:
+    pass
+
+
+def timeit(fn, iters=20, warmup=3, flush=None):
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    ts = []
+    for _ in range(iters):
+        if flush is not None:
+            flush.zero_()
+        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s.record()
+        fn()
+        e.record()
+        torch.cuda.synchronize()
+        ts.append(s.elapsed_time(e))
+    ts.sort()
+    return ts[len(ts) // 2] * 1e-3
+
+
+def bench_gla_decode(B, H=28, Hkv=4, D=128, layout="compact", gdt=torch.bfloat16, flush=None):
+    dev = "cuda"
+    Hs = Hkv if layout == "compact" else H
+    Hk = Hkv if layout == "compact" else H
+    q = torch.randn(B, H, D, device=dev).bfloat16().relu()
+    k = torch.randn(B, Hk, D, device=dev).bfloat16().relu()
+    v = torch.randn(B, Hk, D, device=dev).bfloat16()
+    g = (-torch.rand(B, Hk, D, device=dev) * 0.1).to(gdt)
+    state = torch.zeros(B, Hs, D, D, device=dev, dtype=torch.bfloat16)
+    slots = torch.randperm(B, device=dev).to(torch.int32)
+    out = torch.empty(B, H, D, device=dev, dtype=torch.bfloat16)
+    t = timeit(lambda: ops.gla_decode(q, k, v, g, state, slots, out=out), flush=flush)
+    gb = g.element_size()
+    alg = B * (Hs * 2 * D * D * 2 + H * 2 * D * 2 + Hk * D * (4 + gb))
+    print(f"gla_decode B={B} layout={layout}: {t*1e6:8.1f} us  {alg/t/1e9:8.1f} GB/s "
+          f"({alg/t/1e9/PEAK:.2%} of measured {PEAK:.0f})  alg={alg/1e6:.1f} MB")
+
+
+def bench_swa_decode(B, ctx, H=28, Hkv=4, D=128, bs=256, wl=4096, M=0, flush=None):
+    dev = "cuda"
+    nblk = (ctx + bs - 1) // bs
+    nb = B * nblk + 1
+    kv = torch.randn(2, nb, bs, Hkv, D, device=dev).bfloat16()
+    tables = torch.randperm(nb - 1, device=dev).to(torch.int32).view(B, nblk)
+    lens = torch.full((B,), ctx, dtype=torch.int32, device=dev)
+    q = torch.randn(B, H, D, device=dev).bfloat16()
+    mk = mv = None
+    if M:
+        mk = torch.randn(M, Hkv, D, device=dev).bfloat16()
+        mv = torch.randn(M, Hkv, D, device=dev).bfloat16()
+    out = torch.empty(B, H, D, device=dev, dtype=torch.bfloat16)
+    t = timeit(lambda: ops.swa_meta_decode_paged(q, kv[0], kv[1], tables, lens, mk, mv, wl, out=out),
+               flush=flush)
+    nk = min(ctx, wl + 1) if wl >= 0 else ctx
+    alg = B * (Hkv * 2 * D * 2 * nk + H * 2 * D * 2) + Hkv * 2 * D * 2 * M
+    print(f"swa_decode B={B} ctx={ctx} wl={wl} M={M}: {t*1e6:8.1f} us  {alg/t/1e9:8.1f} GB/s "
+          f"({alg/t/1e9/PEAK:.2%})  alg={alg/1e6:.1f} MB")
+
+
+def bench_kv_write(T, Hkv=4, D=128, bs=256, flush=None):
+    dev = "cuda"
+    nb = (T + bs - 1) // bs
+    kv = torch.zeros(2, nb, bs, Hkv, D, device=dev, dtype=torch.bfloat16)
+    key = torch.randn(T, Hkv, D, device=dev).bfloat16()
+    val = torch.randn(T, Hkv, D, device=dev).bfloat16()
+    slots = torch.randperm(nb * bs, device=dev)[:T].to(torch.int64)
+    t = timeit(lambda: ops.kv_write_paged(key, val, kv[0], kv[1], slots), flush=flush)
+    alg = T * (2 * Hkv * D * 2 * 2 + 8)
+    print(f"kv_write T={T}: {t*1e6:8.1f} us  {alg/t/1e9:8.1f} GB/s ({alg/t/1e9/PEAK:.2%})")
+
+
+if __name__ == "__main__":
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--which", default="all")
+    a = ap.parse_args()
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+    if a.which in ("all", "gla_decode"):
+        for B in (64, 256, 1000):
+            bench_gla_decode(B, flush=flush)
+        bench_gla_decode(64, layout="reference", flush=flush)
+        bench_gla_decode(1000, layout="reference", gdt=torch.float32, flush=flush)
+    if a.which in ("all", "swa_decode"):
+        bench_swa_decode(64, 8192, flush=flush)
+        bench_swa_decode(64, 8704, M=128, wl=4095, flush=flush)
+        bench_swa_decode(1000, 5000, flush=flush)
+        bench_swa_decode(8, 8192, flush=flush)
+        bench_swa_decode(1, 8192, flush=flush)
+    if a.which in ("all", "kv_write"):
+        bench_kv_write(64)
+        bench_kv_write(524288, flush=flush)
