@@ -4,8 +4,3 @@ extern "C" int hymeta_gla_prefill_varlen(const void*, const void*, const void*, 
     const void*, const int32_t*, const int32_t*, const int32_t*, int, int, int, int, int, int,
     int64_t, int64_t, int64_t, int64_t, int64_t, int64_t, int64_t, int64_t, int64_t, int64_t, int64_t,
     int64_t, int64_t, int, float, int, int, void*) { return HYMETA_ERR_UNSUPPORTED; }
-extern "C" int hymeta_swa_meta_prefill_varlen(const void*, const void*, const void*, const void*,
-    const void*, const void*, void*, const int32_t*, const int32_t*, const int32_t*, int64_t, int,
-    int, int, int, int, int, int, int, int, int, float, int64_t, int64_t, int64_t, int64_t, int64_t,
-    int64_t, int64_t, int64_t, int64_t, int64_t, int64_t, int64_t, int64_t, int64_t, int64_t, int64_t,
-    void*) { return HYMETA_ERR_UNSUPPORTED; }
