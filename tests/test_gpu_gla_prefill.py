@@ -1,0 +1,108 @@
+"""-m gpu parity: GLA chunked prefill (tcgen05) through the C-ABI vs the CPU oracle recurrence."""
+import pytest
+import torch
+
+from gpu_util import DEV, assert_close
+from oracle import gla as ogla
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ops():
+    import __graft_entry__ as ge
+    ge.build()
+    from vllm_hymeta_b200 import ops as o
+    return o
+
+
+def run_case(ops, lens, H, Hkv, model, layout, seed, modes=None, slots=None, write_state=True,
+             g_override=None):
+    D = 128
+    T = sum(lens)
+    q, k, v, g = ogla.synth_gla_inputs(T, H, Hkv, D, model, seed=seed)
+    if g_override is not None:
+        g = torch.full_like(g, g_override)
+    Hs = Hkv if layout == "compact" else H
+    if layout == "reference":
+        k, v, g = (x.repeat_interleave(H // Hkv, 1).contiguous() for x in (k, v, g))
+    N = len(lens)
+    gen = torch.Generator().manual_seed(seed + 100)
+    nslots = N + 2
+    state = (torch.randn(nslots, Hs, D, D, generator=gen) * 0.2).bfloat16()
+    meta = (torch.randn(Hs, D, D, generator=gen) * 0.2).bfloat16()
+    slots = slots if slots is not None else torch.randperm(nslots, generator=gen)[:N].tolist()
+    modes = modes if modes is not None else [i % 3 for i in range(N)]
+    cu = [0]
+    for L in lens:
+        cu.append(cu[-1] + L)
+    ref_state = state.clone()
+    ref_o = ogla.gla_prefill_varlen(q, k, v, g, ref_state, cu, slots, modes, meta,
+                                    write_state=write_state, out_dtype=torch.float32)
+    d_state = state.to(DEV)
+    i32 = lambda x: torch.tensor(x, dtype=torch.int32, device=DEV)
+    o = ops.gla_prefill_varlen(q.to(DEV), k.to(DEV), v.to(DEV), g.to(DEV), d_state, i32(cu),
+                               i32(slots), i32(modes), meta.to(DEV), write_state=write_state,
+                               max_seqlen=max(lens))
+    torch.cuda.synchronize()
+    assert_close(o, ref_o, f"gla prefill o {lens} {model} {layout}")
+    assert_close(d_state, ref_state, f"gla prefill state {lens} {model} {layout}")
+    used = set(s for s in slots if s >= 0) if write_state else set()
+    for s in range(nslots):
+        if s not in used:
+            assert torch.equal(d_state[s].cpu(), state[s]), f"slot {s} modified"
+    return o, d_state
+
+
+@pytest.mark.parametrize("model", ["7b", "70b"])
+def test_single_sequence(ops, model):
+    run_case(ops, [100], 28, 4, model, "compact", 1, modes=[0])
+
+
+@pytest.mark.parametrize("model", ["7b", "70b"])
+def test_ragged_slots_and_init_modes(ops, model):
+    run_case(ops, [1, 15, 16, 17, 200, 33, 64], 28, 4, model, "compact", 2)
+
+
+def test_reference_and_mixed_layouts(ops):
+    run_case(ops, [40, 70], 8, 2, "70b", "reference", 3)      # one state per q-head, repeated k/v/g
+    run_case(ops, [40, 70], 8, 2, "7b", "mixed", 4)           # one state per q-head, un-repeated k/v/g
+
+
+def test_tp4_shard_geometry(ops):
+    run_case(ops, [300], 7, 1, "70b", "compact", 5, modes=[2])
+
+
+def test_strong_decay_at_clamp_limit(ops):
+    """70B worst case: k clamped at 0.95 -> g = log(0.05) = -2.996 on every channel and step."""
+    run_case(ops, [130], 14, 2, "70b", "compact", 6, modes=[1], g_override=-2.9957)
+
+
+def test_no_decay(ops):
+    run_case(ops, [90], 14, 2, "7b", "compact", 7, modes=[1], g_override=0.0)
+
+
+def test_write_state_false_and_pad_slot(ops):
+    run_case(ops, [50, 20], 28, 4, "70b", "compact", 8, write_state=False)
+    run_case(ops, [50, 20], 28, 4, "70b", "compact", 9, slots=[-1, 1], modes=[0, 1])
+
+
+def test_long_sequence_and_prefill_decode_consistency(ops):
+    """T=4096 vs the fp32 oracle, and the size-independent property
+    prefill(T) == prefill(T-8) followed by 8 recurrent decode steps (same final state / outputs)."""
+    H, Hkv, D, T = 28, 4, 128, 4096
+    q, k, v, g = ogla.synth_gla_inputs(T, H, Hkv, D, "70b", seed=11)
+    ref_o, ref_S = ogla.gla_chunked(q, k, v, g, chunk=16)
+    dq, dk, dv, dg = (x.to(DEV) for x in (q, k, v, g))
+    i32 = lambda x: torch.tensor(x, dtype=torch.int32, device=DEV)
+    st = torch.zeros(2, Hkv, D, D, dtype=torch.bfloat16, device=DEV)
+    o = ops.gla_prefill_varlen(dq, dk, dv, dg, st, i32([0, T]), i32([0]), i32([0]))
+    assert_close(o, ref_o, "long o")
+    assert_close(st[0], ref_S[::H // Hkv], "long state")
+    o2 = ops.gla_prefill_varlen(dq[:T - 8], dk[:T - 8], dv[:T - 8], dg[:T - 8], st,
+                                i32([0, T - 8]), i32([1]), i32([0]))
+    tail = [ops.gla_decode(dq[t:t + 1], dk[t:t + 1], dv[t:t + 1], dg[t:t + 1], st, i32([1]))
+            for t in range(T - 8, T)]
+    assert torch.equal(o2, o[:T - 8])
+    assert_close(torch.cat(tail), ref_o[T - 8:], "decode tail")
+    assert_close(st[1], st[0].float(), "state after prefill+decode", maxabs_frac=2.0 ** -6, rel_rms=1e-2)
