@@ -1,0 +1,447 @@
+#!/usr/bin/env python
+"""Contract benchmark: the Hymeta-7B attention stack (14 GLA + 14 SWA layers), batch 64,
+prefill 8192 tokens + 512 decode steps per request (BASELINE.json configs[1]) on N B200s.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+
+One "step" = one pass of the whole hot path over one synthetic batch: paged-KV write + SWA prefill
+for 14 layers, GLA chunked prefill for 14 layers, then 512 decode steps of (KV write + SWA paged
+decode) x 14 and GLA recurrent decode x 14.  Prints ONE JSON line (see DESIGN.md "Measurement").
+
+N > 1 (torchrun, one rank per GPU): heads are sharded min(N,4)-way exactly as vLLM TP shards them
+(28/4 q/kv heads -> 14/2 -> 7/1) and requests are sharded beyond that (N=8: 4 head shards x 2
+request shards); the global batch is 64*N so per-GPU work is constant (weak scaling).  The path has
+no exchange step, hence no collective in the data path.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+H_FULL, HKV_FULL, D = 28, 4, 128
+N_GLA_LAYERS = N_SWA_LAYERS = 14
+WINDOW_LEFT = 4096          # 7B: window_size=(W, 0) -> W keys before the query
+BLOCK_SIZE = 256
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--batch", type=int, default=64)
+    ap.add_argument("--prefill", type=int, default=8192)
+    ap.add_argument("--decode", type=int, default=512)
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+# ----------------------------------------------------------------------------------------------
+# CPU arm: the reference's torch path (oracle port) on the host cores
+# ----------------------------------------------------------------------------------------------
+def cpu_sample(prefill_T: int, decode_steps: int, threads: int):
+    """One 7B GLA layer + one SWA layer, B=1: prefill `prefill_T` tokens then `decode_steps`
+    single-token steps, fp32 torch on CPU.  Returns seconds."""
+    import torch
+    from oracle import gla as ogla, swa as oswa
+    torch.set_num_threads(threads)
+    T = prefill_T + decode_steps
+    q, k, v, g = ogla.synth_gla_inputs(T, H_FULL, HKV_FULL, D, "7b", seed=0, dtype=torch.float32)
+    sq, sk, sv, _, _ = oswa.synth_swa_inputs(T, H_FULL, HKV_FULL, D, seed=1, dtype=torch.float32)
+    t0 = time.perf_counter()
+    # GLA prefill + decode (step recurrence, as the reference's torch path does it)
+    o, S = ogla.gla_recurrent(q[:prefill_T], k[:prefill_T], v[:prefill_T], g[:prefill_T])
+    for t in range(prefill_T, T):
+        o, S = ogla.gla_recurrent(q[t:t + 1], k[t:t + 1], v[t:t + 1], g[t:t + 1], S)
+    # SWA prefill + decode (dense masked softmax)
+    oswa.swa_meta_dense(sq[:prefill_T], sk[:prefill_T], sv[:prefill_T], None, None, None, WINDOW_LEFT)
+    for t in range(prefill_T, T):
+        lo = max(0, t - WINDOW_LEFT)
+        oswa.swa_meta_dense(sq[t:t + 1], sk[lo:t + 1], sv[lo:t + 1], None, None, None, -1)
+    return time.perf_counter() - t0
+
+
+def cpu_baseline(threads: int, prefill_T=2048, decode_steps=64, reps=2):
+    best = min(cpu_sample(prefill_T, decode_steps, threads) for _ in range(reps))
+    tokens = prefill_T + decode_steps
+    # the stack has 14 layers of each kind; the sample ran one of each
+    value = tokens / (best * N_GLA_LAYERS)
+    return {"value": value, "unit": "tok/s", "cores": threads, "kind": "port",
+            "sample": f"oracle port of the reference torch path, fp32, 1 GLA + 1 SWA layer (7B shape, "
+                      f"28/4 heads, window {WINDOW_LEFT}), B=1, prefill {prefill_T} + {decode_steps} "
+                      f"decode steps, best of {reps}; scaled x1/14 to the 14+14-layer stack",
+            "seconds": best}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    cpu_sample(256, 4, threads)                    # warm-up (allocator, thread pool)
+    for _ in range(max(0, args.warmup - 1)):
+        cpu_sample(256, 4, threads)
+    pt, ds = 2048, 64
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        cpu_sample(pt, ds, threads)
+    dt = (time.perf_counter() - t0) / args.steps
+    value = (pt + ds) / (dt * N_GLA_LAYERS)
+    line = {
+        "impl": "reference", "metric": "attention-stack throughput (prefill + decode tokens)",
+        "value": value, "unit": "tok/s", "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(args, 1),
+        "cpu_baseline": {"value": value, "unit": "tok/s", "cores": threads, "kind": "port",
+                         "sample": f"each step: oracle port of the reference torch path, fp32, 1 GLA + 1 SWA "
+                                   f"layer at the 7B shape, B=1, prefill {pt} + {ds} decode steps, scaled "
+                                   f"x1/14 to the 14+14-layer stack"},
+        "e2e": {"value": value, "unit": "tok/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(args, n):
+    tp = min(n, 4)
+    return {"workload": f"hymeta7b_attention_stack_{N_GLA_LAYERS}gla+{N_SWA_LAYERS}swa_"
+                        f"prefill{args.prefill}_decode{args.decode}_batch{args.batch}_per_gpu",
+            "global_batch": args.batch * n, "prefill_len": args.prefill, "decode_steps": args.decode,
+            "heads_q_kv": [H_FULL, HKV_FULL], "head_dim": D, "window_left": WINDOW_LEFT,
+            "kv_block_size": BLOCK_SIZE, "parallelism": f"tp{tp}(heads) x dp{n // tp}(requests)",
+            "l2": "inputs larger than L2 (>= 5 GB streamed per layer; decode KV 0.5 GB per layer-step)"}
+
+
+# ----------------------------------------------------------------------------------------------
+# GPU arm
+# ----------------------------------------------------------------------------------------------
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.rows, self.proc = [], None
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                 "-i", str(index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.perf_counter(), line.strip()))
+
+    def stop(self, t0, t1):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons = [], None, set()
+        for t, line in self.rows:
+            if t < t0 or t > t1:
+                continue
+            f = [x.strip() for x in line.split(",")]
+            try:
+                sm.append(float(f[0])); mx = float(f[1])
+            except Exception:
+                continue
+            for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown",
+                                  "sw_power_cap"), f[3:7]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def run_gpu(args):
+    import torch
+    import torch.distributed as dist
+    from vllm_hymeta_b200 import ops
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    n = max(world, 1)
+    tp = min(n, 4)
+    H, Hkv = H_FULL // tp, HKV_FULL // tp
+    B = args.batch * tp            # requests resident on this GPU (its request shard)
+    Tp, Sd = args.prefill, args.decode
+    T = B * Tp
+    bs = BLOCK_SIZE
+    bf = torch.bfloat16
+    torch.manual_seed(1234 + rank)
+
+    # ---- synthetic inputs, resident in HBM
+    def randn(*shape):
+        return torch.randn(*shape, device=dev, dtype=bf)
+    swa_q, swa_k, swa_v = randn(T, H, D), randn(T, Hkv, D), randn(T, Hkv, D)
+    gla_q = randn(T, H, D).relu_()
+    gla_k = randn(T, Hkv, D).relu_()
+    gla_v = randn(T, Hkv, D)
+    gla_g = (torch.nn.functional.logsigmoid(torch.randn(T, Hkv, D, device=dev)) / 16).to(bf)
+    out = torch.empty(T, H, D, device=dev, dtype=bf)
+    dq, dk, dv = randn(B, H, D), randn(B, Hkv, D), randn(B, Hkv, D)
+    gq, gk, gv = randn(B, H, D).relu_(), randn(B, Hkv, D).relu_(), randn(B, Hkv, D)
+    gg = (torch.nn.functional.logsigmoid(torch.randn(B, Hkv, D, device=dev)) / 16).to(bf)
+    dout_swa = torch.empty(B, H, D, device=dev, dtype=bf)
+    dout_gla = torch.empty(B, H, D, device=dev, dtype=bf)
+
+    # ---- paged KV (block tables = seeded permutation of physical blocks) and slot states
+    blocks_per_seq = (Tp + Sd + bs - 1) // bs
+    nb = B * blocks_per_seq
+    kv_caches = [torch.zeros(2, nb, bs, Hkv, D, device=dev, dtype=bf) for _ in range(N_SWA_LAYERS)]
+    gen = torch.Generator(device="cpu").manual_seed(7)
+    tables_h = torch.randperm(nb, generator=gen).to(torch.int32).view(B, blocks_per_seq)
+    tables = tables_h.to(dev)
+    pos = torch.arange(Tp)
+    slot_prefill = (tables_h.long()[:, pos // bs] * bs + (pos % bs)).reshape(-1).to(dev)
+    cu = (torch.arange(B + 1, dtype=torch.int32) * Tp).to(dev)
+    gla_state = torch.zeros(N_GLA_LAYERS, B, Hkv, D, D, device=dev, dtype=bf)
+    slots = torch.randperm(B, generator=gen).to(torch.int32).to(dev)
+    init_mode = torch.zeros(B, dtype=torch.int32, device=dev)
+    seqlens = torch.zeros(B, dtype=torch.int32, device=dev)
+    slot_decode = torch.zeros(B, dtype=torch.int64, device=dev)
+    tables_l = tables.long()
+
+    def prefill_swa():
+        for l in range(N_SWA_LAYERS):
+            ops.kv_write_paged(swa_k, swa_v, kv_caches[l][0], kv_caches[l][1], slot_prefill)
+            ops.swa_meta_prefill_varlen(swa_q, swa_k, swa_v, None, None, None, cu, cu, Tp,
+                                        WINDOW_LEFT, out=out)
+
+    def prefill_gla():
+        for l in range(N_GLA_LAYERS):
+            ops.gla_prefill_varlen(gla_q, gla_k, gla_v, gla_g, gla_state[l], cu, slots, init_mode,
+                                   max_seqlen=Tp, out=out)
+
+    def advance():          # position bookkeeping of one decode step, on device
+        p = seqlens.long()                                   # position of the new token
+        blk = tables_l.gather(1, (p // bs).unsqueeze(1)).squeeze(1)
+        slot_decode.copy_(blk * bs + p % bs)
+        seqlens.add_(1)
+
+    def decode_swa():
+        for l in range(N_SWA_LAYERS):
+            ops.kv_write_paged(dk, dv, kv_caches[l][0], kv_caches[l][1], slot_decode)
+            ops.swa_meta_decode_paged(dq, kv_caches[l][0], kv_caches[l][1], tables, seqlens, None,
+                                      None, WINDOW_LEFT, out=dout_swa)
+
+    def decode_gla():
+        for l in range(N_GLA_LAYERS):
+            ops.gla_decode(gq, gk, gv, gg, gla_state[l], slots, out=dout_gla)
+
+    # ---- CUDA graphs for the launch-bound decode step (SWA half, GLA half)
+    seqlens.fill_(Tp)
+    advance(); decode_swa(); decode_gla()                    # eager once: sizes workspaces
+    torch.cuda.synchronize()
+    side = torch.cuda.Stream()
+    l0 = ops.launch_count()
+    g_swa, g_gla = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
+    with torch.cuda.stream(side):
+        with torch.cuda.graph(g_swa, stream=side):
+            advance(); decode_swa()
+        l1 = ops.launch_count()
+        with torch.cuda.graph(g_gla, stream=side):
+            decode_gla()
+    l2 = ops.launch_count()
+    launches_swa_step, launches_gla_step = l1 - l0, l2 - l1
+    torch.cuda.synchronize()
+
+    ev = lambda: torch.cuda.Event(enable_timing=True)
+
+    def one_step(rec=None):
+        seqlens.fill_(Tp)
+        e = [ev() for _ in range(4)] if rec is not None else None
+        if e: e[0].record()
+        prefill_swa()
+        if e: e[1].record()
+        prefill_gla()
+        if e: e[2].record()
+        if rec is None:
+            for _ in range(Sd):
+                g_swa.replay(); g_gla.replay()
+        else:
+            marks = []
+            for _ in range(Sd):
+                a, b, c = ev(), ev(), ev()
+                a.record(); g_swa.replay(); b.record(); g_gla.replay(); c.record()
+                marks.append((a, b, c))
+            e[3].record()
+            rec.append((e, marks))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        one_step()
+    barrier()
+    launches0 = ops.launch_count()
+    sampler = ClockSampler(local) if rank == 0 else None
+    rec = []
+    t_wall0 = time.perf_counter()
+    start, stop = ev(), ev()
+    start.record()
+    for _ in range(args.steps):
+        one_step(rec)
+    stop.record()
+    barrier()
+    t_wall1 = time.perf_counter()
+    clocks = sampler.stop(t_wall0, t_wall1) if sampler else None
+    eager_launches = ops.launch_count() - launches0
+    elapsed = start.elapsed_time(stop) * 1e-3
+    if world > 1:
+        t = torch.tensor([elapsed], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        elapsed = t.item()
+    step_s = elapsed / args.steps
+    tokens_per_gpu = B * (Tp + Sd) / tp       # a head shard does 1/tp of each token's work
+    total_tokens = args.batch * n * (Tp + Sd)
+    value = total_tokens / step_s
+    gpu_launches = eager_launches + args.steps * Sd * (launches_swa_step + launches_gla_step)
+
+    # ---- phase timings from the events recorded inside the timed region
+    ms = lambda a, b: a.elapsed_time(b)
+    t_pswa = sum(ms(e[0], e[1]) for e, _ in rec) / args.steps
+    t_pgla = sum(ms(e[1], e[2]) for e, _ in rec) / args.steps
+    t_dec = sum(ms(e[2], e[3]) for e, _ in rec) / args.steps
+    t_dswa = sum(ms(a, b) for _, m in rec for a, b, c in m) / args.steps
+    t_dgla = sum(ms(b, c) for _, m in rec for a, b, c in m) / args.steps
+
+    peaks = {"hbm_gbs": 6650.0, "bf16_tflops_sustained": 1400.0, "src": "fallback"}
+    try:
+        pk = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        peaks = {"hbm_gbs": pk["hbm_gbs"], "bf16_tflops_sustained": pk["bf16_tflops_sustained"],
+                 "src": "measured"}
+    except Exception:
+        pass
+
+    # ---- algorithmic bytes / FLOPs per launch (per GPU-local heads)
+    b2 = 2
+    mean_ctx = Tp + (Sd + 1) / 2
+    nk = min(mean_ctx, WINDOW_LEFT + 1)
+    swa_dec_bytes = B * (Hkv * 2 * D * b2 * nk + H * 2 * D * b2 + Hkv * 2 * D * b2 + 4 * (nk / bs) + 8)
+    gla_dec_bytes = B * (Hkv * 2 * D * D * b2 + H * 2 * D * b2 + Hkv * D * (2 * b2 + 2))
+    swa_pf_flops = 0.0
+    for i in range(Tp):
+        swa_pf_flops += H * 4 * D * min(i + 1, WINDOW_LEFT + 1)
+    swa_pf_flops *= B
+    gla_pf_bytes = T * (H * 2 * D * b2 + Hkv * D * (2 * b2 + 2))
+    gla_pf_flops = T * H * (4 * D * D + 2 * 64 * 2 * D)
+    kernels = {
+        "swa_decode": {"share": t_dswa / (step_s * 1e3), "us_per_layer_step": t_dswa * 1e3 / (Sd * N_SWA_LAYERS),
+                       "bound": "hbm", "achieved": swa_dec_bytes / (t_dswa * 1e-3 / (Sd * N_SWA_LAYERS)) / 1e9,
+                       "peak": peaks["hbm_gbs"], "unit": "GB/s"},
+        "gla_decode": {"share": t_dgla / (step_s * 1e3), "us_per_layer_step": t_dgla * 1e3 / (Sd * N_GLA_LAYERS),
+                       "bound": "hbm", "achieved": gla_dec_bytes / (t_dgla * 1e-3 / (Sd * N_GLA_LAYERS)) / 1e9,
+                       "peak": peaks["hbm_gbs"], "unit": "GB/s"},
+        "swa_prefill": {"share": t_pswa / (step_s * 1e3), "ms_per_layer": t_pswa / N_SWA_LAYERS,
+                        "tok_s_per_layer": T / (t_pswa * 1e-3 / N_SWA_LAYERS),
+                        "bound": "tensor", "achieved": swa_pf_flops / (t_pswa * 1e-3 / N_SWA_LAYERS) / 1e12,
+                        "peak": peaks["bf16_tflops_sustained"], "unit": "TFLOP/s"},
+        "gla_prefill": {"share": t_pgla / (step_s * 1e3), "ms_per_layer": t_pgla / N_GLA_LAYERS,
+                        "tok_s_per_layer": T / (t_pgla * 1e-3 / N_GLA_LAYERS),
+                        "bound": "hbm", "achieved": gla_pf_bytes / (t_pgla * 1e-3 / N_GLA_LAYERS) / 1e9,
+                        "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                        "tensor_tflops": gla_pf_flops / (t_pgla * 1e-3 / N_GLA_LAYERS) / 1e12},
+    }
+    for kk in kernels.values():
+        kk["frac"] = kk["achieved"] / kk["peak"]
+    dom = max(kernels, key=lambda x: kernels[x]["share"])
+    roofline = {"kernel": dom, "bound": kernels[dom]["bound"], "achieved": kernels[dom]["achieved"],
+                "peak": kernels[dom]["peak"], "unit": kernels[dom]["unit"], "frac": kernels[dom]["frac"],
+                "traffic": None, "peak_source": f"{peaks['src']} (MEASURED_PEAKS.json, sustained)",
+                "note": "kv-write and split-K combine launches are inside the decode figure"}
+
+    # ---- e2e: the same step through the public ops with HOST buffers (pinned), copies timed
+    e2e = None
+    if not args.no_e2e:
+        dev_inputs = [swa_q, swa_k, swa_v, gla_q, gla_k, gla_v, gla_g, dq, dk, dv, gq, gk, gv, gg,
+                      tables, cu, slots, init_mode, slot_prefill]
+        host_inputs = [torch.empty(t.shape, dtype=t.dtype, pin_memory=True) for t in dev_inputs]
+        for hbuf, dbuf in zip(host_inputs, dev_inputs):
+            hbuf.copy_(dbuf)
+        host_out = [torch.empty(t.shape, dtype=t.dtype, pin_memory=True) for t in (dout_swa, dout_gla)]
+        h2d = sum(t.numel() * t.element_size() for t in dev_inputs)
+        d2h = sum(t.numel() * t.element_size() for t in host_out)
+
+        def e2e_step():
+            for hbuf, dbuf in zip(host_inputs, dev_inputs):
+                dbuf.copy_(hbuf, non_blocking=True)
+            one_step()
+            host_out[0].copy_(dout_swa, non_blocking=True)
+            host_out[1].copy_(dout_gla, non_blocking=True)
+        e2e_step()
+        barrier()
+        k = max(1, min(args.steps, 2))
+        s2, p2 = ev(), ev()
+        s2.record()
+        for _ in range(k):
+            e2e_step()
+        p2.record()
+        barrier()
+        el = s2.elapsed_time(p2) * 1e-3
+        if world > 1:
+            t = torch.tensor([el], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            el = t.item()
+        e2e = {"value": total_tokens / (el / k), "unit": "tok/s", "h2d_bytes_per_step": h2d,
+               "d2h_bytes_per_step": d2h, "steps": k,
+               "note": "per-step inputs (one layer-set of q/k/v/g activations, decode inputs, block "
+                       "tables, slot maps) copied from pinned host memory each step; last decode "
+                       "outputs read back"}
+
+    cpu = None
+    if rank == 0 and n == 1 and not args.no_cpu_baseline:
+        cpu = cpu_baseline(os.cpu_count() or 1)
+
+    if rank == 0:
+        line = {
+            "metric": "attention-stack throughput (prefill + decode tokens)", "value": value,
+            "unit": "tok/s", "n_gpus": n, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": step_s * 1e3, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "config": workload_config(args, n), "e2e": e2e, "gpu_launches": int(gpu_launches),
+            "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
+            "detail": {"prefill_tok_s": args.batch * n * Tp / ((t_pswa + t_pgla) * 1e-3),
+                       "decode_us_per_step": t_dec * 1e3 / Sd, "kernels": kernels,
+                       "tokens_per_gpu_equiv": tokens_per_gpu,
+                       "per_gpu": {"q_heads": H, "kv_heads": Hkv, "requests": B}},
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_gpu(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -115,7 +115,7 @@ def kv_write_paged(key, value, k_cache, v_cache, slot_mapping) -> None:
 
 # ----------------------------------------------------------------------------------- a8
 def _workspace(nbytes: int, device) -> torch.Tensor:
-    key = (device.index, torch.cuda.current_stream().cuda_stream)
+    key = device.index        # one workspace per device: calls on one device are stream-ordered by the caller
     ws = _workspaces.get(key)
     if ws is None or ws.numel() < nbytes:
         if torch.cuda.is_current_stream_capturing():
