@@ -111,7 +111,10 @@ int hymeta_kv_write_paged(const void* key, const void* value, void* k_cache, voi
  * cached keys at logical positions max(0, L-1-window_left) .. L-1], L = cache_seqlens[b]
  * (window_left < 0: all positions).  Logical position p lives at
  * cache[block_tables[b, p / block_size], p % block_size].  meta_k/meta_v: [M, Hkv, D] or null
- * when M == 0.  workspace: hymeta_swa_decode_workspace_bytes(...) bytes, any contents.
+ * when M == 0.  num_blocks = physical blocks in the cache (extent of the TMA tensor map),
+ * max_blocks = columns of block_tables.  block_size must be a multiple of 16 (as the reference
+ * requires, meta_attention.py:88-91).  workspace: hymeta_swa_decode_workspace_bytes(...) bytes,
+ * any contents.
  * ---------------------------------------------------------------------------------------------- */
 size_t hymeta_swa_decode_workspace_bytes(int B, int H, int Hkv, int D, int max_blocks,
                                          int block_size, int window_left, int M);
@@ -120,7 +123,8 @@ int hymeta_swa_meta_decode_paged(const void* q, const void* k_cache, const void*
                                  const void* meta_k, const void* meta_v, void* out,
                                  void* workspace, size_t workspace_bytes,
                                  int B, int H, int Hkv, int D, int M, int block_size,
-                                 int max_blocks, int64_t bt_stride, int window_left, float scale,
+                                 int num_blocks, int max_blocks, int64_t bt_stride,
+                                 int window_left, float scale,
                                  int64_t q_sb, int64_t q_sh, int64_t o_sb, int64_t o_sh,
                                  int64_t kc_sblk, int64_t kc_stok, int64_t kc_sh,
                                  int64_t vc_sblk, int64_t vc_stok, int64_t vc_sh,

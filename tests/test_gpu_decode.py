@@ -195,3 +195,30 @@ def test_swa_decode_kv_cache_views_and_padding(ops):
                                     torch.tensor(lens, dtype=torch.int32, device=DEV),
                                     k2.to(DEV), v2.to(DEV), wl)
     assert_close(out, ref, "swa decode views")
+
+
+@pytest.mark.parametrize("bs", [16, 256])
+def test_swa_decode_ignores_uninitialised_rows(ops, bs):
+    """Rows of a page past the sequence end (and recycled rows before the window start) may hold
+    arbitrary bit patterns, NaN included; they are masked and must not leak into the output."""
+    lens, wl, M, H, Hkv, D = [70, 300, 1], 100, 0, 28, 4, 128
+    kc, vc, tables, keys, vals = make_paged(lens, Hkv, D, bs, seed=3)
+    ref = None
+    gen = torch.Generator().manual_seed(4)
+    q = torch.randn(len(lens), H, D, generator=gen).bfloat16()
+    ref = oswa.swa_meta_decode_paged(q, kc, vc, tables, lens, None, None, wl, out_dtype=torch.float32)
+    nan = torch.tensor(float("nan")).bfloat16()
+    for i, L in enumerate(lens):
+        lo = max(0, L - 1 - wl)
+        nblk = (L + bs - 1) // bs
+        for p in list(range(L, nblk * bs)) + list(range(0, lo)):
+            kc[tables[i, p // bs], p % bs] = nan
+            vc[tables[i, p // bs], p % bs] = nan
+    used = set(int(x) for i, L in enumerate(lens) for x in tables[i, :(L + bs - 1) // bs])
+    for blk in range(kc.shape[0]):          # blocks no sequence owns: all NaN
+        if blk not in used:
+            kc[blk] = nan
+            vc[blk] = nan
+    out = ops.swa_meta_decode_paged(q.to(DEV), kc.to(DEV), vc.to(DEV), tables.to(DEV),
+                                    torch.tensor(lens, dtype=torch.int32, device=DEV), None, None, wl)
+    assert_close(out, ref, "swa decode with NaN garbage")

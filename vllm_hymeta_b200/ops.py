@@ -151,7 +151,8 @@ def swa_meta_decode_paged(q, k_cache, v_cache, block_tables, cache_seqlens, meta
     check(lib().hymeta_swa_meta_decode_paged(
         _ptr(q), _ptr(k_cache), _ptr(v_cache), _ptr(block_tables), _ptr(cache_seqlens),
         _ptr(meta_k), _ptr(meta_v), _ptr(out), _ptr(ws), ws.numel(),
-        B, H, Hkv, D, M, bs, max_blocks, block_tables.stride(0), int(window_left), float(scale),
+        B, H, Hkv, D, M, bs, k_cache.shape[0], max_blocks, block_tables.stride(0), int(window_left),
+        float(scale),
         q.stride(0), q.stride(1), out.stride(0), out.stride(1),
         k_cache.stride(0), k_cache.stride(1), k_cache.stride(2),
         v_cache.stride(0), v_cache.stride(1), v_cache.stride(2),
