@@ -10,9 +10,10 @@ import torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from vllm_hymeta_b200 import ops  # noqa: E402
 
-PEAK = 6524.6
+PEAK, TPEAK = 6524.6, 1401.9
 try:
-    PEAK = json.load(open(os.path.join(os.path.dirname(__file__), "..", "MEASURED_PEAKS.json")))["hbm_gbs"]
+    _pk = json.load(open(os.path.join(os.path.dirname(__file__), "..", "MEASURED_PEAKS.json")))
+    PEAK, TPEAK = _pk["hbm_gbs"], _pk["bf16_tflops_sustained"]
 except Exception:
     pass
 
@@ -86,6 +87,45 @@ def bench_kv_write(T, Hkv=4, D=128, bs=256, flush=None):
     print(f"kv_write T={T}: {t*1e6:8.1f} us  {alg/t/1e9:8.1f} GB/s ({alg/t/1e9/PEAK:.2%})")
 
 
+def bench_swa_prefill(N, T, H=28, Hkv=4, D=128, wl=4096, M=0, iters=5):
+    dev = "cuda"
+    q = torch.randn(N * T, H, D, device=dev).bfloat16()
+    k = torch.randn(N * T, Hkv, D, device=dev).bfloat16()
+    v = torch.randn(N * T, Hkv, D, device=dev).bfloat16()
+    mk = mv = None
+    if M:
+        mk = torch.randn(M, Hkv, D, device=dev).bfloat16()
+        mv = torch.randn(M, Hkv, D, device=dev).bfloat16()
+    cu = (torch.arange(N + 1, device=dev) * T).to(torch.int32)
+    out = torch.empty(N * T, H, D, device=dev, dtype=torch.bfloat16)
+    t = timeit(lambda: ops.swa_meta_prefill_varlen(q, k, v, None, mk, mv, cu, cu, T, wl, out=out),
+               iters=iters, warmup=2)
+    i = torch.arange(T, dtype=torch.float64)
+    nkeys = (M + (torch.clamp(i + 1, max=wl + 1) if wl >= 0 else i + 1)).sum().item()
+    fl = N * H * 4 * D * nkeys
+    print(f"swa_prefill N={N} T={T} H={H}/{Hkv} wl={wl} M={M}: {t*1e3:8.3f} ms  {fl/t/1e12:7.1f} TFLOP/s "
+          f"({fl/t/1e12/TPEAK:.2%} of sustained {TPEAK:.0f})  {N*T/t/1e6:.2f} Mtok/s")
+
+
+def bench_gla_prefill(N, T, H=28, Hkv=4, D=128, gdt=torch.bfloat16, iters=5):
+    dev = "cuda"
+    q = torch.randn(N * T, H, D, device=dev).bfloat16().relu()
+    k = torch.randn(N * T, Hkv, D, device=dev).bfloat16().relu()
+    v = torch.randn(N * T, Hkv, D, device=dev).bfloat16()
+    g = (torch.nn.functional.logsigmoid(torch.randn(N * T, Hkv, D, device=dev)) / 16).to(gdt)
+    state = torch.zeros(N, Hkv, D, D, device=dev, dtype=torch.bfloat16)
+    cu = (torch.arange(N + 1, device=dev) * T).to(torch.int32)
+    slots = torch.arange(N, device=dev, dtype=torch.int32)
+    init = torch.zeros(N, device=dev, dtype=torch.int32)
+    out = torch.empty(N * T, H, D, device=dev, dtype=torch.bfloat16)
+    t = timeit(lambda: ops.gla_prefill_varlen(q, k, v, g, state, cu, slots, init, max_seqlen=T, out=out),
+               iters=iters, warmup=2)
+    by = N * T * (H * 2 * D * 2 + Hkv * D * (4 + g.element_size()))
+    fl = N * T * H * (4 * D * D + 2 * 64 * 2 * D)
+    print(f"gla_prefill N={N} T={T} H={H}/{Hkv}: {t*1e3:8.3f} ms  {by/t/1e9:7.1f} GB/s ({by/t/1e9/PEAK:.2%})  "
+          f"{fl/t/1e12:6.1f} TFLOP/s ({fl/t/1e12/TPEAK:.2%})  {N*T/t/1e6:.2f} Mtok/s")
+
+
 if __name__ == "__main__":
     ap = argparse.ArgumentParser()
     ap.add_argument("--which", default="all")
@@ -102,6 +142,14 @@ if __name__ == "__main__":
         bench_swa_decode(1000, 5000, flush=flush)
         bench_swa_decode(8, 8192, flush=flush)
         bench_swa_decode(1, 8192, flush=flush)
+    if a.which in ("all", "swa_prefill"):
+        bench_swa_prefill(64, 8192)
+        bench_swa_prefill(1, 32768, H=7, Hkv=1, wl=4095, M=128)
+        bench_swa_prefill(1, 32768, H=7, Hkv=1, wl=-1, M=128)
+    if a.which in ("all", "gla_prefill"):
+        bench_gla_prefill(64, 8192)
+        bench_gla_prefill(8, 32768)
+        bench_gla_prefill(1, 32768, H=7, Hkv=1, gdt=torch.float32)
     if a.which in ("all", "kv_write"):
         bench_kv_write(64)
         bench_kv_write(524288, flush=flush)

@@ -9,7 +9,7 @@
 
 namespace hymeta {
 
-struct SelfCase { int a_mn, b_mn, N, K, tma; };
+struct SelfCase { int a_mn, b_mn, N, K, tma, a_tmem; };   // a_tmem: A staged in TMEM (tcgen05.st), K-major
 
 // A: !a_mn -> [128][K] (K contiguous), a_mn -> [K][128].  B: !b_mn -> [N][K], b_mn -> [K][N].
 __global__ void __launch_bounds__(128)
@@ -31,7 +31,7 @@ selftest_umma_kernel(const __nv_bfloat16* __restrict__ A, const __nv_bfloat16* _
     mbar_init(bar_mma, 1);
     fence_mbar_init();
   }
-  if (warp == 0) tmem_alloc<128>(smem_u32(&tmem_base_s));
+  if (warp == 0) tmem_alloc<256>(smem_u32(&tmem_base_s));
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -65,6 +65,18 @@ selftest_umma_kernel(const __nv_bfloat16* __restrict__ A, const __nv_bfloat16* _
     }
     fence_proxy_async_smem();
   }
+  if (c.a_tmem) {   // row tid of A -> lane tid, bf16 pairs in columns [128, 128 + K/2)
+    for (int c0 = 0; c0 < K / 2; c0 += 16) {
+      uint32_t w[16];
+#pragma unroll
+      for (int j = 0; j < 16; ++j) {
+        const __nv_bfloat16 lo = A[tid * K + 2 * (c0 + j)], hi = A[tid * K + 2 * (c0 + j) + 1];
+        w[j] = (uint32_t)__bfloat16_as_ushort(lo) | ((uint32_t)__bfloat16_as_ushort(hi) << 16);
+      }
+      tmem_st16(tmem_base_s + ((uint32_t)(warp * 32) << 16) + 128 + c0, w);
+    }
+    tmem_wait_st();
+  }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -76,7 +88,8 @@ selftest_umma_kernel(const __nv_bfloat16* __restrict__ A, const __nv_bfloat16* _
                             : umma_desc_sw128(sA + ks * 2048, K * 128, 1024);
       uint64_t db = !c.b_mn ? umma_desc_sw128(sB + (ks / 4) * N * 128 + (ks % 4) * 32, 16, 1024)
                             : umma_desc_sw128(sB + ks * 2048, K * 128, 1024);
-      umma_bf16(tmem, da, db, idesc, ks > 0);
+      if (c.a_tmem) umma_bf16_ts(tmem, tmem + 128 + ks * 8, db, idesc, ks > 0);
+      else umma_bf16(tmem, da, db, idesc, ks > 0);
     }
     umma_commit(bar_mma);
   }
@@ -90,7 +103,7 @@ selftest_umma_kernel(const __nv_bfloat16* __restrict__ A, const __nv_bfloat16* _
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 0) tmem_dealloc<128>(tmem);
+  if (warp == 0) tmem_dealloc<256>(tmem);
 }
 
 __global__ void selftest_ref_kernel(const __nv_bfloat16* A, const __nv_bfloat16* B, float* D, SelfCase c) {
@@ -123,6 +136,7 @@ extern "C" int hymeta_selftest_umma(float* max_err_out) {
       {0, 1, 128, 64, 0}, {0, 1, 128, 64, 1}, {0, 1, 128, 16, 0}, {0, 1, 128, 128, 1},
       {1, 0, 128, 64, 0}, {1, 1, 128, 16, 0}, {1, 1, 128, 64, 1}, {0, 0, 128, 16, 0},
       {0, 1, 64, 64, 1},
+      {0, 1, 128, 128, 1, 1}, {0, 1, 128, 32, 0, 1}, {0, 0, 64, 64, 0, 1},   // A from TMEM (P @ V)
   };
   __nv_bfloat16 *A, *B;
   float *D, *R;

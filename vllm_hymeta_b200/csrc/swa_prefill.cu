@@ -5,45 +5,58 @@
 // (fa_kernel_metatoken.py:198-285): the meta keys are simply the first key tiles of every query
 // tile's single online softmax.
 //
-// CTA = 128 query rows of one q-head (thread r <-> TMEM lane r <-> query row r), 128 threads,
-// two CTAs per SM so one CTA's softmax overlaps the other's MMAs.
-//   S[128 x 64]   = Q[128 x 128] K^T   : tcgen05.mma SS, K-major A/B (TMA, SWIZZLE_128B), fp32 in TMEM
-//   P             = exp2(S*scale - m)  : registers; bf16 P written to smem (K-major canonical layout)
-//   Ot[128 x 128] = P[128 x 64] V      : tcgen05.mma SS, V consumed MN-major exactly as TMA lands it
-//   O             = O*alpha + Ot       : registers (one row per thread, no shuffles anywhere)
-// K/V tiles (64 keys) are double-buffered; S(j+1) is issued behind PV(j) so the tensor pipe works
-// while the CTA folds Ot(j).  grid.x = q-head so the 7 heads of a GQA group run back to back and
-// share K/V tiles through L2.
+// CTA = TWO 128-row query tiles of one q-head (256 consecutive queries) against 128-key tiles,
+// warp-specialised, one CTA per SM (all 512 TMEM columns, 224 KB of smem):
+//   warp 8      TMA producer: Q0/Q1 once, then K tiles (2-stage ring) and V tiles (3-stage ring),
+//               SWIZZLE_128B boxes straight from the packed [T, Hkv, D] tensors
+//   warp 9      MMA issuer (one lane):  S_i = Q_i K^T          tcgen05.mma SS, fp32 S in TMEM
+//                                       O_i += P_i V           tcgen05.mma TS: A = bf16 P in TMEM
+//                                                              (aliases S_i), B = V MN-major as landed
+//   warps 0-3   softmax of query tile 0, warps 4-7 of tile 1 (thread = query row = TMEM lane):
+//               one tcgen05.ld of the 128 scores, masks only on boundary tiles, exp2 in the log2
+//               domain, bf16 P stored back over S with tcgen05.st.  O stays in TMEM for the whole
+//               key loop; it is rescaled in place only when a row maximum grows by more than 2^8
+//               (lazy rescale), so the common step touches neither O nor shared memory.
+// The issue order  PV0(t) S0(t+1) PV1(t) S1(t+1)  lets tile 1's softmax run under tile 0's MMAs and
+// vice versa; MMAs of one CTA complete in order, so "S_i(t) has landed" also means O_i holds every
+// PV up to t-1 and the rescale needs no extra barrier.
+// grid.x = q-head so the G heads of a GQA group run side by side and share K/V tiles through L2.
 #include "umma.cuh"
 
 namespace hymeta {
 
-constexpr int PF_BM = 128;   // query rows per CTA
-constexpr int PF_BN = 64;    // keys per tile
-constexpr int PF_SQ = 0;                       // [2][128][64] bf16
-constexpr int PF_SK = 32768;                   // [2 stages][2][64][64]
-constexpr int PF_SV = PF_SK + 32768;           // [2 stages][2][64][64]
-constexpr int PF_SP = PF_SV + 32768;           // [128][64]
-constexpr int PF_BAR = PF_SP + 16384;          // barriers + tmem ptr
-constexpr int PF_SMEM = PF_BAR + 128;
+constexpr int PF_BM = 128;    // query rows per tile (two tiles per CTA)
+constexpr int PF_BN = 128;    // keys per tile
+constexpr int PF_NKS = 2;     // K ring stages
+constexpr int PF_NVS = 3;     // V ring stages
+constexpr int PF_TILE = 32768;                          // one [128][128] bf16 tile: 2 halves x [128][64]
+constexpr int PF_SQ = 0;                                // Q0, Q1
+constexpr int PF_SK = 2 * PF_TILE;
+constexpr int PF_SV = PF_SK + PF_NKS * PF_TILE;
+constexpr int PF_BAR = PF_SV + PF_NVS * PF_TILE;        // mbarriers + tmem ptr
+constexpr int PF_SMEM = PF_BAR + 256;
+constexpr int PF_THREADS = 320;
+constexpr float PF_RESCALE_T = 8.f;                     // lazy rescale threshold (log2 domain)
 
 struct SwaPrefillParams {
   const int32_t *cu_q, *cu_k;
   __nv_bfloat16* out;
-  int N, H, Hkv, M, window_left, has_q2, n_qtiles;
+  int N, H, Hkv, M, window_left, has_q2, n_qpairs;
   float scale_log2;
   int64_t o_st, o_sh;
 };
 
-__global__ void __launch_bounds__(128, 2)
+struct QTile { int on, rows, pmin, pmax, lo, hi; };   // real key-tile range [lo, hi] (empty if hi < lo)
+
+__global__ void __launch_bounds__(PF_THREADS, 1)
 swa_prefill_kernel(const SwaPrefillParams p, const __grid_constant__ CUtensorMap tmQ,
                    const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV,
                    const __grid_constant__ CUtensorMap tmQ2, const __grid_constant__ CUtensorMap tmMK,
                    const __grid_constant__ CUtensorMap tmMV) {
   extern __shared__ __align__(1024) uint8_t smem[];
-  const int tid = threadIdx.x, warp = tid >> 5;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int h = blockIdx.x, hkv = h / (p.H / p.Hkv);
-  const int qt = p.n_qtiles - 1 - blockIdx.y;   // long tiles first
+  const int qp = p.n_qpairs - 1 - blockIdx.y;   // long pairs first
   const int n = blockIdx.z;
   const bool meta_q = n == p.N;                 // pseudo-sequence of the M meta queries
 
@@ -53,190 +66,271 @@ swa_prefill_kernel(const SwaPrefillParams p, const __grid_constant__ CUtensorMap
     q_row0 = p.cu_q[n]; Lq = p.cu_q[n + 1] - q_row0;
     k_row0 = p.cu_k[n]; Lk = p.cu_k[n + 1] - k_row0;
   }
-  if (qt * PF_BM >= Lq) return;
+  if (qp * 2 * PF_BM >= Lq) return;
+
+  // ---- geometry shared by every role ------------------------------------------------------------
+  const int shift = Lk - Lq;                                   // queries sit at the END of the keys
+  const int nm = (p.M + PF_BN - 1) / PF_BN;                    // meta key tiles come first
+  QTile qt[2];
+#pragma unroll
+  for (int i = 0; i < 2; ++i) {
+    const int row0 = qp * 2 * PF_BM + i * PF_BM;
+    QTile t;
+    t.on = row0 < Lq;
+    t.rows = t.on ? min(PF_BM, Lq - row0) : 0;
+    t.pmin = shift + row0; t.pmax = t.pmin + t.rows - 1;
+    t.lo = 0; t.hi = -1;
+    if (t.on && !meta_q && t.pmax >= 0 && Lk > 0) {
+      t.lo = p.window_left < 0 ? 0 : max(0, t.pmin - p.window_left) / PF_BN;
+      t.hi = min(t.pmax, Lk - 1) / PF_BN;
+    }
+    qt[i] = t;
+  }
+  int u_lo = 0, u_hi = -1;
+  if (qt[0].hi >= qt[0].lo) { u_lo = qt[0].lo; u_hi = qt[0].hi; }
+  if (qt[1].hi >= qt[1].lo) {
+    if (u_hi < u_lo) { u_lo = qt[1].lo; u_hi = qt[1].hi; }
+    else { u_lo = min(u_lo, qt[1].lo); u_hi = max(u_hi, qt[1].hi); }
+  }
+  const int n_steps = nm + (u_hi >= u_lo ? u_hi - u_lo + 1 : 0);
+  int last_step[2];   // last key step each query tile takes part in (-1: none)
+#pragma unroll
+  for (int i = 0; i < 2; ++i)
+    last_step[i] = !qt[i].on ? -1 : (qt[i].hi >= qt[i].lo ? nm + qt[i].hi - u_lo : nm - 1);
+  auto active = [&](int i, int t) -> bool {
+    if (!qt[i].on || t >= n_steps) return false;
+    if (t < nm) return true;
+    const int jt = u_lo + t - nm;
+    return jt >= qt[i].lo && jt <= qt[i].hi;
+  };
 
   const uint32_t sbase = smem_u32(smem);
-  const uint32_t sQ = sbase + PF_SQ, sK = sbase + PF_SK, sV = sbase + PF_SV, sP = sbase + PF_SP;
-  const uint32_t bar_q = sbase + PF_BAR, bar_kv0 = bar_q + 8, bar_s = bar_q + 24, bar_o = bar_q + 32;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + PF_BAR + 40);
-
-  // key-position geometry of this query tile (queries aligned to the END of the keys)
-  const int shift = Lk - Lq;
-  const int rows = min(PF_BM, Lq - qt * PF_BM);
-  const int pq_min = shift + qt * PF_BM, pq_max = pq_min + rows - 1;
-  const int nm = (p.M + PF_BN - 1) / PF_BN;                       // meta tiles come first
-  int kt_lo = 0, n_real = 0;
-  if (!meta_q) {
-    kt_lo = p.window_left < 0 ? 0 : max(0, pq_min - p.window_left) / PF_BN;
-    n_real = pq_max >= 0 ? pq_max / PF_BN - kt_lo + 1 : 0;
-  }
-  const int nt = nm + n_real;
+  const uint32_t sQ = sbase + PF_SQ, sK = sbase + PF_SK, sV = sbase + PF_SV;
+  const uint32_t bars = sbase + PF_BAR;
+  const uint32_t bar_q = bars, bar_kf = bars + 8, bar_ke = bar_kf + 8 * PF_NKS, bar_vf = bar_ke + 8 * PF_NKS,
+                 bar_ve = bar_vf + 8 * PF_NVS, bar_s = bar_ve + 8 * PF_NVS, bar_p = bar_s + 16, bar_o = bar_p + 16;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + PF_BAR + 200);
 
   if (tid == 0) {
     if (sbase & 1023) asm volatile("trap;");
-    mbar_init(bar_q, 1); mbar_init(bar_kv0, 1); mbar_init(bar_kv0 + 8, 1);
-    mbar_init(bar_s, 1); mbar_init(bar_o, 1);
+    mbar_init(bar_q, 1);
+    for (int s = 0; s < PF_NKS; ++s) { mbar_init(bar_kf + 8 * s, 1); mbar_init(bar_ke + 8 * s, 1); }
+    for (int s = 0; s < PF_NVS; ++s) { mbar_init(bar_vf + 8 * s, 1); mbar_init(bar_ve + 8 * s, 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(bar_s + 8 * i, 1); mbar_init(bar_p + 8 * i, 128); mbar_init(bar_o + 8 * i, 1); }
     fence_mbar_init();
-    tma_prefetch_desc(&tmQ); tma_prefetch_desc(&tmK); tma_prefetch_desc(&tmV);
   }
-  if (warp == 0) tmem_alloc<256>(smem_u32(tmem_slot));
+  if (warp == 9) tmem_alloc<512>(smem_u32(tmem_slot));
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
-  const uint32_t tS = tmem, tO = tmem + PF_BN;
-  const uint32_t lane_off = (uint32_t)(warp * 32) << 16;
+  // TMEM columns: S0 [0,128) S1 [128,256) O0 [256,384) O1 [384,512); P_i aliases S_i[0,64)
 
-  auto load_kv = [&](int j) {   // thread 0 only
-    const int st = j & 1;
-    const uint32_t bar = bar_kv0 + 8 * st, dk = sK + st * 16384, dv = sV + st * 16384;
-    mbar_expect_tx(bar, 32768);
-    if (j < nm) {
-      tma_load_3d(dk, &tmMK, bar, 0, hkv, j * PF_BN);  tma_load_3d(dk + 8192, &tmMK, bar, 64, hkv, j * PF_BN);
-      tma_load_3d(dv, &tmMV, bar, 0, hkv, j * PF_BN);  tma_load_3d(dv + 8192, &tmMV, bar, 64, hkv, j * PF_BN);
-    } else {
-      const int row = k_row0 + (kt_lo + j - nm) * PF_BN;
-      tma_load_3d(dk, &tmK, bar, 0, hkv, row);  tma_load_3d(dk + 8192, &tmK, bar, 64, hkv, row);
-      tma_load_3d(dv, &tmV, bar, 0, hkv, row);  tma_load_3d(dv + 8192, &tmV, bar, 64, hkv, row);
-    }
-  };
-  const uint32_t idesc_s = umma_idesc_bf16(PF_BM, PF_BN, 0, 0);
-  const uint32_t idesc_o = umma_idesc_bf16(PF_BM, kD, 0, 1);
-  auto issue_s = [&](int j) {   // thread 0 only: S = Q K^T
-    const uint32_t kb = sK + (j & 1) * 16384;
-#pragma unroll
-    for (int ks = 0; ks < 8; ++ks) {
-      const uint64_t da = umma_desc_sw128(sQ + (ks >> 2) * 16384 + (ks & 3) * 32, 16, 1024);
-      const uint64_t db = umma_desc_sw128(kb + (ks >> 2) * 8192 + (ks & 3) * 32, 16, 1024);
-      umma_bf16(tS, da, db, idesc_s, ks > 0);
-    }
-    umma_commit(bar_s);
-  };
-  auto issue_pv = [&](int j) {  // thread 0 only: Ot = P V
-    const uint32_t vb = sV + (j & 1) * 16384;
-#pragma unroll
-    for (int ks = 0; ks < 4; ++ks) {
-      const uint64_t da = umma_desc_sw128(sP + ks * 32, 16, 1024);
-      const uint64_t db = umma_desc_sw128(vb + ks * 2048, 8192, 1024);
-      umma_bf16(tO, da, db, idesc_o, ks > 0);
-    }
-    umma_commit(bar_o);
-  };
-
-  if (tid == 0) {
-    mbar_expect_tx(bar_q, 32768);
-    const CUtensorMap* tq = meta_q ? &tmQ2 : &tmQ;
-    tma_load_3d(sQ, tq, bar_q, 0, h, q_row0 + qt * PF_BM);
-    tma_load_3d(sQ + 16384, tq, bar_q, 64, h, q_row0 + qt * PF_BM);
-    load_kv(0);
-    if (nt > 1) load_kv(1);
-    mbar_wait(bar_q, 0);
-    mbar_wait(bar_kv0, 0);
-    tc_fence_after();
-    issue_s(0);
-  }
-
-  const int r = tid;                    // my query row
-  const int pq = pq_min + r;            // its key position
-  float o_acc[kD];
-#pragma unroll
-  for (int i = 0; i < kD; ++i) o_acc[i] = 0.f;
-  float m_run = -INFINITY, l_run = 0.f;
-
-  for (int j = 0; j < nt; ++j) {
-    mbar_wait(bar_s, j & 1);
-    tc_fence_after();
-    float s[PF_BN];
-    {
-      float t0[32], t1[32];
-      tmem_ld32(tS + lane_off, t0);
-      tmem_ld32(tS + lane_off + 32, t1);
-#pragma unroll
-      for (int i = 0; i < 32; ++i) { s[i] = t0[i]; s[32 + i] = t1[i]; }
-    }
-    // ---- mask (tile-uniform decision) + scale
-    bool need_mask;
-    int kp0;
-    if (j < nm) { kp0 = j * PF_BN; need_mask = kp0 + PF_BN > p.M; }
-    else {
-      kp0 = (kt_lo + j - nm) * PF_BN;
-      need_mask = (kp0 + PF_BN - 1 > pq_min) || (kp0 + PF_BN > Lk) ||
-                  (p.window_left >= 0 && kp0 < pq_max - p.window_left);
-    }
-    float mx = -INFINITY;
-    if (need_mask) {
-      int lo, hi;   // visible key positions for this row: [lo, hi]
-      if (j < nm) { lo = 0; hi = p.M - 1; }
-      else { hi = min(pq, Lk - 1); lo = p.window_left < 0 ? 0 : pq - p.window_left; }
-#pragma unroll
-      for (int i = 0; i < PF_BN; ++i) {
-        const int kp = kp0 + i;
-        s[i] = (kp >= lo && kp <= hi) ? s[i] * p.scale_log2 : -INFINITY;
-        mx = fmaxf(mx, s[i]);
+  if (warp == 8) {
+    // ================================================================== TMA producer
+    if (lane == 0) {
+      const CUtensorMap* tq = meta_q ? &tmQ2 : &tmQ;
+      tma_prefetch_desc(tq); tma_prefetch_desc(&tmK); tma_prefetch_desc(&tmV);
+      const int nq = qt[1].on ? 2 : 1;
+      mbar_expect_tx(bar_q, nq * PF_TILE);
+      for (int i = 0; i < nq; ++i) {
+        const int row = q_row0 + qp * 2 * PF_BM + i * PF_BM;
+        tma_load_3d(sQ + i * PF_TILE, tq, bar_q, 0, h, row);
+        tma_load_3d(sQ + i * PF_TILE + 16384, tq, bar_q, 64, h, row);
       }
-    } else {
-#pragma unroll
-      for (int i = 0; i < PF_BN; ++i) { s[i] *= p.scale_log2; mx = fmaxf(mx, s[i]); }
+      for (int t = 0; t < n_steps; ++t) {
+        const CUtensorMap *mk, *mv;
+        int row;
+        if (t < nm) { mk = &tmMK; mv = &tmMV; row = t * PF_BN; }
+        else { mk = &tmK; mv = &tmV; row = k_row0 + (u_lo + t - nm) * PF_BN; }
+        {
+          const int st = t % PF_NKS;
+          if (t >= PF_NKS) mbar_wait(bar_ke + 8 * st, ((t / PF_NKS) - 1) & 1);
+          const uint32_t bar = bar_kf + 8 * st, dst = sK + st * PF_TILE;
+          mbar_expect_tx(bar, PF_TILE);
+          tma_load_3d(dst, mk, bar, 0, hkv, row);
+          tma_load_3d(dst + 16384, mk, bar, 64, hkv, row);
+        }
+        {
+          const int st = t % PF_NVS;
+          if (t >= PF_NVS) mbar_wait(bar_ve + 8 * st, ((t / PF_NVS) - 1) & 1);
+          const uint32_t bar = bar_vf + 8 * st, dst = sV + st * PF_TILE;
+          mbar_expect_tx(bar, PF_TILE);
+          tma_load_3d(dst, mv, bar, 0, hkv, row);
+          tma_load_3d(dst + 16384, mv, bar, 64, hkv, row);
+        }
+      }
     }
-    const float m_new = fmaxf(m_run, mx);
-    const float alpha = (m_new == -INFINITY) ? 1.f : exp2f(m_run - m_new);
-    const float msafe = (m_new == -INFINITY) ? 0.f : m_new;
-    m_run = m_new;
-    float rs = 0.f;
+    __syncwarp();
+  } else if (warp == 9) {
+    // ================================================================== MMA issuer
+    if (lane == 0) {
+      const uint32_t idesc_s = umma_idesc_bf16(PF_BM, PF_BN, 0, 0);
+      const uint32_t idesc_o = umma_idesc_bf16(PF_BM, kD, 0, 1);
+      auto issue_s = [&](int i, int t) {   // S_i = Q_i K(t)^T
+        const uint32_t qb = sQ + i * PF_TILE, kb = sK + (t % PF_NKS) * PF_TILE;
 #pragma unroll
-    for (int i = 0; i < PF_BN; ++i) { s[i] = exp2f(s[i] - msafe); rs += s[i]; }
-    l_run = l_run * alpha + rs;
-    // ---- P (bf16) -> smem, K-major SWIZZLE_128B row r
+        for (int ks = 0; ks < 8; ++ks) {
+          const uint64_t da = umma_desc_sw128(qb + (ks >> 2) * 16384 + (ks & 3) * 32, 16, 1024);
+          const uint64_t db = umma_desc_sw128(kb + (ks >> 2) * 16384 + (ks & 3) * 32, 16, 1024);
+          umma_bf16(tmem + i * 128, da, db, idesc_s, ks > 0);
+        }
+        umma_commit(bar_s + 8 * i);
+      };
+      auto issue_pv = [&](int i, int t, bool acc) {   // O_i (+)= P_i V(t)
+        const uint32_t vb = sV + (t % PF_NVS) * PF_TILE;
 #pragma unroll
-    for (int c = 0; c < 8; ++c) {
-      uint4 v;
-      v.x = pack_bf16(s[8 * c + 0], s[8 * c + 1]); v.y = pack_bf16(s[8 * c + 2], s[8 * c + 3]);
-      v.z = pack_bf16(s[8 * c + 4], s[8 * c + 5]); v.w = pack_bf16(s[8 * c + 6], s[8 * c + 7]);
-      *reinterpret_cast<uint4*>(smem + PF_SP + sw128_chunk(r, c)) = v;
-    }
-    fence_proxy_async_smem();
-    tc_fence_before();
-    __syncthreads();
-    if (tid == 0) {
-      tc_fence_after();
-      issue_pv(j);
-      if (j + 1 < nt) {
-        mbar_wait(bar_kv0 + 8 * ((j + 1) & 1), ((j + 1) >> 1) & 1);
+        for (int ks = 0; ks < 8; ++ks) {
+          const uint64_t db = umma_desc_sw128(vb + ks * 2048, 16384, 1024);
+          umma_bf16_ts(tmem + 256 + i * 128, tmem + i * 128 + ks * 8, db, idesc_o, (acc || ks > 0) ? 1u : 0u);
+        }
+      };
+      int cnt[2] = {0, 0};
+      if (n_steps > 0) {
+        mbar_wait(bar_q, 0);
+        mbar_wait(bar_kf, 0);
         tc_fence_after();
-        issue_s(j + 1);
+        for (int i = 0; i < 2; ++i) if (active(i, 0)) issue_s(i, 0);
+        umma_commit(bar_ke);
+      }
+      for (int t = 0; t < n_steps; ++t) {
+        bool v_ready = false, k_ready = false;
+        for (int i = 0; i < 2; ++i) {
+          if (active(i, t)) {
+            mbar_wait(bar_p + 8 * i, cnt[i] & 1);
+            if (!v_ready) { mbar_wait(bar_vf + 8 * (t % PF_NVS), (t / PF_NVS) & 1); v_ready = true; }
+            tc_fence_after();
+            issue_pv(i, t, cnt[i] > 0);
+            ++cnt[i];
+            if (t == last_step[i]) umma_commit(bar_o + 8 * i);   // last key tile of this query tile
+          }
+          if (active(i, t + 1)) {
+            if (!k_ready) { mbar_wait(bar_kf + 8 * ((t + 1) % PF_NKS), ((t + 1) / PF_NKS) & 1); k_ready = true; }
+            tc_fence_after();
+            issue_s(i, t + 1);
+          }
+        }
+        umma_commit(bar_ve + 8 * (t % PF_NVS));
+        if (t + 1 < n_steps) umma_commit(bar_ke + 8 * ((t + 1) % PF_NKS));
       }
     }
-    mbar_wait(bar_o, j & 1);
-    tc_fence_after();
-    if (tid == 0 && j + 2 < nt) load_kv(j + 2);   // stage j&1 is free: S(j) and PV(j) are complete
+    __syncwarp();
+  } else {
+    // ================================================================== softmax warps
+    const int i = warp >> 2;                     // query tile
+    const int r = (warp & 3) * 32 + lane;        // row inside the tile == TMEM lane
+    const QTile T = qt[i];
+    const uint32_t lane_off = (uint32_t)((warp & 3) * 32) << 16;
+    const uint32_t tS = tmem + i * 128 + lane_off, tO = tmem + 256 + i * 128 + lane_off;
+    const int pq = T.pmin + r;                   // key position of my query
+    float m_ref = -INFINITY, l_run = 0.f;        // running reference max (scaled, log2 domain) / sum
+    int cnt = 0;
+    if (T.on) {
+      for (int t = 0; t < n_steps; ++t) {
+        if (!active(i, t)) continue;
+        mbar_wait(bar_s + 8 * i, cnt & 1);
+        tc_fence_after();
+        uint32_t sr[128];
+        tmem_ld32_nowait(tS + 0, *reinterpret_cast<uint32_t(*)[32]>(&sr[0]));
+        tmem_ld32_nowait(tS + 32, *reinterpret_cast<uint32_t(*)[32]>(&sr[32]));
+        tmem_ld32_nowait(tS + 64, *reinterpret_cast<uint32_t(*)[32]>(&sr[64]));
+        tmem_ld32_nowait(tS + 96, *reinterpret_cast<uint32_t(*)[32]>(&sr[96]));
+        tmem_wait_ld();
+        // ---- mask (tile-uniform decision)
+        bool need_mask;
+        int kp0, lo, hi;   // visible key positions of this row: [lo, hi]
+        if (t < nm) { kp0 = t * PF_BN; need_mask = kp0 + PF_BN > p.M; lo = 0; hi = p.M - 1; }
+        else {
+          kp0 = (u_lo + t - nm) * PF_BN;
+          need_mask = (kp0 + PF_BN - 1 > T.pmin) || (kp0 + PF_BN > Lk) ||
+                      (p.window_left >= 0 && kp0 < T.pmax - p.window_left);
+          hi = min(pq, Lk - 1); lo = p.window_left < 0 ? 0 : pq - p.window_left;
+        }
+        if (need_mask) {
 #pragma unroll
-    for (int c = 0; c < 4; ++c) {
-      float t[32];
-      tmem_ld32(tO + lane_off + 32 * c, t);
+          for (int c = 0; c < 128; ++c) {
+            const int kp = kp0 + c;
+            if (kp < lo || kp > hi) sr[c] = 0xff800000u;   // -inf
+          }
+        }
+        float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
 #pragma unroll
-      for (int i = 0; i < 32; ++i) o_acc[32 * c + i] = fmaf(o_acc[32 * c + i], alpha, t[i]);
-    }
-    tc_fence_before();   // orders these TMEM reads before the next iteration's barrier / MMAs
-  }
-
-  // ---- epilogue: normalise, bf16, one 256-byte row per thread
-  if (r < rows) {
-    const float inv = l_run > 0.f ? 1.f / l_run : 0.f;
-    const int64_t orow = (meta_q ? 0 : (int64_t)(p.has_q2 ? p.M : 0) + q_row0) + qt * PF_BM + r;
-    __nv_bfloat16* dst = p.out + orow * p.o_st + (int64_t)h * p.o_sh;
+        for (int c = 0; c < 128; c += 4) {
+          mx0 = fmaxf(mx0, __uint_as_float(sr[c])); mx1 = fmaxf(mx1, __uint_as_float(sr[c + 1]));
+          mx2 = fmaxf(mx2, __uint_as_float(sr[c + 2])); mx3 = fmaxf(mx3, __uint_as_float(sr[c + 3]));
+        }
+        const float mx = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3)) * p.scale_log2;
+        // ---- lazy rescale of O (in TMEM) when the row maximum jumps
+        const bool grow = mx > m_ref + PF_RESCALE_T || (m_ref == -INFINITY && mx > -INFINITY);
+        if (__any_sync(0xffffffffu, grow)) {
+          float alpha = 1.f;
+          if (grow) {
+            alpha = (m_ref == -INFINITY) ? 1.f : exp2f(m_ref - mx);
+            m_ref = mx;
+            l_run *= alpha;
+          }
+          if (cnt > 0) {   // O_i holds PV(0..cnt-1): all complete, since S_i(t) completed after them
 #pragma unroll
-    for (int c = 0; c < 16; ++c) {
-      uint4 v;
-      v.x = pack_bf16(o_acc[8 * c + 0] * inv, o_acc[8 * c + 1] * inv);
-      v.y = pack_bf16(o_acc[8 * c + 2] * inv, o_acc[8 * c + 3] * inv);
-      v.z = pack_bf16(o_acc[8 * c + 4] * inv, o_acc[8 * c + 5] * inv);
-      v.w = pack_bf16(o_acc[8 * c + 6] * inv, o_acc[8 * c + 7] * inv);
-      stg_v4(dst + 8 * c, v);
+            for (int c = 0; c < 4; ++c) {
+              uint32_t o[32];
+              tmem_ld32_nowait(tO + 32 * c, o);
+              tmem_wait_ld();
+#pragma unroll
+              for (int j = 0; j < 32; ++j) o[j] = __float_as_uint(__uint_as_float(o[j]) * alpha);
+              tmem_st32(tO + 32 * c, o);
+            }
+          }
+        }
+        const float msub = (m_ref == -INFINITY) ? 0.f : m_ref;
+        float rs0 = 0.f, rs1 = 0.f, rs2 = 0.f, rs3 = 0.f;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          uint32_t w[16];
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            const float a = exp2f(fmaf(__uint_as_float(sr[32 * c + 2 * j]), p.scale_log2, -msub));
+            const float b = exp2f(fmaf(__uint_as_float(sr[32 * c + 2 * j + 1]), p.scale_log2, -msub));
+            if (j & 1) { rs2 += a; rs3 += b; } else { rs0 += a; rs1 += b; }
+            w[j] = pack_bf16(a, b);
+          }
+          tmem_st16(tS + 16 * c, w);
+        }
+        l_run += (rs0 + rs1) + (rs2 + rs3);
+        tmem_wait_st();
+        tc_fence_before();
+        mbar_arrive(bar_p + 8 * i);
+        ++cnt;
+      }
+      // ---- epilogue: normalise, bf16, one 256-byte row per thread
+      if (cnt > 0) { mbar_wait(bar_o + 8 * i, 0); tc_fence_after(); }
+      const float inv = l_run > 0.f ? 1.f / l_run : 0.f;
+      const int64_t orow = (meta_q ? 0 : (int64_t)(p.has_q2 ? p.M : 0) + q_row0) + qp * 2 * PF_BM + i * PF_BM + r;
+      __nv_bfloat16* dst = p.out + orow * p.o_st + (int64_t)h * p.o_sh;
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        uint32_t o[32];
+        if (cnt > 0) { tmem_ld32_nowait(tO + 32 * c, o); tmem_wait_ld(); }
+        else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) o[j] = 0u;
+        }
+        if (r < T.rows) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            uint4 v;
+            v.x = pack_bf16(__uint_as_float(o[8 * j + 0]) * inv, __uint_as_float(o[8 * j + 1]) * inv);
+            v.y = pack_bf16(__uint_as_float(o[8 * j + 2]) * inv, __uint_as_float(o[8 * j + 3]) * inv);
+            v.z = pack_bf16(__uint_as_float(o[8 * j + 4]) * inv, __uint_as_float(o[8 * j + 5]) * inv);
+            v.w = pack_bf16(__uint_as_float(o[8 * j + 6]) * inv, __uint_as_float(o[8 * j + 7]) * inv);
+            stg_v4(dst + 32 * c + 8 * j, v);
+          }
+        }
+      }
     }
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 0) tmem_dealloc<256>(tmem);
+  if (warp == 9) tmem_dealloc<512>(tmem);
 }
 
 }  // namespace hymeta
@@ -293,7 +387,7 @@ extern "C" int hymeta_swa_meta_prefill_varlen(
   int msq = real ? max_seqlen_q : 0;
   if (q2 && M > msq) msq = M;
   if (msq <= 0) msq = real ? Tq : M;
-  p.n_qtiles = (msq + PF_BM - 1) / PF_BM;
+  p.n_qpairs = (msq + 2 * PF_BM - 1) / (2 * PF_BM);
   p.scale_log2 = scale * 1.4426950408889634f;
   p.o_st = o_st; p.o_sh = o_sh;
 
@@ -302,8 +396,8 @@ extern "C" int hymeta_swa_meta_prefill_varlen(
     cudaFuncSetAttribute(swa_prefill_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PF_SMEM);
     attr_set = true;
   }
-  dim3 grid(H, p.n_qtiles, p.N + (q2 ? 1 : 0));
-  swa_prefill_kernel<<<grid, 128, PF_SMEM, (cudaStream_t)stream>>>(p, tmQ, tmK, tmV, tmQ2, tmMK, tmMV);
+  dim3 grid(H, p.n_qpairs, p.N + (q2 ? 1 : 0));
+  swa_prefill_kernel<<<grid, PF_THREADS, PF_SMEM, (cudaStream_t)stream>>>(p, tmQ, tmK, tmV, tmQ2, tmMK, tmMV);
   count_launch();
   return check_launch();
 }
