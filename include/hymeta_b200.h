@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define HYMETA_ABI_VERSION 1
+#define HYMETA_ABI_VERSION 2
 
 typedef enum {
   HYMETA_OK = 0,
@@ -53,16 +53,18 @@ int64_t hymeta_launch_count(void);
  *
  * One recurrent step for B requests, state updated IN PLACE:
  *     S <- bf16(k (x) v) + exp(g)[:,None] * S ;  o = (q*scale)^T S   (fp32 math, bf16 stores)
- * q,o: [B, H, D].  k,v,g: [B, Hk, D].  state: [slots, Hs, D, D] (row = d_k, col = d_v).
+ * q,o: [B, H, D].  k,g: [B, Hk, D].  v: [B, Hv, D].  state: [slots, Hs, D, D] (row = d_k, col = d_v).
  * Hs is the number of states per request: Hs == H reproduces the reference layout
  * (one state per q-head, k/v/g already repeat_kv'ed or not), Hs == Hkv stores one state
  * per kv-head (the 7 q-heads of a GQA group share a bit-identical state -- SURVEY F7).
- * Requires H % Hs == 0 and Hs % Hk == 0.  slot_idx[b] == -1 skips the request
+ * Hk and Hv may differ: with the 70B per-q-head lower bound k and g carry H heads while v stays
+ * un-repeated (Hv = Hkv).  Requires H % Hs == 0, Hs % Hk == 0, Hs % Hv == 0: state-head s uses
+ * k/g head s / (Hs/Hk) and v head s / (Hs/Hv).  slot_idx[b] == -1 skips the request
  * (my_fused_recurrent.py:31-35); its output row is written as zeros.
  * ---------------------------------------------------------------------------------------------- */
 int hymeta_gla_decode(const void* q, const void* k, const void* v, const void* g, void* o,
                       void* state, const int32_t* slot_idx,
-                      int B, int H, int Hk, int Hs, int D,
+                      int B, int H, int Hk, int Hv, int Hs, int D,
                       int64_t q_sb, int64_t q_sh, int64_t k_sb, int64_t k_sh,
                       int64_t v_sb, int64_t v_sh, int64_t g_sb, int64_t g_sh,
                       int64_t o_sb, int64_t o_sh, int64_t st_ss, int64_t st_sh,
@@ -73,7 +75,8 @@ int hymeta_gla_decode(const void* q, const void* k, const void* v, const void* g
  *     (vllm_hymeta/models/modeling_hymeta.py:441-549 incl. the meta pass :447-467;
  *      vllm_hymeta/model_for_7B/gla_attention.py:179-221).
  *
- * q,o: [T, H, D].  k,v,g: [T, Hk, D].  Sequence n covers tokens [cu_seqlens[n], cu_seqlens[n+1]).
+ * q,o: [T, H, D].  k,g: [T, Hk, D].  v: [T, Hv, D] (head mapping as in hymeta_gla_decode).
+ * Sequence n covers tokens [cu_seqlens[n], cu_seqlens[n+1]).
  * init_mode[n]: 0 = zero state, 1 = state[slot_idx[n]], 2 = meta_state ([Hs, D, D], may be null
  * if unused).  If write_state != 0 and slot_idx[n] >= 0 the final state is stored (bf16) to
  * state[slot_idx[n]].  No host synchronisation (replaces the isnan()/context_len host syncs,
@@ -83,12 +86,39 @@ int hymeta_gla_prefill_varlen(const void* q, const void* k, const void* v, const
                               void* state, const void* meta_state,
                               const int32_t* cu_seqlens, const int32_t* slot_idx,
                               const int32_t* init_mode,
-                              int N, int T, int H, int Hk, int Hs, int D,
+                              int N, int T, int H, int Hk, int Hv, int Hs, int D,
                               int64_t q_st, int64_t q_sh, int64_t k_st, int64_t k_sh,
                               int64_t v_st, int64_t v_sh, int64_t g_st, int64_t g_sh,
                               int64_t o_st, int64_t o_sh, int64_t st_ss, int64_t st_sh,
                               int64_t meta_sh, int g_is_fp32, float scale, int write_state,
                               int max_seqlen, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * a4  GLA feature map + gate pre-processing -- replaces the eager torch elementwise chain between
+ *     qkv_proj and the GLA kernels:
+ *       70B  vllm_hymeta/models/modeling_hymeta.py:598-629 (relu(q); sigmoid(float(k)); clamp or
+ *            lower bound; g = log(.) in fp32; k -> bf16), HF twin hf_model/linear_attention.py:143-157
+ *       7B   vllm_hymeta/model_for_7B/gla_attention.py:251-262 (relu(q); relu(k);
+ *            g = logsigmoid(gk) / gate_logit_normalizer in bf16)
+ * q_in: [T, H, D], k_in (and gk_in): [T, Hk, D] -- strided views of the projection output are fine
+ * (strides in elements).  q_out may alias q_in, k_out may alias k_in when Ho == Hk.
+ * 70B: lower_bound == null (or the first layer of a group, modeling_hymeta.py:616) -> k_out, g_out
+ * have Ho == Hk heads.  lower_bound != null: fp32 [Ho, D], the rank-local slice of the reference's
+ * per-q-head row (:620-625); Ho == H reproduces the reference (each q-head its own gate, the raw
+ * k-head is broadcast over its GQA group in-kernel, no repeat_kv copy); Ho must be a multiple of Hk.
+ * g_out: fp32 [T, Ho, D] (70B) / bf16 [T, Hk, D] (7B).
+ * ---------------------------------------------------------------------------------------------- */
+int hymeta_gla_gate_70b(const void* q_in, const void* k_in, void* q_out, void* k_out, float* g_out,
+                        const float* lower_bound, int T, int H, int Hk, int Ho, int D,
+                        int64_t qi_st, int64_t qi_sh, int64_t ki_st, int64_t ki_sh,
+                        int64_t qo_st, int64_t qo_sh, int64_t ko_st, int64_t ko_sh,
+                        int64_t go_st, int64_t go_sh, float clamp_max, void* stream);
+int hymeta_gla_gate_7b(const void* q_in, const void* k_in, const void* gk_in, void* q_out,
+                       void* k_out, void* g_out, int T, int H, int Hk, int D,
+                       int64_t qi_st, int64_t qi_sh, int64_t ki_st, int64_t ki_sh,
+                       int64_t gi_st, int64_t gi_sh, int64_t qo_st, int64_t qo_sh,
+                       int64_t ko_st, int64_t ko_sh, int64_t go_st, int64_t go_sh,
+                       float normalizer, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * a9  Paged-KV write -- replaces torch.ops._C_cache_ops.reshape_and_cache_flash

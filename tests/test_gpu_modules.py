@@ -1,0 +1,263 @@
+"""-m gpu parity at the MODULE boundary: gate pre-processing kernels, the GLA cores
+(70B ``HLinearAttention`` / 7B ``GatedLinearAttention``) on mixed [meta | prefill | decode]
+batches with slot states, and ``FlashAttention`` -> ``MetaAttentionImpl.forward`` over the paged
+cache -- each against the CPU oracle composed the way the reference composes its torch path."""
+from types import SimpleNamespace
+
+import pytest
+import torch
+
+from gpu_util import DEV, assert_close
+from oracle import gla as ogla
+from oracle import swa as oswa
+
+pytestmark = pytest.mark.gpu
+D = 128
+
+
+@pytest.fixture(scope="module")
+def ops():
+    import __graft_entry__ as ge
+    ge.build()
+    from vllm_hymeta_b200 import ops as o
+    return o
+
+
+def _qkv(T, H, Hkv, seed):
+    gen = torch.Generator().manual_seed(seed)
+    return torch.randn(T, (H + 2 * Hkv) * D, generator=gen).bfloat16()
+
+
+# ------------------------------------------------------------------------------------- a4
+@pytest.mark.parametrize("T", [1, 37, 1000])
+def test_gate_70b_kernel(ops, T):
+    H, Hkv = 14, 2
+    qkv = _qkv(T, H, Hkv, 3)
+    q = qkv[:, :H * D].view(T, H, D)
+    k = qkv[:, H * D:(H + Hkv) * D].view(T, Hkv, D)
+    v = qkv[:, (H + Hkv) * D:].view(T, Hkv, D)
+    dq = qkv.to(DEV)
+    dqv = dq[:, :H * D].view(T, H, D)
+    dkv = dq[:, H * D:(H + Hkv) * D].view(T, Hkv, D)
+    # no lower bound: per kv-head outputs
+    rq, rk, rg = ogla.gate_70b(q, k, v)
+    oq, ok, og = ops.gla_gate_70b(dqv, dkv)
+    assert torch.equal(oq.cpu(), rq) and og.dtype == torch.float32 and ok.shape == (T, Hkv, D)
+    assert (ok.float().cpu() - rk.float()).abs().max() <= 2 ** -8      # 1 bf16 ulp at k' <= 0.95
+    assert torch.allclose(og.cpu(), rg, atol=2e-6, rtol=2e-6)
+    # lower bound (per q-head, rank-local slice): k', g per q-head, raw k broadcast in-kernel
+    gen = torch.Generator().manual_seed(5)
+    lb_full = torch.rand(2 * H * D, generator=gen) * 0.5               # 2 ranks' worth of heads
+    rq, rk, rg = ogla.gate_70b(q, k.repeat_interleave(H // Hkv, 1), v, lower_bound=lb_full,
+                               layer_idx=3, num_heads=2 * H, head_start=H)
+    lb_local = lb_full.view(2 * H, D)[H:].contiguous().to(DEV)
+    oq, ok, og = ops.gla_gate_70b(dqv, dkv, lb_local)
+    assert ok.shape == (T, H, D) and og.shape == (T, H, D)
+    assert (ok.float().cpu() - rk.float()).abs().max() <= 2 ** -8
+    assert torch.allclose(og.cpu(), rg, atol=2e-6, rtol=2e-6)
+
+
+@pytest.mark.parametrize("T", [1, 37, 1000])
+def test_gate_7b_kernel(ops, T):
+    H, Hkv = 28, 4
+    qkv = _qkv(T, H, Hkv, 7)
+    gk = torch.randn(T, Hkv * D, generator=torch.Generator().manual_seed(8)).bfloat16() * 3
+    q = qkv[:, :H * D].view(T, H, D)
+    k = qkv[:, H * D:(H + Hkv) * D].view(T, Hkv, D)
+    rq, rk, rg = ogla.gate_7b(q, k, gk.view(T, Hkv, D))
+    dq = qkv.to(DEV)
+    oq, ok, og = ops.gla_gate_7b(dq[:, :H * D].view(T, H, D), dq[:, H * D:(H + Hkv) * D].view(T, Hkv, D),
+                                 gk.to(DEV).view(T, Hkv, D))
+    assert torch.equal(oq.cpu(), rq) and torch.equal(ok.cpu(), rk)
+    assert og.dtype == torch.bfloat16
+    # bf16 logsigmoid then /16: allow one bf16 ulp where the fp32 value sits on a rounding boundary
+    d = (og.float().cpu() - rg.float()).abs()
+    assert (d <= rg.float().abs() * 2 ** -7 + 1e-9).all()
+    assert (d == 0).float().mean() > 0.99
+
+
+# ------------------------------------------------------------------------------------- a3 + a2 (70B core)
+def _md(num_prefills, prefill_lens, num_decodes, ctx):
+    qsl = [0]
+    for L in prefill_lens:
+        qsl.append(qsl[-1] + L)
+    for _ in range(num_decodes):
+        qsl.append(qsl[-1] + 1)
+    return SimpleNamespace(
+        num_prefills=num_prefills, num_prefill_tokens=sum(prefill_lens), num_decode_tokens=num_decodes,
+        query_start_loc=torch.tensor(qsl, dtype=torch.int32, device=DEV),
+        context_lens_tensor=torch.tensor(ctx, dtype=torch.int32, device=DEV),
+        max_query_len=max(prefill_lens + [1]))
+
+
+@pytest.mark.parametrize("use_lb", [False, True])
+def test_hlinear_attention_mixed_batch_with_meta_warmup(ops, use_lb):
+    from vllm_hymeta_b200.models.hymeta_cache import HymetaCacheParams
+    from vllm_hymeta_b200.models.linear_attention import HLinearAttention
+    Htot, Hkvtot, tp, rank, M = 28, 4, 2, 1, 128
+    H, Hkv = Htot // tp, Hkvtot // tp
+    lens, ctx, n_dec = [70, 33], [0, 48], 3
+    T = M + sum(lens) + n_dec
+    qkv = _qkv(T, H, Hkv, 11)
+    Hs = H if use_lb else Hkv
+    gen = torch.Generator().manual_seed(12)
+    nslots = 8
+    state = (torch.randn(nslots, Hs, D, D, generator=gen) * 0.2).bfloat16()
+    slots = [5, 2, 7, 0, 3]                       # [prefill0, prefill1, dec0, dec1, dec2]
+    lb_full = torch.rand(Htot * D, generator=gen) * 0.5 if use_lb else None
+    layer_idx = 3
+
+    # ---- oracle, composed like the reference (modeling_hymeta.py:441-659)
+    q = qkv[:, :H * D].view(T, H, D)
+    k = qkv[:, H * D:(H + Hkv) * D].view(T, Hkv, D)
+    v = qkv[:, (H + Hkv) * D:].view(T, Hkv, D)
+    if use_lb:
+        rq, rk, rg = ogla.gate_70b(q, k.repeat_interleave(H // Hkv, 1), v, lower_bound=lb_full,
+                                   layer_idx=layer_idx, num_heads=Htot, head_start=rank * H)
+        rv = v.repeat_interleave(H // Hkv, 1)
+    else:
+        rq, rk, rg = ogla.gate_70b(q, k, v)
+        rv = v
+    ref_state = state.clone()
+    o_meta, S_meta = ogla.gla_recurrent(rq[:M], rk[:M], rv[:M], rg[:M])
+    S_meta = S_meta[:: S_meta.shape[0] // Hs].bfloat16()               # meta_cache.copy_(state)
+    cu = [0, lens[0], lens[0] + lens[1]]
+    modes = [ogla.INIT_META if c == 0 else ogla.INIT_SLOT for c in ctx]
+    sl = slice(M, M + sum(lens))
+    o_pf = ogla.gla_prefill_varlen(rq[sl], rk[sl], rv[sl], rg[sl], ref_state, cu, slots[:2], modes,
+                                   S_meta, out_dtype=torch.float32)
+    ds = slice(M + sum(lens), T)
+    o_dec = ogla.gla_decode_step(rq[ds], rk[ds], rv[ds], rg[ds], ref_state,
+                                 torch.tensor(slots[2:])).float()
+    ref = torch.cat([o_meta, o_pf, o_dec]).reshape(T, H * D)
+
+    # ---- module on the kernels
+    core = HLinearAttention(hidden_size=Htot * D, num_heads=Htot, num_key_value_heads=Hkvtot,
+                            num_meta_tokens=M, layer_idx=layer_idx, tp_size=tp, tp_rank=rank)
+    d_state = state.to(DEV)
+    meta_lin = torch.zeros(Hs, D, D, dtype=torch.bfloat16, device=DEV)
+    params = HymetaCacheParams(d_state, meta_lin, torch.empty(0, device=DEV),
+                               torch.tensor(slots, dtype=torch.int32, device=DEV))
+    md = _md(2, lens, n_dec, ctx + [0] * n_dec)
+    out = core.forward(qkv.to(DEV), params, md, has_meta_cache=False,
+                       lower_bound=lb_full.to(DEV) if use_lb else None)
+    torch.cuda.synchronize()
+    assert out.shape == (T, H * D)
+    assert_close(out, ref, "HLinearAttention mixed batch")
+    assert_close(meta_lin, S_meta, "meta_linear_cache")
+    assert_close(d_state, ref_state, "slot states")
+    for s in (1, 4, 6):
+        assert torch.equal(d_state[s].cpu(), state[s])
+
+    # ---- steady state: meta cache present, decode only
+    qkv2 = _qkv(n_dec, H, Hkv, 13)
+    q2 = qkv2[:, :H * D].view(n_dec, H, D)
+    k2 = qkv2[:, H * D:(H + Hkv) * D].view(n_dec, Hkv, D)
+    v2 = qkv2[:, (H + Hkv) * D:].view(n_dec, Hkv, D)
+    if use_lb:
+        rq, rk, rg = ogla.gate_70b(q2, k2.repeat_interleave(H // Hkv, 1), v2, lower_bound=lb_full,
+                                   layer_idx=layer_idx, num_heads=Htot, head_start=rank * H)
+        rv = v2.repeat_interleave(H // Hkv, 1)
+    else:
+        rq, rk, rg = ogla.gate_70b(q2, k2, v2)
+        rv = v2
+    ref2 = ogla.gla_decode_step(rq, rk, rv, rg, ref_state, torch.tensor(slots[2:]))
+    params.state_indices_tensor = torch.tensor(slots[2:], dtype=torch.int32, device=DEV)
+    out2 = core.forward(qkv2.to(DEV), params, _md(0, [], n_dec, [0] * n_dec), has_meta_cache=True,
+                        lower_bound=lb_full.to(DEV) if use_lb else None)
+    torch.cuda.synchronize()
+    assert_close(out2, ref2.reshape(n_dec, H * D), "HLinearAttention decode only")
+    assert_close(d_state, ref_state, "slot states after decode")
+
+
+def test_gated_linear_attention_7b_mixed_batch(ops):
+    from vllm_hymeta_b200.model_for_7B.gla_attention import GatedLinearAttention
+    from vllm_hymeta_b200.model_for_7B.gla_cache import GLACacheParams
+    H, Hkv = 28, 4
+    lens, n_dec = [45, 130], 2
+    T = sum(lens) + n_dec
+    qkv = _qkv(T, H, Hkv, 21)
+    gen = torch.Generator().manual_seed(22)
+    gk = (torch.randn(T, Hkv * D, generator=gen) * 2).bfloat16()
+    w = (1 + 0.1 * torch.randn(D, generator=gen)).bfloat16()
+    state = (torch.randn(6, Hkv, D, D, generator=gen) * 0.2).bfloat16()
+    slots = [4, 1, 0, 5]
+    q = qkv[:, :H * D].view(T, H, D)
+    k = qkv[:, H * D:(H + Hkv) * D].view(T, Hkv, D)
+    v = qkv[:, (H + Hkv) * D:].view(T, Hkv, D)
+    rq, rk, rg = ogla.gate_7b(q, k, gk.view(T, Hkv, D))
+    ref_state = state.clone()
+    n_pf = sum(lens)
+    o_pf = ogla.gla_prefill_varlen(rq[:n_pf], rk[:n_pf], v[:n_pf], rg[:n_pf], ref_state,
+                                   [0, lens[0], n_pf], slots[:2], [ogla.INIT_SLOT] * 2)
+    o_dec = ogla.gla_decode_step(rq[n_pf:], rk[n_pf:], v[n_pf:], rg[n_pf:], ref_state,
+                                 torch.tensor(slots[2:]))
+    ref = ogla.rms_norm_head(torch.cat([o_pf, o_dec]), w, 1e-6).reshape(T, H * D)
+
+    core = GatedLinearAttention(H * D, H, Hkv, norm_eps=1e-6, g_norm_weight=w.to(DEV))
+    d_state = state.to(DEV)
+    params = GLACacheParams(d_state, torch.tensor(slots, dtype=torch.int32, device=DEV))
+    out = core.forward(qkv.to(DEV), gk.to(DEV), params, _md(2, lens, n_dec, [0] * 4))
+    torch.cuda.synchronize()
+    # the norm divides by the row rms, so compare with a slightly wider max-abs band
+    assert_close(out, ref, "GatedLinearAttention mixed batch", maxabs_frac=2 ** -6, rel_rms=8e-3)
+    assert_close(d_state, ref_state, "7B slot states")
+
+
+# ------------------------------------------------------------------------------------- a7-a10 (backend)
+def test_flash_attention_backend_warmup_then_decode(ops):
+    from vllm_hymeta_b200.attention.meta_attention import MetaAttentionMetadataBuilder, SeqData
+    from vllm_hymeta_b200.models.attention import FlashAttention
+    from vllm_hymeta_b200.models.hymeta_cache import HymetaCacheParams
+    H, Hkv, M, bs, W = 14, 2, 128, 16, 64
+    lens = [150, 40]
+    nb = 40
+    gen = torch.Generator().manual_seed(31)
+    T = M + sum(lens)
+    q = torch.randn(T, H * D, generator=gen).bfloat16()
+    k = torch.randn(T, Hkv * D, generator=gen).bfloat16()
+    v = torch.randn(T, Hkv * D, generator=gen).bfloat16()
+    perm = torch.randperm(nb, generator=gen).tolist()
+    tables = [perm[:11], perm[11:15]]             # room for decode growth
+    kv_cache = torch.randn(2, nb, bs, Hkv, D, generator=gen).bfloat16()      # garbage everywhere
+    layer = FlashAttention(H, Hkv, D, num_meta_tokens=M, sliding_window=W)
+    d_cache = kv_cache.to(DEV)
+    layer.attn.bind_kv_cache(d_cache)
+    meta_fa = torch.zeros(2, M, Hkv, D, dtype=torch.bfloat16, device=DEV)
+    params = HymetaCacheParams(torch.empty(0), torch.empty(0), meta_fa, torch.empty(0))
+
+    # ---- pass 1: [meta | two prompts], nothing cached yet
+    b = MetaAttentionMetadataBuilder(block_size=bs, sliding_window=None, device=DEV)
+    for L, bt in zip(lens, tables):
+        b.add(SeqData(True, L, L, 0, bt))
+    md = b.build()
+    out = layer.forward(q.to(DEV), k.to(DEV), v.to(DEV), params, md, has_meta_cache=False)
+    torch.cuda.synchronize()
+    q3, k3, v3 = q.view(T, H, D), k.view(T, Hkv, D), v.view(T, Hkv, D)
+    ref = oswa.swa_meta_prefill_varlen(q3[M:], k3[M:], v3[M:], q3[:M], k3[:M], v3[:M],
+                                       [0, lens[0], sum(lens)], [0, lens[0], sum(lens)], W - 1,
+                                       out_dtype=torch.float32)
+    assert_close(out.view(T, H, D), ref, "FlashAttention warm-up pass (meta rows first)")
+    assert torch.equal(meta_fa[0].cpu(), k3[:M]) and torch.equal(meta_fa[1].cpu(), v3[:M])
+    ref_cache = kv_cache.clone()
+    oswa.kv_write_paged(k3[M:], v3[M:], ref_cache[0], ref_cache[1], md.slot_mapping.cpu().tolist())
+    assert torch.equal(d_cache.cpu(), ref_cache), "paged KV write must be bit-exact"
+
+    # ---- pass 2: one decode token per request, meta caches warm
+    qd = torch.randn(2, H * D, generator=gen).bfloat16()
+    kd = torch.randn(2, Hkv * D, generator=gen).bfloat16()
+    vd = torch.randn(2, Hkv * D, generator=gen).bfloat16()
+    b = MetaAttentionMetadataBuilder(block_size=bs, sliding_window=None, device=DEV)
+    for L, bt in zip(lens, tables):
+        b.add(SeqData(False, L + 1, 1, L, bt))
+    md2 = b.build()
+    out2 = layer.forward(qd.to(DEV), kd.to(DEV), vd.to(DEV), params, md2, has_meta_cache=True)
+    torch.cuda.synchronize()
+    oswa.kv_write_paged(kd.view(2, Hkv, D), vd.view(2, Hkv, D), ref_cache[0], ref_cache[1],
+                        md2.slot_mapping.cpu().tolist())
+    assert torch.equal(d_cache.cpu(), ref_cache)
+    bt_rows = md2.block_tables.cpu().tolist()
+    ref2 = oswa.swa_meta_decode_paged(qd.view(2, H, D), ref_cache[0], ref_cache[1], bt_rows,
+                                      [L + 1 for L in lens], k3[:M], v3[:M], W - 1,
+                                      out_dtype=torch.float32)
+    assert_close(out2.view(2, H, D), ref2, "FlashAttention decode pass")

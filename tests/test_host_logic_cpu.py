@@ -1,0 +1,154 @@
+"""Host-side mirror of the reference interface, on CPU: slot allocator (vLLM ConstantSizeCache
+behaviour the reference cache managers inherit), cache managers, metadata builder (bit-exact
+slot mapping / block tables), backend surface and error behaviour, plugin entry points."""
+import pytest
+import torch
+
+from vllm_hymeta_b200.attention.meta_attention import (MetaAttentionBackend, MetaAttentionImpl,
+                                                       MetaAttentionMetadataBuilder, SeqData)
+from vllm_hymeta_b200.model_for_7B.gla_cache import GLACacheManager
+from vllm_hymeta_b200.models.hymeta_cache import HymetaCacheManager, HymetaCacheParams
+from vllm_hymeta_b200.slot_cache import PAD_SLOT_ID, SlotAllocator
+
+
+def test_slot_allocator_lifecycle():
+    a = SlotAllocator(4)
+    copies = []
+    cp = lambda s, d: copies.append((s, d))
+    s0 = a.prepare({"r0": [0], "r1": [1]}, [], cp)
+    assert len(set(s0)) == 2 and all(0 <= s < 4 for s in s0)
+    # same requests keep their slots; a sibling sequence forks the state of its request
+    s1 = a.prepare({"r0": [0, 7], "r1": [1]}, [], cp)
+    assert s1[0] == s0[0] and s1[2] == s0[1] and s1[1] not in s0
+    assert copies == [(s0[0], s1[1])]
+    # finishing r0 frees both of its slots; a new request may reuse them
+    s2 = a.prepare({"r1": [1], "r2": [2], "r3": [3]}, ["r0"], cp)
+    assert s2[0] == s0[1] and set(s2[1:]) <= {s0[0], s1[1], 0, 1, 2, 3} - {s0[1]}
+    assert len(a.free_cache_indices) == 1
+    # a request finished before it ever ran gets the PAD slot
+    assert a.prepare({"r9": [0]}, ["r9"], cp) == [PAD_SLOT_ID]
+    a.prepare({"r4": [0]}, [], cp)
+    with pytest.raises(RuntimeError, match="no free state slot"):
+        a.prepare({"r5": [0]}, [], cp)
+    assert a.cache_indices_mapping["r1"] == {1: s0[1]}
+
+
+def test_cache_managers_cpu_tensors():
+    L, S, Hs, D, M, Hkv = 2, 3, 2, 8, 4, 1
+    m = HymetaCacheManager(torch.bfloat16, (L, S, Hs, D, D), (L, Hs, D, D), (L, 2, M, Hkv, D), device="cpu")
+    state, meta_lin, meta_fa, idx = m.current_run_tensors(request_ids_to_seq_ids={"a": [0], "b": [1]},
+                                                          finished_requests_ids=[])
+    assert state.shape == (L, S, Hs, D, D) and state.abs().max() == 0          # zero-initialised (Q7)
+    assert meta_lin.shape == (L, Hs, D, D) and meta_fa.shape == (L, 2, M, Hkv, D)
+    assert idx.dtype == torch.int32 and idx.numel() == 2
+    state[:, idx[0].item()] = 1.0
+    m._copy_cache(idx[0].item(), idx[1].item())
+    assert torch.equal(state[:, idx[1].item()], state[:, idx[0].item()])
+    m.clear_slots([idx[0].item()])
+    assert state[:, idx[0].item()].abs().max() == 0 and state[:, idx[1].item()].min() == 1
+    p = HymetaCacheParams(state, meta_lin, meta_fa, idx).at_layer_idx(1)
+    assert p.hymeta_cache.shape == (S, Hs, D, D) and p.meta_fattn_cache.shape == (2, M, Hkv, D)
+    # CUDA-graph protocol: capture buffers get PAD for rows beyond the live batch
+    cap = m.get_seqlen_agnostic_capture_inputs(4)
+    assert cap[1].tolist() == [PAD_SLOT_ID] * 4
+    m.copy_inputs_before_cuda_graphs({"seqlen_agnostic_capture_inputs": cap},
+                                     request_ids_to_seq_ids={"a": [0], "b": [1]}, finished_requests_ids=[])
+    assert cap[1].tolist() == idx.tolist() + [PAD_SLOT_ID] * 2
+    g = GLACacheManager(torch.bfloat16, (L, S, Hs, D, D), device="cpu")
+    cache, gi = g.current_run_tensors(request_ids_to_seq_ids={"x": [0]}, finished_requests_ids=[])
+    cache[:, gi[0].item()] = 2.0
+    g._copy_cache(gi[0].item(), (gi[0].item() + 1) % S)           # copies SLOTS
+    assert cache[:, (gi[0].item() + 1) % S].min() == 2
+
+
+def test_metadata_builder_mixed_batch_bit_exact():
+    bs = 16
+    b = MetaAttentionMetadataBuilder(block_size=bs, sliding_window=None, device="cpu")
+    # two prompts (one chunk-continued with context 16) then two decodes
+    b.add(SeqData(True, 20, 20, 0, [3, 9]))
+    b.add(SeqData(True, 40, 24, 16, [5, 1, 7]))
+    b.add(SeqData(False, 33, 1, 32, [2, 4, 6]))
+    b.add(SeqData(False, 17, 1, 16, [8, 0]))
+    md = b.build()
+    assert (md.num_prefills, md.num_prefill_tokens, md.num_decode_tokens) == (2, 44, 2)
+    exp = [3 * bs + i for i in range(16)] + [9 * bs + i for i in range(4)]
+    exp += [1 * bs + i for i in range(16)] + [7 * bs + i for i in range(8)]
+    exp += [6 * bs + 0, 0 * bs + 0]
+    assert md.slot_mapping.tolist() == exp and md.slot_mapping.dtype == torch.int64
+    assert md.query_start_loc.tolist() == [0, 20, 44, 45, 46]
+    assert md.seq_start_loc.tolist() == [0, 20, 60, 93, 110]
+    assert md.context_lens_tensor.tolist() == [0, 16, 32, 16]
+    assert md.block_tables.dtype == torch.int32
+    assert md.block_tables.tolist() == [[0, 0, 0], [0, 0, 0], [2, 4, 6], [8, 0, 0]]   # prompts: no cache read
+    pm, dm = md.prefill_metadata, md.decode_metadata
+    assert pm.seq_lens == [20, 40] and pm.slot_mapping.numel() == 44 and pm.max_prefill_seq_len == 40
+    assert dm.seq_lens_tensor.tolist() == [33, 17] and dm.query_start_loc.tolist() == [0, 1, 2]
+    assert dm.block_tables.tolist() == [[2, 4, 6], [8, 0, 0]] and dm.max_decode_seq_len == 33
+
+
+def test_metadata_builder_window_graph_and_profile():
+    bs = 16
+    # sliding window 32: prompt tokens that fall out of the window are never cached
+    b = MetaAttentionMetadataBuilder(block_size=bs, sliding_window=32, device="cpu")
+    b.add(SeqData(True, 40, 40, 0, [1, 2, 3]))
+    md = b.build()
+    assert md.slot_mapping.tolist() == [PAD_SLOT_ID] * 8 + [1 * bs + i for i in range(8, 16)] + \
+        [2 * bs + i for i in range(16)] + [3 * bs + i for i in range(8)]
+    # decode with a windowed block table keeps the last blocks only
+    b = MetaAttentionMetadataBuilder(block_size=bs, sliding_window=32, device="cpu")
+    b.add(SeqData(False, 32, 1, 49, [1, 2, 3, 4], curr_sliding_window_block=2, orig_seq_len=50))
+    assert b.block_tables == [[3, 4]]
+    # CUDA-graph build pads slots with PAD and uses the runner's fixed-width table
+    import numpy as np
+    b = MetaAttentionMetadataBuilder(block_size=bs, sliding_window=None, device="cpu",
+                                     graph_block_tables=np.zeros((4, 5), dtype=np.int32))
+    b.add(SeqData(False, 18, 1, 17, [7, 8]))
+    md = b.build(cuda_graph_pad_size=3, batch_size=4)
+    assert md.use_cuda_graph and md.slot_mapping.tolist() == [8 * bs + 1] + [PAD_SLOT_ID] * 3
+    assert md.block_tables.shape == (1, 5) and md.block_tables[0].tolist() == [7, 8, 0, 0, 0]
+    assert md.num_decode_tokens == 4
+    # profiling run: no block table -> every slot is PAD
+    b = MetaAttentionMetadataBuilder(block_size=bs, sliding_window=None, device="cpu")
+    b.add(SeqData(True, 6, 6, 0, None))
+    assert b.build().slot_mapping.tolist() == [PAD_SLOT_ID] * 6
+
+
+def test_backend_surface_and_errors():
+    B = MetaAttentionBackend
+    assert B.get_name() == "META_FLASH_ATTN" and B.accept_output_buffer
+    assert B.get_kv_cache_shape(10, 256, 4, 128) == (2, 10, 256, 4, 128)
+    for bad in (8, 24, 250):
+        with pytest.raises(ValueError):
+            B.get_kv_cache_shape(10, bad, 4, 128)
+    assert B.get_impl_cls() is MetaAttentionImpl
+    kw = dict(num_heads=28, head_size=128, scale=128 ** -0.5, num_kv_heads=4, alibi_slopes=None,
+              sliding_window=4096, kv_cache_dtype="auto")
+    impl = MetaAttentionImpl(**kw)
+    assert impl.sliding_window == (4095, 0) and impl.num_queries_per_kv == 7 and impl.num_meta_tokens == 128
+    assert MetaAttentionImpl(**{**kw, "sliding_window": None}).sliding_window == (-1, -1)
+    with pytest.raises(ValueError):
+        MetaAttentionImpl(**{**kw, "head_size": 80})
+    with pytest.raises(ValueError):
+        MetaAttentionImpl(**kw, blocksparse_params={"x": 1})
+    with pytest.raises(NotImplementedError):
+        MetaAttentionImpl(**kw, kv_sharing_target_layer_name="l0")
+    with pytest.raises(NotImplementedError):
+        MetaAttentionImpl(**{**kw, "kv_cache_dtype": "fp8"})
+    # swap / copy blocks are plain tensor moves
+    kv = torch.arange(2 * 4 * 2 * 1 * 2, dtype=torch.float32).view(2, 4, 2, 1, 2)
+    dst = torch.zeros_like(kv)
+    B.swap_blocks(kv, dst, torch.tensor([[1, 3]]))
+    assert torch.equal(dst[:, 3], kv[:, 1]) and dst[:, 1].abs().max() == 0
+    B.copy_blocks([kv], torch.tensor([[0, 2]]))
+    assert torch.equal(kv[:, 2], kv[:, 0])
+
+
+def test_plugin_entry_points_do_not_touch_cuda():
+    import vllm_hymeta_b200 as pkg
+    assert pkg.register() == "vllm_hymeta_b200.platform.HymetaCudaPlatform"
+    pkg.register_model()                      # no reference plugin importable here: a no-op
+    from vllm_hymeta_b200.platform import HymetaCudaPlatform as P
+    assert P.get_attn_backend_cls("XFORMERS", 128, None, None, 256, False, False).endswith("FlashAttentionBackend")
+    assert P.get_attn_backend_cls(None, 128, None, None, 256, False, False) == \
+        "vllm_hymeta_b200.attention.meta_attention.MetaAttentionBackend"
+    assert not torch.cuda.is_initialized()

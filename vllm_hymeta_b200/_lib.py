@@ -20,8 +20,10 @@ SIGNATURES = {
     "hymeta_status_string": (C.c_char_p, [_i]),
     "hymeta_last_cuda_error": (_i, []),
     "hymeta_launch_count": (_i64, []),
-    "hymeta_gla_decode": (_i, [_p] * 7 + [_i] * 5 + [_i64] * 12 + [_i, _f, _p]),
-    "hymeta_gla_prefill_varlen": (_i, [_p] * 10 + [_i] * 6 + [_i64] * 13 + [_i, _f, _i, _i, _p]),
+    "hymeta_gla_decode": (_i, [_p] * 7 + [_i] * 6 + [_i64] * 12 + [_i, _f, _p]),
+    "hymeta_gla_prefill_varlen": (_i, [_p] * 10 + [_i] * 7 + [_i64] * 13 + [_i, _f, _i, _i, _p]),
+    "hymeta_gla_gate_70b": (_i, [_p] * 6 + [_i] * 5 + [_i64] * 10 + [_f, _p]),
+    "hymeta_gla_gate_7b": (_i, [_p] * 6 + [_i] * 4 + [_i64] * 12 + [_f, _p]),
     "hymeta_kv_write_paged": (_i, [_p] * 5 + [_i] * 4 + [_i64] * 10 + [_p]),
     "hymeta_swa_decode_workspace_bytes": (_sz, [_i] * 8),
     "hymeta_swa_meta_decode_paged": (_i, [_p] * 9 + [_sz] + [_i] * 8 + [_i64, _i, _f] + [_i64] * 14 + [_p]),
@@ -49,7 +51,7 @@ def lib() -> C.CDLL:
         for name, (res, args) in SIGNATURES.items():
             fn = getattr(h, name)      # AttributeError if the library lacks a declared symbol
             fn.restype, fn.argtypes = res, args
-        if h.hymeta_abi_version() != 1:
+        if h.hymeta_abi_version() != 2:
             raise ImportError("hymeta_b200 ABI version mismatch")
         _lib = h
     return _lib

@@ -4,11 +4,20 @@
 //   S <- bf16(k (x) v) + exp(g)[:,None] * S        (fp32 math, bf16 store)
 //   o  = (q * scale)^T S                            (all q-heads sharing the state)
 //
-// Grid (D/DVS, Hs, B): one CTA owns all 128 d_k rows of a DVS-wide d_v slice, so the reduction
-// over d_k stays inside the CTA (warp shuffles + one smem pass) and every state byte is touched
-// by exactly one thread with 128-bit loads/stores.  The G = H/Hs q-heads of a GQA group are all
-// served from the single state read.
+// Grid (D/DVS, Hs, B), 128 threads.  One CTA owns all 128 d_k rows of a DVS-wide d_v slice of one
+// state; a lane owns 8 consecutive d_v columns (one 128-bit load / store per row it visits) and warp
+// w owns rows [32w, 32w+32), so every lane has DVS/8 independent 16-byte loads in flight before the
+// first use and every state byte is touched by exactly one thread.  The G = H/Hs q-heads of a GQA
+// group are all served from the single state read.
+// Instruction diet (the kernel is issue-bound long before it is FLOP-bound: 7 heads x 128 x 128 FMAs
+// per 32 KB of state): the bf16 product k*v is ONE packed HMUL2.BF16 per column pair (bit-identical
+// to the reference's bf16 `b_k[:, None] * b_v[None, :]`, my_fused_recurrent.py:65), the decay and the
+// per-head read-out run on packed FFMA2 (fma.rn.f32x2), q is fetched as two 128-bit shared loads
+// per row for all heads.  The reduction over d_k is log2(rows per warp instr) shuffle stages plus
+// one pass through shared memory across the 4 warps.
 #include "common.cuh"
+
+#include <cstdlib>
 
 namespace hymeta {
 
@@ -18,129 +27,244 @@ struct GlaDecodeParams {
   __nv_bfloat16* o;
   __nv_bfloat16* state;
   const int32_t* slot_idx;
-  int B, H, Hk, Hs;
+  int B, H, Hk, Hv, Hs;
+  uint32_t kmagic, vmagic;   // (hs * magic) >> 16 == hs / (Hs/Hk) resp. hs / (Hs/Hv), checked on the host
   int64_t q_sb, q_sh, k_sb, k_sh, v_sb, v_sh, g_sb, g_sh, o_sb, o_sh, st_ss, st_sh;
   float scale;
 };
 
-template <int DVS, int GT, bool GF32>
-__global__ void __launch_bounds__(256) gla_decode_kernel(const GlaDecodeParams p) {
-  constexpr int TPR = DVS / 8;    // threads per state row (16 B each)
-  constexpr int RPP = 256 / TPR;  // rows per pass
-  constexpr int NP = kD / RPP;    // passes
-  const int b = blockIdx.z, hs = blockIdx.y, dv0 = blockIdx.x * DVS;
-  const int G = p.H / p.Hs;
-  const int hk = hs / (p.Hs / p.Hk);
-  const int h0 = hs * G;
+typedef unsigned long long u64;
+__device__ __forceinline__ u64 pack2(float lo, float hi) {
+  u64 r;
+  asm("mov.b64 %0, {%1,%2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void unpack2(u64 v, float& lo, float& hi) {
+  asm("mov.b64 {%0,%1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ u64 ffma2(u64 a, u64 b, u64 c) {
+  u64 d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
+__device__ __forceinline__ uint32_t hmul2_bf16(uint32_t a, uint32_t b) {
+  uint32_t d;
+  asm("mul.rn.bf16x2 %0, %1, %2;" : "=r"(d) : "r"(a), "r"(b));
+  return d;
+}
+
+constexpr int GD_NS = 3;                         // ring stages (one item each)
+constexpr int GD_STATE_BYTES = kD * kD * 2;       // 32 KB state
+constexpr int GD_RAW_Q = GD_STATE_BYTES;          // raw q   [8 heads][128] bf16   2 KB
+constexpr int GD_RAW_K = GD_RAW_Q + 2048;         // raw k   [128] bf16
+constexpr int GD_RAW_V = GD_RAW_K + 256;          // raw v   [128] bf16
+constexpr int GD_RAW_G = GD_RAW_V + 256;          // raw g   [128] fp32 (or bf16 in the first half)
+constexpr int GD_STAGE = GD_RAW_G + 512;          // 35840 B per stage
+constexpr int GD_THREADS = 256;
+constexpr int GD_SQ = GD_NS * GD_STAGE;           // s_q  [128][8] f32  (scaled, fp32)
+constexpr int GD_SKG = GD_SQ + kD * 8 * 4;        // s_kg [128] {k bf16x2, exp(g)}
+constexpr int GD_SMEM = GD_SKG + kD * 8;
+
+// Persistent, software-pipelined: CTA c handles items c, c+grid, ... (item = one (request,
+// state-head) 128x128 state with its small operands).  Item i+2 streams into a 3-stage
+// shared-memory ring with cp.async while item i is being computed, so no global-load latency is
+// ever exposed inside the loop: per item the CTA waits on one cp.async group, converts the small
+// operands warp-locally (each warp only needs q/k/g of its own 16 d_k rows), runs the FFMA2 main
+// loop out of shared memory and stores the new state straight from registers.
+// GT >= G = H/Hs: q-heads served per state (accumulators per lane: GT x 8 columns).
+template <int GT, bool GF32>
+__global__ void __launch_bounds__(GD_THREADS, 2) gla_decode_kernel(const GlaDecodeParams p, const int n_items) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  float (*s_q)[8] = reinterpret_cast<float (*)[8]>(smem + GD_SQ);
+  uint2* s_kg = reinterpret_cast<uint2*>(smem + GD_SKG);
+  const uint32_t ring = smem_u32(smem);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int c = tid % TPR, r0 = tid / TPR;
+  const int c = lane & 15, rg = lane >> 4;          // 16-byte column chunk / row inside a warp instr
+  const int G = p.H / p.Hs;
+  const int gs = gridDim.x;
+  const int gs_b = gs / p.Hs, gs_h = gs % p.Hs;     // item stride decomposed: no per-item division
 
-  const int slot = p.slot_idx[b];
-  if (slot < 0) {  // PAD slot (CUDA-graph padding): skip, emit zeros
-    for (int i = tid; i < G * DVS; i += 256)
-      p.o[b * p.o_sb + (h0 + i / DVS) * p.o_sh + dv0 + (i % DVS)] = __float2bfloat16(0.f);
-    return;
-  }
-
-  __shared__ float s_k[kD], s_eg[kD];
-  __shared__ float s_q[GT][kD];
-  __shared__ float s_red[8][GT][DVS];
-
-  // 1. state loads first: they head the longest dependency chain
-  __nv_bfloat16* sp = p.state + (int64_t)slot * p.st_ss + (int64_t)hs * p.st_sh + dv0 + c * 8;
-  uint4 sv[NP];
+  struct Item { int b, hs, slot; };
+  auto advance = [&](Item x) -> Item {              // item + gs
+    x.b += gs_b; x.hs += gs_h;
+    if (x.hs >= p.Hs) { x.hs -= p.Hs; ++x.b; }
+    x.slot = x.b < p.B ? p.slot_idx[x.b] : -1;
+    return x;
+  };
+  // small-operand copy role of this thread: one 16-byte chunk (or none)
+  //   tid <  128: q head tid/16, rows 8*(tid%16)..   128..143: k   144..159: v   160..191: g
+  auto issue = [&](const Item& x, int stage) {
+    if (x.slot >= 0) {
+      const uint32_t sb = ring + stage * GD_STAGE;
+      {  // this thread's 8 chunks of the state
+        const __nv_bfloat16* src = p.state + (int64_t)x.slot * p.st_ss + (int64_t)x.hs * p.st_sh +
+                                   (warp * 16 + rg) * kD + c * 8;
+        const uint32_t dst = sb + (warp * 16 + rg) * 256 + c * 16;
 #pragma unroll
-  for (int i = 0; i < NP; ++i) sv[i] = ldg_v4(sp + (i * RPP + r0) * kD);
+        for (int i = 0; i < 8; ++i) cp_async16(dst + i * 512, src + i * 2 * kD, true);
+      }
+      if (tid < 128) {
+        const int hh = tid >> 4, ch = tid & 15;
+        const bool ok = hh < G;
+        cp_async16(sb + GD_RAW_Q + tid * 16, p.q + x.b * p.q_sb + (int64_t)(x.hs * G + (ok ? hh : 0)) * p.q_sh + ch * 8, ok);
+      } else if (tid < 144) {
+        cp_async16(sb + GD_RAW_K + (tid - 128) * 16,
+                   p.k + x.b * p.k_sb + (int64_t)((x.hs * p.kmagic) >> 16) * p.k_sh + (tid - 128) * 8, true);
+      } else if (tid < 160) {
+        cp_async16(sb + GD_RAW_V + (tid - 144) * 16,
+                   p.v + x.b * p.v_sb + (int64_t)((x.hs * p.vmagic) >> 16) * p.v_sh + (tid - 144) * 8, true);
+      } else if (tid < (GF32 ? 192 : 176)) {
+        const int64_t off = x.b * p.g_sb + (int64_t)((x.hs * p.kmagic) >> 16) * p.g_sh;
+        if (GF32) cp_async16(sb + GD_RAW_G + (tid - 160) * 16, reinterpret_cast<const float*>(p.g) + off + (tid - 160) * 4, true);
+        else cp_async16(sb + GD_RAW_G + (tid - 160) * 16, reinterpret_cast<const __nv_bfloat16*>(p.g) + off + (tid - 160) * 8, true);
+      }
+    }
+    cp_async_commit();
+  };
 
-  // 2. k, exp(g) -> smem; v slice -> registers
-  if (tid < kD) {
-    s_k[tid] = __bfloat162float(p.k[b * p.k_sb + hk * p.k_sh + tid]);
-    float gv;
-    if (GF32) gv = reinterpret_cast<const float*>(p.g)[b * p.g_sb + hk * p.g_sh + tid];
-    else gv = __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(p.g)[b * p.g_sb + hk * p.g_sh + tid]);
-    s_eg[tid] = expf(gv);
-  }
-  float vv[8];
-  {
-    uint4 t = ldg_nc_v4(p.v + b * p.v_sb + hk * p.v_sh + dv0 + c * 8);
-    vv[0] = bf16_lo(t.x); vv[1] = bf16_hi(t.x); vv[2] = bf16_lo(t.y); vv[3] = bf16_hi(t.y);
-    vv[4] = bf16_lo(t.z); vv[5] = bf16_hi(t.z); vv[6] = bf16_lo(t.w); vv[7] = bf16_hi(t.w);
-  }
+  Item cur_i;
+  cur_i.b = blockIdx.x / p.Hs; cur_i.hs = blockIdx.x % p.Hs;
+  cur_i.slot = p.slot_idx[cur_i.b];
+  Item n1 = advance(cur_i), n2 = advance(n1), n3 = advance(n2);
+  issue(cur_i, 0);
+  issue(n1, 1);
 
-  float sn[NP][8];  // new state (fp32, un-rounded: the output reduces this, my_fused_recurrent.py:75)
-  for (int hc = 0; hc < G; hc += GT) {
-    const int ng = min(GT, G - hc);
-    for (int i = tid; i < ng * kD; i += 256)
-      s_q[i / kD][i % kD] =
-          __bfloat162float(p.q[b * p.q_sb + (h0 + hc + i / kD) * p.q_sh + (i % kD)]) * p.scale;
-    __syncthreads();
+  for (int k = 0; cur_i.b < p.B; ++k) {
+    const int stage = k % GD_NS;
+    const Item n4 = advance(n3);                     // slot prefetched two iterations before its use
+    cp_async_wait<1>();                              // own chunks of item k have landed ...
+    __syncthreads();                                 // ... and everyone else's; item k-1 is fully consumed
+    issue(n2, (k + 2) % GD_NS);                      // refill the stage item k-1 used
+    const int h0 = cur_i.hs * G;
+    __nv_bfloat16* op = p.o + cur_i.b * p.o_sb + (int64_t)(h0 + (tid >> 7)) * p.o_sh + (tid & 127);
+    if (cur_i.slot < 0) {   // PAD slot (CUDA-graph padding): skip, emit zeros (CTA-uniform branch)
+#pragma unroll 1
+      for (int hh = tid >> 7; hh < G; hh += 2, op += 2 * p.o_sh) *op = __float2bfloat16(0.f);
+      cur_i = n1; n1 = n2; n2 = n3; n3 = n4;
+      continue;
+    }
+    uint8_t* sbase = smem + stage * GD_STAGE;
+    {  // warp-local conversion of the small operands of this warp's 16 rows
+      const int row = warp * 16 + (lane & 15), hf = lane >> 4;
+      const __nv_bfloat16* rq = reinterpret_cast<const __nv_bfloat16*>(sbase + GD_RAW_Q) + row;
+      float4 t;
+      t.x = __bfloat162float(rq[(hf * 4 + 0) * kD]) * p.scale;
+      t.y = __bfloat162float(rq[(hf * 4 + 1) * kD]) * p.scale;
+      t.z = __bfloat162float(rq[(hf * 4 + 2) * kD]) * p.scale;
+      t.w = __bfloat162float(rq[(hf * 4 + 3) * kD]) * p.scale;
+      *reinterpret_cast<float4*>(&s_q[row][hf * 4]) = t;
+      if (hf == 0) {
+        const uint32_t kb = (uint32_t)reinterpret_cast<const uint16_t*>(sbase + GD_RAW_K)[row];
+        s_kg[row].x = kb | (kb << 16);
+      } else {
+        float gv;
+        if (GF32) gv = reinterpret_cast<const float*>(sbase + GD_RAW_G)[row];
+        else gv = __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(sbase + GD_RAW_G)[row]);
+        s_kg[row].y = __float_as_uint(expf(gv));
+      }
+    }
+    const uint4 vraw = *reinterpret_cast<const uint4*>(sbase + GD_RAW_V + c * 16);
+    const uint32_t vv[4] = {vraw.x, vraw.y, vraw.z, vraw.w};
+    __nv_bfloat16* sp = p.state + (int64_t)cur_i.slot * p.st_ss + (int64_t)cur_i.hs * p.st_sh +
+                        (warp * 16 + rg) * kD + c * 8;
+    const uint32_t st_base = ring + stage * GD_STAGE + (warp * 16 + rg) * 256 + c * 16;
+    __syncwarp();
 
-    float acc[GT][8];
+    u64 acc[GT][4];
 #pragma unroll
     for (int hh = 0; hh < GT; ++hh)
 #pragma unroll
-      for (int j = 0; j < 8; ++j) acc[hh][j] = 0.f;
+      for (int j = 0; j < 4; ++j) acc[hh][j] = 0ull;
 
+    const uint2* kgp = s_kg + warp * 16 + rg;
+    const float* qrow = &s_q[warp * 16 + rg][0];
 #pragma unroll
-    for (int i = 0; i < NP; ++i) {
-      const int r = i * RPP + r0;
-      if (hc == 0) {
-        const float kr = s_k[r], eg = s_eg[r];
-        const uint32_t w[4] = {sv[i].x, sv[i].y, sv[i].z, sv[i].w};
+    for (int i = 0; i < 8; ++i) {                    // row r = warp*16 + 2i + rg
+      uint4 w4;
+      asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];"
+                   : "=r"(w4.x), "=r"(w4.y), "=r"(w4.z), "=r"(w4.w) : "r"(st_base + i * 512));
+      const uint2 kg = kgp[2 * i];
+      const float eg = __uint_as_float(kg.y);
+      const uint32_t w[4] = {w4.x, w4.y, w4.z, w4.w};
+      u64 sn[4];   // new state, fp32 pairs, un-rounded (the output reduces this, my_fused_recurrent.py:75)
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          sn[i][2 * j] = round_bf16(kr * vv[2 * j]) + eg * bf16_lo(w[j]);
-          sn[i][2 * j + 1] = round_bf16(kr * vv[2 * j + 1]) + eg * bf16_hi(w[j]);
-        }
+      for (int j = 0; j < 4; ++j) {
+        const uint32_t kv = hmul2_bf16(kg.x, vv[j]);            // bf16(k * v), both columns
+        sn[j] = ffma2(pack2(eg, eg), pack2(bf16_lo(w[j]), bf16_hi(w[j])),
+                      pack2(bf16_lo(kv), bf16_hi(kv)));
+      }
+      {
         uint4 st;
-        st.x = pack_bf16(sn[i][0], sn[i][1]); st.y = pack_bf16(sn[i][2], sn[i][3]);
-        st.z = pack_bf16(sn[i][4], sn[i][5]); st.w = pack_bf16(sn[i][6], sn[i][7]);
-        stg_v4(sp + r * kD, st);
+        float a, bb;
+        unpack2(sn[0], a, bb); st.x = pack_bf16(a, bb);
+        unpack2(sn[1], a, bb); st.y = pack_bf16(a, bb);
+        unpack2(sn[2], a, bb); st.z = pack_bf16(a, bb);
+        unpack2(sn[3], a, bb); st.w = pack_bf16(a, bb);
+        stg_v4(sp + i * 2 * kD, st);
+      }
+      float qr[8];
+      {
+        const float4 t0 = *reinterpret_cast<const float4*>(qrow + i * 16);
+        qr[0] = t0.x; qr[1] = t0.y; qr[2] = t0.z; qr[3] = t0.w;
+        if (GT > 4) {
+          const float4 t1 = *reinterpret_cast<const float4*>(qrow + i * 16 + 4);
+          qr[4] = t1.x; qr[5] = t1.y; qr[6] = t1.z; qr[7] = t1.w;
+        }
       }
 #pragma unroll
       for (int hh = 0; hh < GT; ++hh) {
-        if (hh < ng) {
-          const float qr = s_q[hh][r];
+        const u64 q2 = pack2(qr[hh], qr[hh]);
 #pragma unroll
-          for (int j = 0; j < 8; ++j) acc[hh][j] = fmaf(qr, sn[i][j], acc[hh][j]);
-        }
+        for (int j = 0; j < 4; ++j) acc[hh][j] = ffma2(q2, sn[j], acc[hh][j]);
       }
     }
 
-    // reduce over d_k: lanes sharing the column chunk, then the 8 warps
+    // reduce over d_k: the two rows of a warp instr by shuffle, then the 8 warps through smem
+    // (the scratch aliases this item's state: every thread is done reading it after the barrier)
+    __syncthreads();
+    float* s_red = reinterpret_cast<float*>(sbase);   // [8][GT][128]
 #pragma unroll
     for (int hh = 0; hh < GT; ++hh) {
-      if (hh < ng) {
+      float a[8];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          float x = acc[hh][j];
+      for (int j = 0; j < 4; ++j) unpack2(acc[hh][j], a[2 * j], a[2 * j + 1]);
 #pragma unroll
-          for (int off = 16; off >= TPR; off >>= 1) x += __shfl_xor_sync(0xffffffffu, x, off);
-          acc[hh][j] = x;
-        }
-        if (lane < TPR) {
-#pragma unroll
-          for (int j = 0; j < 8; ++j) s_red[warp][hh][c * 8 + j] = acc[hh][j];
-        }
+      for (int j = 0; j < 8; ++j) a[j] += __shfl_xor_sync(0xffffffffu, a[j], 16);
+      if (lane < 16) {
+        float4* dst = reinterpret_cast<float4*>(&s_red[(warp * GT + hh) * kD + c * 8]);
+        dst[0] = make_float4(a[0], a[1], a[2], a[3]);
+        dst[1] = make_float4(a[4], a[5], a[6], a[7]);
       }
     }
     __syncthreads();
-    for (int i = tid; i < ng * DVS; i += 256) {
-      const int hh = i / DVS, j = i % DVS;
-      float x = 0.f;
+    {
+      const float* rp = s_red + (tid >> 7) * kD + (tid & 127);
+#pragma unroll 1
+      for (int hh = tid >> 7; hh < G; hh += 2, op += 2 * p.o_sh, rp += 2 * kD) {
+        float x = 0.f;
 #pragma unroll
-      for (int w = 0; w < 8; ++w) x += s_red[w][hh][j];
-      p.o[b * p.o_sb + (h0 + hc + hh) * p.o_sh + dv0 + j] = __float2bfloat16_rn(x);
+        for (int w = 0; w < 8; ++w) x += rp[w * GT * kD];
+        *op = __float2bfloat16_rn(x);
+      }
     }
-    __syncthreads();
+    // no barrier here: the next iteration's top barrier orders these reads before the refill
+    cur_i = n1; n1 = n2; n2 = n3; n3 = n4;
   }
+  cp_async_wait<0>();
 }
 
-template <int DVS, int GT>
+template <int GT>
 static void launch_gla_decode(const GlaDecodeParams& p, bool g_fp32, cudaStream_t st) {
-  dim3 grid(kD / DVS, p.Hs, p.B), block(256);
-  if (g_fp32) gla_decode_kernel<DVS, GT, true><<<grid, block, 0, st>>>(p);
-  else gla_decode_kernel<DVS, GT, false><<<grid, block, 0, st>>>(p);
+  const long n_items = (long)p.B * p.Hs;
+  const int grid = (int)(n_items < 2 * 148 ? n_items : 2 * 148);
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaFuncSetAttribute(gla_decode_kernel<GT, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, GD_SMEM);
+    cudaFuncSetAttribute(gla_decode_kernel<GT, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, GD_SMEM);
+    attr_set = true;
+  }
+  if (g_fp32) gla_decode_kernel<GT, true><<<grid, GD_THREADS, GD_SMEM, st>>>(p, (int)n_items);
+  else gla_decode_kernel<GT, false><<<grid, GD_THREADS, GD_SMEM, st>>>(p, (int)n_items);
 }
 
 }  // namespace hymeta
@@ -148,36 +272,44 @@ static void launch_gla_decode(const GlaDecodeParams& p, bool g_fp32, cudaStream_
 using namespace hymeta;
 
 extern "C" int hymeta_gla_decode(const void* q, const void* k, const void* v, const void* g, void* o,
-                                 void* state, const int32_t* slot_idx, int B, int H, int Hk, int Hs,
-                                 int D, int64_t q_sb, int64_t q_sh, int64_t k_sb, int64_t k_sh,
+                                 void* state, const int32_t* slot_idx, int B, int H, int Hk, int Hv,
+                                 int Hs, int D, int64_t q_sb, int64_t q_sh, int64_t k_sb, int64_t k_sh,
                                  int64_t v_sb, int64_t v_sh, int64_t g_sb, int64_t g_sh,
                                  int64_t o_sb, int64_t o_sh, int64_t st_ss, int64_t st_sh,
                                  int g_is_fp32, float scale, void* stream) {
   if (B == 0) return HYMETA_OK;
-  if (!q || !k || !v || !g || !o || !state || !slot_idx || B < 0 || H <= 0 || Hk <= 0 || Hs <= 0)
+  if (!q || !k || !v || !g || !o || !state || !slot_idx || B < 0 || H <= 0 || Hk <= 0 || Hv <= 0 || Hs <= 0)
     return HYMETA_ERR_INVALID_ARG;
   if (D != kD) return HYMETA_ERR_UNSUPPORTED;
-  if (H % Hs != 0 || Hs % Hk != 0) return HYMETA_ERR_INVALID_ARG;
-  if ((st_ss % 8) || (st_sh % 8) || (v_sb % 8) || (v_sh % 8)) return HYMETA_ERR_INVALID_ARG;
+  if (H % Hs != 0 || Hs % Hk != 0 || Hs % Hv != 0) return HYMETA_ERR_INVALID_ARG;
+  if (H / Hs > 8 || Hs > 4096) return HYMETA_ERR_UNSUPPORTED;   // as the prefill kernel: at most 8 q-heads per state
+  // every operand is moved with 16-byte cp.async: bases and strides must keep that alignment
+  const int gdiv = g_is_fp32 ? 4 : 8;
+  if ((st_ss % 8) || (st_sh % 8) || (v_sb % 8) || (v_sh % 8) || (q_sb % 8) || (q_sh % 8) || (k_sb % 8) ||
+      (k_sh % 8) || (g_sb % gdiv) || (g_sh % gdiv))
+    return HYMETA_ERR_INVALID_ARG;
+  if (((uintptr_t)q | (uintptr_t)k | (uintptr_t)v | (uintptr_t)g | (uintptr_t)state) & 15)
+    return HYMETA_ERR_INVALID_ARG;
   if (B > 65535) return HYMETA_ERR_UNSUPPORTED;
   GlaDecodeParams p{(const __nv_bfloat16*)q, (const __nv_bfloat16*)k, (const __nv_bfloat16*)v, g,
-                    (__nv_bfloat16*)o, (__nv_bfloat16*)state, slot_idx, B, H, Hk, Hs,
+                    (__nv_bfloat16*)o, (__nv_bfloat16*)state, slot_idx, B, H, Hk, Hv, Hs, 0u, 0u,
                     q_sb, q_sh, k_sb, k_sh, v_sb, v_sh, g_sb, g_sh, o_sb, o_sh, st_ss, st_sh, scale};
+  auto magic = [&](int div) -> uint32_t {   // exact for hs < Hs <= 4096 (verified below)
+    const uint32_t m = (65536u + div - 1) / div;
+    for (int x = 0; x < Hs; ++x)
+      if ((int)((x * m) >> 16) != x / div) return 0u;
+    return m;
+  };
+  p.kmagic = magic(Hs / Hk); p.vmagic = magic(Hs / Hv);
+  if (!p.kmagic || !p.vmagic) return HYMETA_ERR_UNSUPPORTED;
   cudaStream_t st = (cudaStream_t)stream;
   const int G = H / Hs;
-  const long states = (long)B * Hs;
-  // enough CTAs to cover 148 SMs a few times over; wider slices once the batch alone does that
-  const int dvs = states >= 1184 ? 128 : (states >= 592 ? 64 : 32);
+  if ((long)B * Hs > 0x7fffffffL) return HYMETA_ERR_UNSUPPORTED;
   const bool f = g_is_fp32 != 0;
-  if (G == 1) {
-    if (dvs == 128) launch_gla_decode<128, 1>(p, f, st);
-    else if (dvs == 64) launch_gla_decode<64, 1>(p, f, st);
-    else launch_gla_decode<32, 1>(p, f, st);
-  } else {
-    if (dvs == 128) launch_gla_decode<128, 8>(p, f, st);
-    else if (dvs == 64) launch_gla_decode<64, 8>(p, f, st);
-    else launch_gla_decode<32, 8>(p, f, st);
-  }
+  if (G == 1) launch_gla_decode<1>(p, f, st);
+  else if (G <= 4) launch_gla_decode<4>(p, f, st);
+  else if (G == 7) launch_gla_decode<7>(p, f, st);
+  else launch_gla_decode<8>(p, f, st);
   count_launch();
   return check_launch();
 }

@@ -35,7 +35,7 @@ struct GlaPrefillParams {
   __nv_bfloat16 *o, *state;
   const __nv_bfloat16* meta_state;
   const int32_t *cu, *slot, *init_mode;
-  int N, H, Hk, Hs, write_state;
+  int N, H, Hk, Hv, Hs, write_state;
   float scale;
   int64_t q_st, q_sh, k_st, k_sh, v_st, v_sh, g_st, g_sh, o_st, o_sh, st_ss, st_sh, meta_sh;
 };
@@ -45,7 +45,7 @@ __global__ void __launch_bounds__(128, 2) gla_prefill_kernel(const GlaPrefillPar
   extern __shared__ __align__(1024) uint8_t smem[];
   const int tid = threadIdx.x, warp = tid >> 5;
   const int hs = blockIdx.x, n = blockIdx.y;
-  const int G = p.H / p.Hs, h0 = hs * G, hk = hs / (p.Hs / p.Hk);
+  const int G = p.H / p.Hs, h0 = hs * G, hk = hs / (p.Hs / p.Hk), hv = hs / (p.Hs / p.Hv);
   const int tok_begin = p.cu[n], len = p.cu[n + 1] - tok_begin;
   const int slot = p.slot[n], mode = p.init_mode[n];
 
@@ -146,7 +146,7 @@ __global__ void __launch_bounds__(128, 2) gla_prefill_kernel(const GlaPrefillPar
     for (int i = 0; i < 2; ++i) {
       const int idx = tid + i * 128, t = idx >> 4, c = idx & 15;
       uint4 v4 = make_uint4(0, 0, 0, 0);
-      if (t < clen) v4 = ldg_nc_v4(p.v + (int64_t)(tok0 + t) * p.v_st + (int64_t)hk * p.v_sh + c * 8);
+      if (t < clen) v4 = ldg_nc_v4(p.v + (int64_t)(tok0 + t) * p.v_st + (int64_t)hv * p.v_sh + c * 8);
       *reinterpret_cast<uint4*>(smem + GP_SV + (c >> 3) * 2048 + sw128_chunk(t, c & 7)) = v4;
     }
     __syncthreads();   // sEq visible
@@ -265,17 +265,17 @@ using namespace hymeta;
 extern "C" int hymeta_gla_prefill_varlen(
     const void* q, const void* k, const void* v, const void* g, void* o, void* state,
     const void* meta_state, const int32_t* cu_seqlens, const int32_t* slot_idx,
-    const int32_t* init_mode, int N, int T, int H, int Hk, int Hs, int D, int64_t q_st, int64_t q_sh,
+    const int32_t* init_mode, int N, int T, int H, int Hk, int Hv, int Hs, int D, int64_t q_st, int64_t q_sh,
     int64_t k_st, int64_t k_sh, int64_t v_st, int64_t v_sh, int64_t g_st, int64_t g_sh, int64_t o_st,
     int64_t o_sh, int64_t st_ss, int64_t st_sh, int64_t meta_sh, int g_is_fp32, float scale,
     int write_state, int max_seqlen, void* stream) {
   (void)max_seqlen;
   if (N == 0) return HYMETA_OK;
-  if (N < 0 || T < 0 || H <= 0 || Hk <= 0 || Hs <= 0 || !cu_seqlens || !slot_idx || !init_mode || !state)
+  if (N < 0 || T < 0 || H <= 0 || Hk <= 0 || Hv <= 0 || Hs <= 0 || !cu_seqlens || !slot_idx || !init_mode || !state)
     return HYMETA_ERR_INVALID_ARG;
   if (T > 0 && (!q || !k || !v || !g || !o)) return HYMETA_ERR_INVALID_ARG;
   if (D != kD) return HYMETA_ERR_UNSUPPORTED;
-  if (H % Hs || Hs % Hk) return HYMETA_ERR_INVALID_ARG;
+  if (H % Hs || Hs % Hk || Hs % Hv) return HYMETA_ERR_INVALID_ARG;
   if (H / Hs > 8) return HYMETA_ERR_UNSUPPORTED;   // q-heads per state are stacked into one M=128 tile
   if (N > 65535) return HYMETA_ERR_UNSUPPORTED;
   const int64_t vec[] = {q_st, q_sh, v_st, v_sh, o_st, o_sh, st_ss, st_sh, meta_state ? meta_sh : 0};
@@ -285,7 +285,7 @@ extern "C" int hymeta_gla_prefill_varlen(
   p.q = (const __nv_bfloat16*)q; p.k = (const __nv_bfloat16*)k; p.v = (const __nv_bfloat16*)v; p.g = g;
   p.o = (__nv_bfloat16*)o; p.state = (__nv_bfloat16*)state; p.meta_state = (const __nv_bfloat16*)meta_state;
   p.cu = cu_seqlens; p.slot = slot_idx; p.init_mode = init_mode;
-  p.N = N; p.H = H; p.Hk = Hk; p.Hs = Hs; p.write_state = write_state; p.scale = scale;
+  p.N = N; p.H = H; p.Hk = Hk; p.Hv = Hv; p.Hs = Hs; p.write_state = write_state; p.scale = scale;
   p.q_st = q_st; p.q_sh = q_sh; p.k_st = k_st; p.k_sh = k_sh; p.v_st = v_st; p.v_sh = v_sh;
   p.g_st = g_st; p.g_sh = g_sh; p.o_st = o_st; p.o_sh = o_sh; p.st_ss = st_ss; p.st_sh = st_sh;
   p.meta_sh = meta_sh;

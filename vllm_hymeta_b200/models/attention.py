@@ -1,0 +1,90 @@
+"""SWA-with-meta-prefix module glue -- the reference ``MetaAttention`` layer
+(vllm_hymeta/models/attention.py:25-283) and the q/k/v handling of ``FlashAttention``
+(vllm_hymeta/models/modeling_hymeta.py:747-815), on the sm_100a backend.
+
+``MetaAttention`` owns the backend impl and the (vLLM-allocated) paged KV tensor and allocates the
+``[(M)+T, H*D]`` output buffer the impl writes in place; ``FlashAttention`` splits the meta tokens
+off the front of the batch while the shared meta caches warm up and stores their K/V in
+``meta_fattn_cache`` (they never enter the paged cache, :776-792).  Projections and RoPE are
+vLLM-side -- ``forward`` takes post-RoPE q/k/v.
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+
+from ..attention.meta_attention import MetaAttentionBackend, MetaAttentionImpl
+from .hymeta_cache import HymetaCacheParams
+
+
+class MetaAttention:
+    """Reference models/attention.py:25-283 without the vLLM config plumbing: same ``forward``
+    arguments; ``attn_metadata`` is passed explicitly instead of through vLLM's forward context."""
+
+    def __init__(self, num_heads: int, head_size: int, scale: float, num_kv_heads: Optional[int] = None,
+                 per_layer_sliding_window: Optional[int] = None, num_meta_tokens: int = 128,
+                 kv_cache_dtype: str = "auto", prefix: str = ""):
+        self.num_heads = num_heads
+        self.head_size = head_size
+        self.num_kv_heads = num_kv_heads if num_kv_heads is not None else num_heads
+        self.sliding_window = per_layer_sliding_window
+        self.attn_backend = MetaAttentionBackend
+        self.impl = MetaAttentionImpl(num_heads, head_size, scale, self.num_kv_heads, None,
+                                      per_layer_sliding_window, kv_cache_dtype,
+                                      num_meta_tokens=num_meta_tokens)
+        self.use_output = self.attn_backend.accept_output_buffer
+        self.layer_name = prefix
+        self.kv_cache = torch.tensor([])          # replaced by bind_kv_cache (reference :170-176)
+
+    def bind_kv_cache(self, kv_cache: torch.Tensor) -> None:
+        self.kv_cache = kv_cache
+
+    def forward(self, query, key, value, query2=None, key2=None, value2=None, attn_metadata=None,
+                output_shape: Optional[torch.Size] = None) -> torch.Tensor:
+        rows = query.shape[0] + (query2.shape[0] if query2 is not None else 0)
+        hidden = self.num_heads * self.head_size
+        output = torch.empty(output_shape if output_shape is not None else (rows, hidden),
+                             dtype=query.dtype, device=query.device)
+        q = query.view(-1, self.num_heads, self.head_size)
+        k = key.view(-1, self.num_kv_heads, self.head_size) if key is not None else None
+        v = value.view(-1, self.num_kv_heads, self.head_size) if value is not None else None
+        q2 = query2.view(-1, self.num_heads, self.head_size) if query2 is not None else None
+        self.impl.forward(self, q, k, v, q2, key2, value2, self.kv_cache, attn_metadata,
+                          output=output.view(-1, self.num_heads, self.head_size))
+        return output.view(-1, hidden)
+
+
+class FlashAttention:
+    """q/k/v handling of the reference ``FlashAttention.forward`` (modeling_hymeta.py:747-815)."""
+
+    def __init__(self, num_heads: int, num_kv_heads: int, head_dim: int, num_meta_tokens: int = 128,
+                 sliding_window: Optional[int] = None, layer_idx: Optional[int] = None):
+        self.num_heads, self.num_kv_heads, self.head_dim = num_heads, num_kv_heads, head_dim
+        self.q_size, self.kv_size = num_heads * head_dim, num_kv_heads * head_dim
+        self.num_meta_tokens = num_meta_tokens
+        self.layer_idx = layer_idx
+        self.scaling = head_dim ** -0.5
+        self.attn = MetaAttention(num_heads, head_dim, self.scaling, num_kv_heads,
+                                  per_layer_sliding_window=sliding_window,
+                                  num_meta_tokens=num_meta_tokens)
+
+    def forward(self, q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, kv_caches: HymetaCacheParams,
+                attn_metadata, has_meta_cache: Optional[bool] = False,
+                is_vllm_testing: bool = False) -> torch.Tensor:
+        """q [T, H*D], k, v [T, Hkv*D] after RoPE; rows = [meta tokens (warm-up only) | prefill |
+        decode].  Returns [T, H*D] with the meta rows first."""
+        M = self.num_meta_tokens
+        q1, k1, v1 = q, k, v
+        q2 = k2 = v2 = None
+        if (not has_meta_cache) and M > 0 and (not is_vllm_testing):
+            q1, k1, v1 = q[M:], k[M:], v[M:]
+            # only the pass that first sees the meta tokens needs their queries (:780)
+            q2 = q[:M].reshape(M, self.num_heads, self.head_dim)
+            kv_caches.meta_fattn_cache[0].copy_(k[:M].reshape(M, self.num_kv_heads, self.head_dim))
+            kv_caches.meta_fattn_cache[1].copy_(v[:M].reshape(M, self.num_kv_heads, self.head_dim))
+        if M > 0:
+            k2 = kv_caches.meta_fattn_cache[0]
+            v2 = kv_caches.meta_fattn_cache[1]
+        return self.attn.forward(q1, k1, v1, query2=q2, key2=k2, value2=v2,
+                                 attn_metadata=attn_metadata)

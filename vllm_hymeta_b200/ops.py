@@ -41,10 +41,12 @@ def launch_count() -> int:
 def gla_decode(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, g: torch.Tensor,
                state: torch.Tensor, slot_idx: torch.Tensor, scale: Optional[float] = None,
                out: Optional[torch.Tensor] = None) -> torch.Tensor:
-    """q [B,H,D]; k,v,g [B,Hk,D]; state [slots,Hs,D,D] bf16 (updated in place);
+    """q [B,H,D]; k,g [B,Hk,D]; v [B,Hv,D]; state [slots,Hs,D,D] bf16 (updated in place);
     slot_idx [B] int32 (-1 = skip).  Returns o [B,H,D] bf16."""
     B, H, D = q.shape
-    Hk, Hs = k.shape[1], state.shape[1]
+    Hk, Hv, Hs = k.shape[1], v.shape[1], state.shape[1]
+    if g.shape[1] != Hk:
+        raise ValueError("g must have as many heads as k")
     for n, t in (("q", q), ("k", k), ("v", v), ("state", state)):
         _req(t, n, torch.bfloat16)
     _req(g, "g")
@@ -59,7 +61,7 @@ def gla_decode(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, g: torch.Tenso
         scale = D ** -0.5
     check(lib().hymeta_gla_decode(
         _ptr(q), _ptr(k), _ptr(v), _ptr(g), _ptr(out), _ptr(state), _ptr(slot_idx),
-        B, H, Hk, Hs, D, q.stride(0), q.stride(1), k.stride(0), k.stride(1), v.stride(0), v.stride(1),
+        B, H, Hk, Hv, Hs, D, q.stride(0), q.stride(1), k.stride(0), k.stride(1), v.stride(0), v.stride(1),
         g.stride(0), g.stride(1), out.stride(0), out.stride(1), state.stride(0), state.stride(1),
         int(g.dtype == torch.float32), float(scale), _stream()), "hymeta_gla_decode")
     return out
@@ -70,10 +72,12 @@ def gla_prefill_varlen(q, k, v, g, state, cu_seqlens, slot_idx, init_mode,
                        meta_state: Optional[torch.Tensor] = None, scale: Optional[float] = None,
                        write_state: bool = True, max_seqlen: Optional[int] = None,
                        out: Optional[torch.Tensor] = None) -> torch.Tensor:
-    """q [T,H,D]; k,v,g [T,Hk,D]; state [slots,Hs,D,D]; cu_seqlens [N+1], slot_idx [N],
+    """q [T,H,D]; k,g [T,Hk,D]; v [T,Hv,D]; state [slots,Hs,D,D]; cu_seqlens [N+1], slot_idx [N],
     init_mode [N] int32 device tensors.  Returns o [T,H,D] bf16; writes final states."""
     T, H, D = q.shape
-    Hk, Hs = k.shape[1], state.shape[1]
+    Hk, Hv, Hs = k.shape[1], v.shape[1], state.shape[1]
+    if g.shape[1] != Hk:
+        raise ValueError("g must have as many heads as k")
     N = cu_seqlens.numel() - 1
     for n, t in (("q", q), ("k", k), ("v", v), ("state", state)):
         _req(t, n, torch.bfloat16)
@@ -88,13 +92,60 @@ def gla_prefill_varlen(q, k, v, g, state, cu_seqlens, slot_idx, init_mode,
         scale = D ** -0.5
     check(lib().hymeta_gla_prefill_varlen(
         _ptr(q), _ptr(k), _ptr(v), _ptr(g), _ptr(out), _ptr(state), _ptr(meta_state),
-        _ptr(cu_seqlens), _ptr(slot_idx), _ptr(init_mode), N, T, H, Hk, Hs, D,
+        _ptr(cu_seqlens), _ptr(slot_idx), _ptr(init_mode), N, T, H, Hk, Hv, Hs, D,
         q.stride(0), q.stride(1), k.stride(0), k.stride(1), v.stride(0), v.stride(1),
         g.stride(0), g.stride(1), out.stride(0), out.stride(1), state.stride(0), state.stride(1),
         0 if meta_state is None else meta_state.stride(0),
         int(g.dtype == torch.float32), float(scale), int(write_state),
         int(max_seqlen if max_seqlen is not None else T), _stream()), "hymeta_gla_prefill_varlen")
     return out
+
+
+# ----------------------------------------------------------------------------------- a4
+def gla_gate_70b(q: torch.Tensor, k: torch.Tensor, lower_bound: Optional[torch.Tensor] = None,
+                 clamp_max: float = 0.95, inplace_q: bool = False):
+    """70B feature map + gate in one launch.  q [T,H,D], k [T,Hk,D] bf16 (strided views of the
+    qkv projection are fine).  ``lower_bound``: fp32 [Ho,D] rank-local slice or None.
+    Returns (relu(q) [T,H,D] bf16, k' [T,Ho,D] bf16, g [T,Ho,D] fp32), Ho = Hk without a lower
+    bound, else lower_bound.shape[0] (H in the reference)."""
+    T, H, D = q.shape
+    Hk = k.shape[1]
+    _req(q, "q", torch.bfloat16)
+    _req(k, "k", torch.bfloat16)
+    Ho = Hk
+    if lower_bound is not None:
+        _req(lower_bound, "lower_bound", torch.float32)
+        if not lower_bound.is_contiguous() or lower_bound.shape[-1] != D:
+            raise ValueError("lower_bound must be a contiguous fp32 [Ho, D] tensor")
+        Ho = lower_bound.numel() // D
+    q_out = q if inplace_q else torch.empty(T, H, D, dtype=q.dtype, device=q.device)
+    k_out = torch.empty(T, Ho, D, dtype=k.dtype, device=k.device)
+    g_out = torch.empty(T, Ho, D, dtype=torch.float32, device=k.device)
+    check(lib().hymeta_gla_gate_70b(
+        _ptr(q), _ptr(k), _ptr(q_out), _ptr(k_out), _ptr(g_out), _ptr(lower_bound), T, H, Hk, Ho, D,
+        q.stride(0), q.stride(1), k.stride(0), k.stride(1), q_out.stride(0), q_out.stride(1),
+        k_out.stride(0), k_out.stride(1), g_out.stride(0), g_out.stride(1), float(clamp_max),
+        _stream()), "hymeta_gla_gate_70b")
+    return q_out, k_out, g_out
+
+
+def gla_gate_7b(q: torch.Tensor, k: torch.Tensor, gk: torch.Tensor, normalizer: float = 16.0,
+                inplace: bool = False):
+    """7B feature map + gate in one launch.  q [T,H,D], k, gk [T,Hk,D] bf16.
+    Returns (relu(q), relu(k), logsigmoid(gk)/normalizer) all bf16."""
+    T, H, D = q.shape
+    Hk = k.shape[1]
+    for n, t in (("q", q), ("k", k), ("gk", gk)):
+        _req(t, n, torch.bfloat16)
+    q_out = q if inplace else torch.empty(T, H, D, dtype=q.dtype, device=q.device)
+    k_out = k if inplace else torch.empty(T, Hk, D, dtype=k.dtype, device=k.device)
+    g_out = gk if inplace else torch.empty(T, Hk, D, dtype=gk.dtype, device=gk.device)
+    check(lib().hymeta_gla_gate_7b(
+        _ptr(q), _ptr(k), _ptr(gk), _ptr(q_out), _ptr(k_out), _ptr(g_out), T, H, Hk, D,
+        q.stride(0), q.stride(1), k.stride(0), k.stride(1), gk.stride(0), gk.stride(1),
+        q_out.stride(0), q_out.stride(1), k_out.stride(0), k_out.stride(1),
+        g_out.stride(0), g_out.stride(1), float(normalizer), _stream()), "hymeta_gla_gate_7b")
+    return q_out, k_out, g_out
 
 
 # ----------------------------------------------------------------------------------- a9
