@@ -93,6 +93,28 @@ int hymeta_gla_prefill_varlen(const void* q, const void* k, const void* v, const
                               int64_t meta_sh, int g_is_fp32, float scale, int write_state,
                               int max_seqlen, void* stream);
 
+/* Sequence-parallel form of a3 for few long sequences (BASELINE configs 3 and 5): every sequence is
+ * cut into segments of seg_len tokens (a multiple of 16) that run as independent CTAs -- (1) each
+ * segment's local end state from a zero start plus its total decay, (2) a scan over the segments of
+ * each chain, (3) the outputs from the scanned start states.  Same results as the single-pass
+ * form up to fp32 re-association of the state.  seg_len == 0 (or max_seqlen <= seg_len) is the
+ * single-pass form and needs no workspace.  The fla kernel the reference calls is sequential per
+ * (request, head) (modeling_hymeta.py:512-513); the caller owns the fp32 workspace of
+ * hymeta_gla_prefill_workspace_bytes(N, Hs, max_seqlen, seg_len) bytes (16-byte aligned).
+ * k/g/v strides must be multiples of 8 elements (TMA). */
+size_t hymeta_gla_prefill_workspace_bytes(int N, int Hs, int max_seqlen, int seg_len);
+int hymeta_gla_prefill_varlen_seg(const void* q, const void* k, const void* v, const void* g,
+                                  void* o, void* state, const void* meta_state,
+                                  const int32_t* cu_seqlens, const int32_t* slot_idx,
+                                  const int32_t* init_mode,
+                                  int N, int T, int H, int Hk, int Hv, int Hs, int D,
+                                  int64_t q_st, int64_t q_sh, int64_t k_st, int64_t k_sh,
+                                  int64_t v_st, int64_t v_sh, int64_t g_st, int64_t g_sh,
+                                  int64_t o_st, int64_t o_sh, int64_t st_ss, int64_t st_sh,
+                                  int64_t meta_sh, int g_is_fp32, float scale, int write_state,
+                                  int max_seqlen, int seg_len, void* workspace,
+                                  size_t workspace_bytes, void* stream);
+
 /* ------------------------------------------------------------------------------------------------
  * a4  GLA feature map + gate pre-processing -- replaces the eager torch elementwise chain between
  *     qkv_proj and the GLA kernels:

@@ -17,7 +17,7 @@ def ops():
 
 
 def run_case(ops, lens, H, Hkv, model, layout, seed, modes=None, slots=None, write_state=True,
-             g_override=None):
+             g_override=None, seg_len=0):
     D = 128
     T = sum(lens)
     q, k, v, g = ogla.synth_gla_inputs(T, H, Hkv, D, model, seed=seed)
@@ -43,7 +43,7 @@ def run_case(ops, lens, H, Hkv, model, layout, seed, modes=None, slots=None, wri
     i32 = lambda x: torch.tensor(x, dtype=torch.int32, device=DEV)
     o = ops.gla_prefill_varlen(q.to(DEV), k.to(DEV), v.to(DEV), g.to(DEV), d_state, i32(cu),
                                i32(slots), i32(modes), meta.to(DEV), write_state=write_state,
-                               max_seqlen=max(lens))
+                               max_seqlen=max(lens), seg_len=seg_len)
     torch.cuda.synchronize()
     assert_close(o, ref_o, f"gla prefill o {lens} {model} {layout}")
     assert_close(d_state, ref_state, f"gla prefill state {lens} {model} {layout}")
@@ -95,14 +95,42 @@ def test_long_sequence_and_prefill_decode_consistency(ops):
     ref_o, ref_S = ogla.gla_chunked(q, k, v, g, chunk=16)
     dq, dk, dv, dg = (x.to(DEV) for x in (q, k, v, g))
     i32 = lambda x: torch.tensor(x, dtype=torch.int32, device=DEV)
-    st = torch.zeros(2, Hkv, D, D, dtype=torch.bfloat16, device=DEV)
-    o = ops.gla_prefill_varlen(dq, dk, dv, dg, st, i32([0, T]), i32([0]), i32([0]))
-    assert_close(o, ref_o, "long o")
-    assert_close(st[0], ref_S[::H // Hkv], "long state")
-    o2 = ops.gla_prefill_varlen(dq[:T - 8], dk[:T - 8], dv[:T - 8], dg[:T - 8], st,
-                                i32([0, T - 8]), i32([1]), i32([0]))
-    tail = [ops.gla_decode(dq[t:t + 1], dk[t:t + 1], dv[t:t + 1], dg[t:t + 1], st, i32([1]))
-            for t in range(T - 8, T)]
-    assert torch.equal(o2, o[:T - 8])
-    assert_close(torch.cat(tail), ref_o[T - 8:], "decode tail")
-    assert_close(st[1], st[0].float(), "state after prefill+decode", maxabs_frac=2.0 ** -6, rel_rms=1e-2)
+    # the prefix property is bit-exact whenever both runs cut the sequence at the same places:
+    # single pass (seg_len 0) and a fixed segment length
+    for seg_len in (0, 512):
+        st = torch.zeros(2, Hkv, D, D, dtype=torch.bfloat16, device=DEV)
+        o = ops.gla_prefill_varlen(dq, dk, dv, dg, st, i32([0, T]), i32([0]), i32([0]), seg_len=seg_len)
+        assert_close(o, ref_o, "long o")
+        assert_close(st[0], ref_S[::H // Hkv], "long state")
+        o2 = ops.gla_prefill_varlen(dq[:T - 8], dk[:T - 8], dv[:T - 8], dg[:T - 8], st,
+                                    i32([0, T - 8]), i32([1]), i32([0]), seg_len=seg_len)
+        tail = [ops.gla_decode(dq[t:t + 1], dk[t:t + 1], dv[t:t + 1], dg[t:t + 1], st, i32([1]))
+                for t in range(T - 8, T)]
+        assert torch.equal(o2, o[:T - 8])
+        assert_close(torch.cat(tail), ref_o[T - 8:], "decode tail")
+        assert_close(st[1], st[0].float(), "state after prefill+decode", maxabs_frac=2.0 ** -6, rel_rms=1e-2)
+
+
+@pytest.mark.parametrize("model", ["7b", "70b"])
+def test_segmented_matches_oracle(ops, model):
+    """Sequence-parallel form (summaries -> scan -> outputs): ragged lengths around the segment size,
+    every init mode, a PAD slot and a sequence shorter than one segment."""
+    run_case(ops, [700, 130, 1000, 256, 257, 1], 28, 4, model, "compact", 11, seg_len=256,
+             modes=[1, 2, 0, 1, 2, 1], slots=[3, 0, -1, 5, 1, 2])
+
+
+def test_segmented_equals_single_pass(ops):
+    o1, s1 = run_case(ops, [2048], 7, 1, "70b", "compact", 12, modes=[2], seg_len=0)
+    o2, s2 = run_case(ops, [2048], 7, 1, "70b", "compact", 12, modes=[2], seg_len=128)
+    o3, s3 = run_case(ops, [2048], 7, 1, "70b", "compact", 12, modes=[2], seg_len=None)   # auto
+    for o, s in ((o2, s2), (o3, s3)):
+        assert (o.float() - o1.float()).abs().max().item() <= 2 ** -6 * o1.float().abs().max().item()
+        assert (s.float() - s1.float()).abs().max().item() <= 2 ** -6 * s1.float().abs().max().item()
+
+
+def test_seg_len_heuristic():
+    from vllm_hymeta_b200 import ops as o
+    assert o.gla_prefill_seg_len(256, 8192) == 0            # full waves: single pass
+    assert o.gla_prefill_seg_len(4, 300) == 0               # too short to cut
+    s = o.gla_prefill_seg_len(1, 32768)
+    assert s > 0 and s % 16 == 0 and 32768 // s >= 64

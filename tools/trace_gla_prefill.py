@@ -17,8 +17,8 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 CSRC = os.path.join(ROOT, "vllm_hymeta_b200", "csrc")
 TRACE_LIB = os.path.join(CSRC, "build", "libhymeta_b200_trace.so")
-EV = ["gate_kf", "v_kf", "st_wake", "st_x", "q_top", "q_qf", "q_a", "q_p", "q_o", "is_top", "is_x",
-      "is_wp", "is_p", "is_end", "st_ld0", "st_st0"]
+EV = ["gate_kf", "v_kf", "g_cum", "st_x", "q_top", "q_qf", "q_a", "q_p", "q_o", "is_top", "is_x",
+      "is_wp", "is_p", "is_end", "g_land", "g_top"]
 
 
 def build(exp=0):
@@ -93,8 +93,9 @@ def main():
     d = lambda i, e: int(tr[i][e])
     print("avg cycles:")
     print(f"  step period (is_x(i+1)-is_x(i))      {avg(lambda i: d(i + 1, 10) - d(i, 10)):8.0f}")
-    print(f"  is_x -> st_wake (Y MMA + commit)      {avg(lambda i: d(i, 2) - d(i, 10)):8.0f}")
-    print(f"  st_wake -> st_x (rescale pass)        {avg(lambda i: d(i, 3) - d(i, 2)):8.0f}")
+    print(f"  gates: top -> raw landed             {avg(lambda i: d(i, 14) - d(i, 15)):8.0f}")
+    print(f"  gates: landed -> cumsum done          {avg(lambda i: d(i, 2) - d(i, 14)):8.0f}")
+    print(f"  gates: cumsum -> kf arrive (ke wait + writes) {avg(lambda i: d(i, 0) - d(i, 2)):8.0f}")
     print(f"  st_x(i) -> is_x(i+1)                  {avg(lambda i: d(i + 1, 10) - d(i, 3)):8.0f}")
     print(f"  is_top -> is_x wait                   {avg(lambda i: d(i, 10) - d(i, 9)):8.0f}")
     print(f"  is_wp -> is_p wait                    {avg(lambda i: d(i, 12) - d(i, 11)):8.0f}")

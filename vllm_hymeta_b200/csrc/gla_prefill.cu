@@ -36,9 +36,14 @@ constexpr int GP_ST_V = 4096;                   //   v  [2][16][64] bf16        
 constexpr int GP_ST_F = 8192;                   //   scale*exp(b_t - r) [16][128] f32    8 KB
 constexpr int GP_ST_D = 16384;                  //   exp(b_15 - r) [128], exp(r) [128]   1 KB
 constexpr int GP_STAGE = 17408;
-constexpr int GP_BAR = GP_ST + GP_KS * GP_STAGE;
+constexpr int GP_RAW = GP_ST + GP_KS * GP_STAGE;   // raw g / k ring of the gate warps (cp.async)
+constexpr int GP_RS = 2;                        //   stages
+constexpr int GP_RAW_K = 8192;                  //   g [16][64 thr] 4|8 B (8 KB), k [16][64 thr] 4 B (4 KB)
+constexpr int GP_RAW_STAGE = 12288;
+constexpr int GP_BAR = GP_RAW + GP_RS * GP_RAW_STAGE;
 constexpr int GP_SMEM = GP_BAR + 256;
 constexpr int GP_THREADS = 512;
+constexpr int GP_WS_ELEMS = kD * kD + kD;      // per (chain, segment): state [128][128] + decay [128]
 
 struct GlaPrefillParams {
   const __nv_bfloat16 *q, *k, *v;
@@ -47,6 +52,8 @@ struct GlaPrefillParams {
   const __nv_bfloat16* meta_state;
   const int32_t *cu, *slot, *init_mode;
   int N, H, Hk, Hv, Hs, write_state;
+  int seg_len, n_segs, pass;   // sequence segments (0: whole sequences); pass 1 = segment summaries, 3 = outputs
+  float* ws;                   // [N*Hs][n_segs][GP_WS_ELEMS] fp32: local end state + total decay per segment
   float scale;
   int64_t q_st, q_sh, k_st, k_sh, v_st, v_sh, g_st, g_sh, o_st, o_sh, st_ss, st_sh, meta_sh;
 };
@@ -69,20 +76,35 @@ __device__ long long* g_gla_trace = nullptr;   // [steps][16] clock64 stamps of 
 #endif
 
 template <bool GF32>
-__global__ void __launch_bounds__(GP_THREADS, 1) gla_prefill_kernel(const GlaPrefillParams p) {
+__global__ void __launch_bounds__(GP_THREADS, 1)
+gla_prefill_kernel(const GlaPrefillParams p, const __grid_constant__ CUtensorMap tmG,
+                   const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV) {
   extern __shared__ __align__(1024) uint8_t smem[];
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);   // warp-uniform for the compiler
   const int hs = blockIdx.x, n = blockIdx.y;
   const int G = p.H / p.Hs, h0 = hs * G, hk = hs / (p.Hs / p.Hk), hv = hs / (p.Hs / p.Hv);
-  const int tok_begin = p.cu[n], len = p.cu[n + 1] - tok_begin;
+  const int seq_begin = p.cu[n], seq_len = p.cu[n + 1] - seq_begin;
   const int slot = p.slot[n], mode = p.init_mode[n];
+  // segment [seg0, seg0 + len) of the sequence (the whole sequence when seg_len == 0)
+  const int seg = blockIdx.z, seg0 = seg * p.seg_len;
+  const bool summary = p.pass == 1;
+  if (seg > 0 && seg0 >= seq_len) return;
+  const bool last_seg = p.seg_len == 0 || seg0 + p.seg_len >= seq_len;
+  if (summary && last_seg) return;               // nothing follows: no summary needed
+  const int tok_begin = seq_begin + seg0, len = last_seg ? seq_len - seg0 : p.seg_len;
   const int n_steps = (len + GC - 1) / GC;
+  float* ws_out = summary ? p.ws + ((int64_t)(n * p.Hs + hs) * p.n_segs + seg) * GP_WS_ELEMS : nullptr;
+  const float* ws_in = (p.pass == 3 && seg > 0)
+      ? p.ws + ((int64_t)(n * p.Hs + hs) * p.n_segs + seg - 1) * GP_WS_ELEMS : nullptr;
 
   const __nv_bfloat16* init_src = nullptr;
-  if (mode == 1 && slot >= 0) init_src = p.state + (int64_t)slot * p.st_ss + (int64_t)hs * p.st_sh;
-  else if (mode == 2 && p.meta_state) init_src = p.meta_state + (int64_t)hs * p.meta_sh;
-  __nv_bfloat16* final_dst =
-      (p.write_state && slot >= 0) ? p.state + (int64_t)slot * p.st_ss + (int64_t)hs * p.st_sh : nullptr;
+  if (!summary && seg == 0) {
+    if (mode == 1 && slot >= 0) init_src = p.state + (int64_t)slot * p.st_ss + (int64_t)hs * p.st_sh;
+    else if (mode == 2 && p.meta_state) init_src = p.meta_state + (int64_t)hs * p.meta_sh;
+  }
+  __nv_bfloat16* final_dst = (!summary && last_seg && p.write_state && slot >= 0)
+      ? p.state + (int64_t)slot * p.st_ss + (int64_t)hs * p.st_sh : nullptr;
 
   if (n_steps == 0) {   // empty sequence: the slot receives the initial state unchanged
     if (final_dst && final_dst != init_src && warp >= 4 && warp < 8) {
@@ -102,17 +124,18 @@ __global__ void __launch_bounds__(GP_THREADS, 1) gla_prefill_kernel(const GlaPre
   const uint32_t bars = sbase + GP_BAR;
   const uint32_t bar_kf = bars, bar_ke = bar_kf + 8 * GP_KS, bar_qf = bar_ke + 8 * GP_KS,
                  bar_a = bar_qf + 16, bar_p = bar_a + 16, bar_o = bar_p + 16, bar_x = bar_o + 16,
-                 bar_s = bar_x + 8;
+                 bar_xf = bar_x + 16, bar_raw = bar_xf + 16;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + GP_BAR + 200);
 
   if (tid == 0) {
     if (sbase & 1023) asm volatile("trap;");
-    for (int s = 0; s < GP_KS; ++s) { mbar_init(bar_kf + 8 * s, 96); mbar_init(bar_ke + 8 * s, 257); }
+    for (int s = 0; s < GP_KS; ++s) { mbar_init(bar_kf + 8 * s, 64); mbar_init(bar_ke + 8 * s, summary ? 128 : 257); }
     for (int i = 0; i < 2; ++i) {
       mbar_init(bar_qf + 8 * i, 128); mbar_init(bar_a + 8 * i, 1);
       mbar_init(bar_p + 8 * i, 128);  mbar_init(bar_o + 8 * i, 1);
     }
-    mbar_init(bar_x, 128); mbar_init(bar_s, 1);
+    mbar_init(bar_x, 128); mbar_init(bar_x + 8, 128); mbar_init(bar_xf, 1); mbar_init(bar_xf + 8, 1);
+    for (int s = 0; s < GP_RS; ++s) mbar_init(bar_raw + 8 * s, 1);
     fence_mbar_init();
   }
   if (warp == 2) tmem_alloc<512>(smem_u32(tmem_slot));
@@ -120,162 +143,287 @@ __global__ void __launch_bounds__(GP_THREADS, 1) gla_prefill_kernel(const GlaPre
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
-  // TMEM columns: X/Y [0,128)  O0 [128,256)  O1 [256,384)  A0 [384,400)  A1 [400,416); P_i aliases A_i
-  const uint32_t tX = tmem, tO = tmem + 128, tA = tmem + 384;
+  // TMEM columns: O0 [0,128)  O1 [128,256)  A0 [256,272)  A1 [272,288); P_i aliases A_i
+  const uint32_t tO = tmem, tA = tmem + 256;
 
-  if (warp < 2) {
+  // 512 threads x 128 registers at launch; the state warpgroup takes what the others give up
+  if (warp < 4) {
+   setmaxnreg_dec<80>();
+   if (warp < 2) {
     // ================================================================== gates (thread = 2 channels)
     // Straight-line code is kept small on purpose: five roles share the SM's instruction cache.
     const int c = 2 * tid;
     constexpr int GB = GF32 ? 4 : 2;
-    const char* gp = reinterpret_cast<const char*>(p.g) + ((int64_t)tok_begin * p.g_st + (int64_t)hk * p.g_sh + c) * GB;
-    const char* kp = reinterpret_cast<const char*>(p.k + (int64_t)tok_begin * p.k_st + (int64_t)hk * p.k_sh + c);
-    const int64_t gstep = p.g_st * GB, kstep = p.k_st * 2;
     const uint32_t kbase = (uint32_t)((c >> 6) * 2048 + (c & 7) * 2), kcx = (uint32_t)((c >> 3) & 7);
     const float lscale = __log2f(p.scale);
-    float2 g[GC];
-    uint32_t kk[GC];
-    for (int i = -1; i < n_steps; ++i) {
-      if (i >= 0) {
-        const int st = i % GP_KS, clen = len - i * GC;
-        uint8_t* stage = smem + GP_ST + st * GP_STAGE;
-        // cumulative gates in the log2 domain; padded tokens (t >= clen) do not decay
-        float2 b[GC];
-        float bx = 0.f, by = 0.f;
-#pragma unroll
-        for (int t = 0; t < GC; ++t) {
-          if (t < clen) { bx = fmaf(g[t].x, 1.4426950408889634f, bx); by = fmaf(g[t].y, 1.4426950408889634f, by); }
-          b[t] = make_float2(bx, by);
-        }
-        const float2 r = b[GC / 2 - 1];
-        const float rfx = r.x - lscale, rfy = r.y - lscale;
-        if (i >= GP_KS) mbar_wait(bar_ke + 8 * st, ((i / GP_KS) - 1) & 1);
-        uint8_t* sF = stage + GP_ST_F + c * 4;
-        uint8_t* sK = stage + GP_ST_K + kbase;
-#pragma unroll
-        for (int t = 0; t < GC; ++t) {
-          *reinterpret_cast<float2*>(sF + t * (kD * 4)) = make_float2(exp2f(b[t].x - rfx), exp2f(b[t].y - rfy));
-          *reinterpret_cast<uint32_t*>(sK + t * 128 + ((kcx ^ (t & 7)) << 4)) =
-              pack_bf16(bf16_lo(kk[t]) * exp2f(r.x - b[t].x), bf16_hi(kk[t]) * exp2f(r.y - b[t].y));
-        }
-        float* sD = reinterpret_cast<float*>(stage + GP_ST_D);
-        *reinterpret_cast<float2*>(sD + c) = make_float2(exp2f(b[GC - 1].x - r.x), exp2f(b[GC - 1].y - r.y));
-        *reinterpret_cast<float2*>(sD + kD + c) = make_float2(exp2f(r.x), exp2f(r.y));
-        fence_proxy_async_smem();
-        mbar_arrive(bar_kf + 8 * st);
-        if (tid == 0) GP_TRACE(i, 0);
+    // raw g / k of the next GP_RS steps are TMA-loaded into a small ring ([16][128] rows, no swizzle)
+    // and v straight into its SWIZZLE_128B stage tile: no load instructions in this role
+    constexpr uint32_t RAW_BYTES = GC * kD * (GB + 2);
+    const uint8_t* rawp = smem + GP_RAW + c * GB;
+    const uint8_t* rawkp = smem + GP_RAW + GP_RAW_K + c * 2;
+    auto fetch = [&](int i) {
+      if (i < n_steps && tid == 0) {
+        const uint32_t bar = bar_raw + 8 * (i % GP_RS), dst = sbase + GP_RAW + (i % GP_RS) * GP_RAW_STAGE;
+        mbar_expect_tx(bar, RAW_BYTES);
+        tma_load_3d(dst, &tmG, bar, 0, hk, tok_begin + i * GC);
+        tma_load_3d(dst + GP_RAW_K, &tmK, bar, 0, hk, tok_begin + i * GC);
       }
-      if (i + 1 < n_steps) {   // next step's raw gates / keys: rows past the sequence end re-read its last token
-        const int base = (i + 1) * GC;
+    };
+    if (tid == 0) { tma_prefetch_desc(&tmG); tma_prefetch_desc(&tmK); tma_prefetch_desc(&tmV); }
 #pragma unroll
-        for (int t = 0; t < GC; ++t) {
-          const int64_t tt = min(base + t, len - 1);
-          if (GF32) g[t] = *reinterpret_cast<const float2*>(gp + tt * gstep);
-          else {
-            const uint32_t u = *reinterpret_cast<const uint32_t*>(gp + tt * gstep);
-            g[t] = make_float2(bf16_lo(u), bf16_hi(u));
+    for (int i = 0; i < GP_RS; ++i) fetch(i);
+    for (int i = 0; i < n_steps; ++i) {
+      const int st = i % GP_KS, clen = len - i * GC;
+      const uint32_t so = (uint32_t)((i % GP_RS) * GP_RAW_STAGE);
+      uint8_t* stage = smem + GP_ST + st * GP_STAGE;
+      if (tid == 0) GP_TRACE(i, 15);
+      mbar_wait(bar_raw + 8 * (i % GP_RS), (i / GP_RS) & 1);
+      if (tid == 0) GP_TRACE(i, 14);
+      // cumulative gates in the log2 domain; rows past the sequence end (t >= clen) hold another
+      // sequence's tokens: they neither decay nor contribute (k~ = 0)
+      float2 b[GC];
+      uint32_t kk[GC];
+      float bx = 0.f, by = 0.f;
+#pragma unroll
+      for (int t = 0; t < GC; ++t) {
+        float2 g;
+        if (GF32) g = *reinterpret_cast<const float2*>(rawp + so + t * 512);
+        else {
+          const uint32_t u = *reinterpret_cast<const uint32_t*>(rawp + so + t * 256);
+          g = make_float2(bf16_lo(u), bf16_hi(u));
+        }
+        kk[t] = *reinterpret_cast<const uint32_t*>(rawkp + so + t * 256);
+        if (t < clen) { bx = fmaf(g.x, 1.4426950408889634f, bx); by = fmaf(g.y, 1.4426950408889634f, by); }
+        else kk[t] = 0;
+        b[t] = make_float2(bx, by);
+      }
+      asm volatile("bar.sync 1, 64;" ::: "memory");   // both gate warps are done with the raw slot
+      fetch(i + GP_RS);
+      const float2 r = b[GC / 2 - 1];
+      const float rfx = r.x - lscale, rfy = r.y - lscale;
+      if (tid == 0) GP_TRACE(i, 2);
+      if (i >= GP_KS) mbar_wait(bar_ke + 8 * st, ((i / GP_KS) - 1) & 1);
+      if (clen >= GC) {
+        if (tid == 0) {
+          const uint32_t dst = sT + st * GP_STAGE + GP_ST_V;
+          mbar_expect_tx_only(bar_kf + 8 * st, GC * kD * 2);
+          tma_load_3d(dst, &tmV, bar_kf + 8 * st, 0, hv, tok_begin + i * GC);
+          tma_load_3d(dst + 2048, &tmV, bar_kf + 8 * st, 64, hv, tok_begin + i * GC);
+        }
+      } else {   // ragged last step: copy by hand, zero rows past the sequence end
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const int id = tid + 64 * j, t = id >> 4, vc = id & 15;
+          uint4 x = make_uint4(0, 0, 0, 0);
+          if (t < clen) x = ldg_nc_v4(p.v + (int64_t)(tok_begin + i * GC + t) * p.v_st + (int64_t)hv * p.v_sh + vc * 8);
+          *reinterpret_cast<uint4*>(stage + GP_ST_V + (vc >> 3) * 2048 + sw128_chunk(t, vc & 7)) = x;
+        }
+      }
+      uint8_t* sF = stage + GP_ST_F + c * 4;
+      uint8_t* sK = stage + GP_ST_K + kbase;
+#pragma unroll
+      for (int t = 0; t < GC; ++t) {
+        *reinterpret_cast<float2*>(sF + t * (kD * 4)) = make_float2(exp2f(b[t].x - rfx), exp2f(b[t].y - rfy));
+        *reinterpret_cast<uint32_t*>(sK + t * 128 + ((kcx ^ (t & 7)) << 4)) =
+            pack_bf16(bf16_lo(kk[t]) * exp2f(r.x - b[t].x), bf16_hi(kk[t]) * exp2f(r.y - b[t].y));
+      }
+      float* sD = reinterpret_cast<float*>(stage + GP_ST_D);
+      *reinterpret_cast<float2*>(sD + c) = make_float2(exp2f(b[GC - 1].x - r.x), exp2f(b[GC - 1].y - r.y));
+      *reinterpret_cast<float2*>(sD + kD + c) = make_float2(exp2f(r.x), exp2f(r.y));
+      fence_proxy_async_smem();
+      mbar_arrive(bar_kf + 8 * st);
+      if (tid == 0) GP_TRACE(i, 0);
+    }
+   } else if (warp == 3) {
+    // idle: g / k / v arrive by TMA
+   } else {
+    // ================================================================== MMA issuer
+    if (!summary && elect_one_sync()) {
+      const uint32_t idesc_a = umma_idesc_bf16(128, 16, 0, 0);
+      const uint32_t idesc_o = umma_idesc_bf16(128, 128, 0, 1);
+      // descriptors differ from these templates only in the 16-byte-granular start address
+      const uint64_t dk = umma_desc_sw128(0, 16, 1024);          // K-major tiles (q~, k~ as B of A)
+      const uint64_t dmn = umma_desc_sw128(0, 2048, 1024);       // MN-major 16-row tiles (k~ as A of Y, v)
+      const uint64_t dx = umma_desc_sw128(0, 16384, 1024);       // MN-major X (two 64-wide halves)
+      auto issue_a = [&](int i) {                   // A = q~ k~^T
+        const int w = i & 1;
+        const uint32_t qb = (sQ + w * 32768) >> 4, kb = (sT + (i % GP_KS) * GP_STAGE + GP_ST_K) >> 4;
+#pragma unroll 1
+        for (int ks = 0; ks < 8; ++ks)
+          umma_bf16(tA + 16 * w, dk + qb + (ks >> 2) * 1024 + (ks & 3) * 2, dk + kb + (ks >> 2) * 128 + (ks & 3) * 2,
+                    idesc_a, ks > 0);
+        umma_commit(bar_a + 8 * w);
+      };
+      mbar_wait(bar_kf, 0);
+      mbar_wait(bar_qf, 0);
+      tc_fence_after();
+      issue_a(0);
+      for (int i = 0; i < n_steps; ++i) {
+        const int w = i & 1, st = i % GP_KS;
+        const uint32_t vb = (sT + st * GP_STAGE + GP_ST_V) >> 4;
+        GP_TRACE(i, 9);
+        mbar_wait(bar_x + 8 * w, (i >> 1) & 1);
+        tc_fence_after();
+        GP_TRACE(i, 10);
+        {                                                // O = q~ X
+          const uint32_t qb = (sQ + w * 32768) >> 4, xb = (sS + w * 32768) >> 4;
+#pragma unroll 1
+          for (int ks = 0; ks < 8; ++ks)
+            umma_bf16(tO + 128 * w, dk + qb + (ks >> 2) * 1024 + (ks & 3) * 2, dx + xb + ks * 128, idesc_o, ks > 0);
+          umma_commit(bar_xf + 8 * w);                   // X buffer w free once these complete
+        }
+        // A(i+1) goes ahead of P v (i) only when its operands are already there; otherwise P v (i)
+        // and the epilogue behind it are not held up by the next tile's builder
+        bool a_done = i + 1 >= n_steps;
+        if (!a_done && mbar_test(bar_qf + 8 * (w ^ 1), ((i + 1) >> 1) & 1) &&
+            mbar_test(bar_kf + 8 * ((i + 1) % GP_KS), ((i + 1) / GP_KS) & 1)) {
+          tc_fence_after();
+          issue_a(i + 1);
+          a_done = true;
+        }
+        GP_TRACE(i, 11);
+        mbar_wait(bar_p + 8 * w, (i >> 1) & 1);
+        tc_fence_after();
+        GP_TRACE(i, 12);
+        umma_bf16_ts(tO + 128 * w, tA + 16 * w, dmn + vb, idesc_o, 1);   // O += P v
+        umma_commit(bar_o + 8 * w);
+        umma_commit(bar_ke + 8 * st);                    // k~, v of step i consumed
+        if (!a_done) {
+          mbar_wait(bar_kf + 8 * ((i + 1) % GP_KS), ((i + 1) / GP_KS) & 1);
+          mbar_wait(bar_qf + 8 * (w ^ 1), ((i + 1) >> 1) & 1);
+          tc_fence_after();
+          issue_a(i + 1);
+        }
+        GP_TRACE(i, 13);
+      }
+    }
+    __syncwarp();
+   }
+  } else if (warp < 8) {
+    setmaxnreg_inc<208>();
+    // ================================================================== state (fp32 master in registers)
+    // TMEM -> register traffic is 64 B/clk per SM and the O epilogue already needs most of it, so the
+    // state never enters TMEM: Y = X + k~^T v runs on mma.sync with the accumulator fragments as the
+    // master (warp = 32 d_k rows x 128 d_v), is rescaled in registers and its bf16 copy goes to smem.
+    // The chain needs only the gate ring and a free X buffer, so it runs ahead of the MMA issuer.
+    const int ws = warp - 4, gid = lane >> 2, tig = lane & 3;
+    const int row0 = 32 * ws + gid;                 // rows row0 + 8j, j = 0..3 (m-tile j>>1, half j&1)
+    float S[2][16][4];
+    float Ptot[4] = {1.f, 1.f, 1.f, 1.f};            // total decay of the segment (summary pass)
+#pragma unroll
+    for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+      for (int nt = 0; nt < 16; ++nt)
+#pragma unroll
+        for (int hf = 0; hf < 2; ++hf) {
+          const int off = (row0 + 16 * mt + 8 * hf) * kD + 8 * nt + 2 * tig;
+          if (ws_in) {
+            const float2 f = *reinterpret_cast<const float2*>(ws_in + off);
+            S[mt][nt][2 * hf] = f.x; S[mt][nt][2 * hf + 1] = f.y;
+          } else {
+            uint32_t u = 0;
+            if (init_src) u = *reinterpret_cast<const uint32_t*>(init_src + off);
+            S[mt][nt][2 * hf] = bf16_lo(u); S[mt][nt][2 * hf + 1] = bf16_hi(u);
           }
-          kk[t] = *reinterpret_cast<const uint32_t*>(kp + tt * kstep);
         }
-      }
-    }
-  } else if (warp == 3) {
-    // ================================================================== v loader (one warp)
-    const int vc = lane & 15, vt = lane >> 4;       // 16-byte chunk vc of tokens vt + 2j
-    const __nv_bfloat16* vp = p.v + (int64_t)(tok_begin + vt) * p.v_st + (int64_t)hv * p.v_sh + vc * 8;
-    const uint32_t voff = (uint32_t)(GP_ST_V + (vc >> 3) * 2048 + vt * 128);
-    uint4 x[8];
-    for (int i = -1; i < n_steps; ++i) {
-      if (i >= 0) {
-        const int st = i % GP_KS;
-        uint8_t* sv = smem + GP_ST + st * GP_STAGE + voff;
-        if (i >= GP_KS) mbar_wait(bar_ke + 8 * st, ((i / GP_KS) - 1) & 1);
-#pragma unroll
-        for (int j = 0; j < 8; ++j)   // row vt + 2j: 16-byte slot (vc ^ row) & 7
-          *reinterpret_cast<uint4*>(sv + j * 256 + (((vc ^ (vt + 2 * j)) & 7) << 4)) = x[j];
-        fence_proxy_async_smem();
-        mbar_arrive(bar_kf + 8 * st);
-        if (lane == 0) GP_TRACE(i, 1);
-      }
-      if (i + 1 < n_steps) {
-        const int rem = len - (i + 1) * GC - vt;    // tokens vt + 2j < clen
-        const __nv_bfloat16* src = vp + (int64_t)(i + 1) * GC * p.v_st;
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          x[j] = make_uint4(0, 0, 0, 0);
-          if (2 * j < rem) x[j] = ldg_nc_v4(src + (int64_t)(2 * j) * p.v_st);
-        }
-      }
-    }
-  } else if (warp >= 4 && warp < 8) {
-    // ================================================================== state (thread = d_k row)
-    // pass i = -1 loads S_init and scales it into the first step's frame; pass i >= 0 rescales Y_i
-    // into the next frame; the last pass stores the final state.  One copy of the 32-column body.
-    const int d = tid - 128;
-    const uint32_t lane_off = (uint32_t)((warp & 3) * 32) << 16;
-    const float* sD0 = reinterpret_cast<const float*>(smem + GP_ST + GP_ST_D) + d;
-    const __nv_bfloat16* src = init_src ? init_src + d * kD : nullptr;
-    __nv_bfloat16* dst = final_dst ? final_dst + d * kD : nullptr;
-    const uint32_t srow = (uint32_t)(GP_SS + d * 128), sx = (uint32_t)(d & 7);
+    // ldmatrix row addresses inside a stage (k~ / v tiles: [2 halves][16 tokens][64] SWIZZLE_128B)
+    const int lt = (lane & 7) + 8 * ((lane >> 4) & 1);          // A: token row, d_k block (lane>>3)&1
+    const uint32_t a_row = (uint32_t)(lt * 128), a_x = (uint32_t)(lt & 7);
+    const int a_blk = 4 * ws + ((lane >> 3) & 1);               // 8-wide d_k block of m-tile 0 (+2 for m-tile 1)
+    const int bt = (lane & 7) + 8 * ((lane >> 3) & 1);          // B: token row, d_v block pair lane>>4
+    const uint32_t b_row = (uint32_t)(bt * 128), b_x = (uint32_t)(bt & 7);
+    const float* sD0 = reinterpret_cast<const float*>(smem + GP_ST + GP_ST_D);
     for (int i = -1; i < n_steps; ++i) {
       const bool first = i < 0, last = i + 1 == n_steps;
-      float D = first ? 1.f : sD0[(i % GP_KS) * (GP_STAGE / 4)];
+      if (!first) {
+        const uint32_t stg = sT + (i % GP_KS) * GP_STAGE;      // kf(i) was awaited in pass i-1
+        uint32_t af[2][4];
+#pragma unroll
+        for (int mt = 0; mt < 2; ++mt) {
+          const int blk = a_blk + 2 * mt;                       // 0..15
+          ldmatrix_x4_trans(af[mt][0], af[mt][1], af[mt][2], af[mt][3],
+                            stg + GP_ST_K + (blk >> 3) * 2048 + a_row + ((((uint32_t)blk & 7) ^ a_x) << 4));
+        }
+#pragma unroll
+        for (int np = 0; np < 8; ++np) {                        // d_v blocks 2np, 2np+1
+          const int blk = 2 * np + (lane >> 4);
+          uint32_t b0, b1, b2, b3;
+          ldmatrix_x4_trans(b0, b1, b2, b3,
+                            stg + GP_ST_V + (blk >> 3) * 2048 + b_row + ((((uint32_t)blk & 7) ^ b_x) << 4));
+#pragma unroll
+          for (int mt = 0; mt < 2; ++mt) {
+            mma_bf16_16816(S[mt][2 * np], af[mt], b0, b1);
+            mma_bf16_16816(S[mt][2 * np + 1], af[mt], b2, b3);
+          }
+        }
+      }
+      float D[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) D[j] = first ? 1.f : sD0[(i % GP_KS) * (GP_STAGE / 4) + row0 + 8 * j];
       if (!last) {
         const int sn = (i + 1) % GP_KS;
         mbar_wait(bar_kf + 8 * sn, ((i + 1) / GP_KS) & 1);
-        D *= sD0[sn * (GP_STAGE / 4) + kD];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) D[j] *= sD0[sn * (GP_STAGE / 4) + kD + row0 + 8 * j];
       }
-      if (!first) {
-        mbar_wait(bar_s, i & 1);   // Y_i complete; every earlier MMA (incl. q~ X of step i-1) too
-        tc_fence_after();
-        if (d == 0) GP_TRACE(i, 2);
-      }
-      if (!last || dst) {
-        uint8_t* sdst = smem + srow + ((i + 1) & 1) * 32768;
-#pragma unroll 1
-        for (int cc = 0; cc < 4; ++cc) {
-          uint32_t x[32];
-          if (first) {
+      if (!first) mbar_arrive(bar_ke + 8 * (i % GP_KS));        // k~, v, D of step i consumed
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              uint4 t = make_uint4(0, 0, 0, 0);
-              if (src) t = ldg_v4(src + 32 * cc + 8 * j);
-              x[8 * j + 0] = t.x << 16; x[8 * j + 1] = t.x & 0xffff0000u; x[8 * j + 2] = t.y << 16;
-              x[8 * j + 3] = t.y & 0xffff0000u; x[8 * j + 4] = t.z << 16; x[8 * j + 5] = t.z & 0xffff0000u;
-              x[8 * j + 6] = t.w << 16; x[8 * j + 7] = t.w & 0xffff0000u;
-            }
-          } else {
-            tmem_ld32_nowait(tX + lane_off + 32 * cc, x);
-            tmem_wait_ld();
-            if (d == 0 && cc == 0) GP_TRACE(i, 14);
-          }
+      for (int mt = 0; mt < 2; ++mt)
 #pragma unroll
-          for (int u = 0; u < 32; ++u) x[u] = __float_as_uint(__uint_as_float(x[u]) * D);
-          if (!last) tmem_st32(tX + lane_off + 32 * cc, x);
-          if (d == 0 && cc == 0 && i >= 0) GP_TRACE(i, 15);
+        for (int nt = 0; nt < 16; ++nt) {
+          S[mt][nt][0] *= D[2 * mt]; S[mt][nt][1] *= D[2 * mt];
+          S[mt][nt][2] *= D[2 * mt + 1]; S[mt][nt][3] *= D[2 * mt + 1];
+        }
 #pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            uint4 w4;
-            w4.x = pack_bf16(__uint_as_float(x[8 * j + 0]), __uint_as_float(x[8 * j + 1]));
-            w4.y = pack_bf16(__uint_as_float(x[8 * j + 2]), __uint_as_float(x[8 * j + 3]));
-            w4.z = pack_bf16(__uint_as_float(x[8 * j + 4]), __uint_as_float(x[8 * j + 5]));
-            w4.w = pack_bf16(__uint_as_float(x[8 * j + 6]), __uint_as_float(x[8 * j + 7]));
-            const uint32_t ch = (uint32_t)(4 * cc + j);
-            if (!last) { if (!(GP_EXP & 2)) *reinterpret_cast<uint4*>(sdst + (ch >> 3) * 16384 + (((ch ^ sx) & 7) << 4)) = w4; }
-            else stg_v4(dst + 32 * cc + 8 * j, w4);
+      for (int j = 0; j < 4; ++j) Ptot[j] *= D[j];
+      if (summary) {
+        if (last) {   // local end state (zero start) and total decay of this segment
+#pragma unroll
+          for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+            for (int nt = 0; nt < 16; ++nt)
+#pragma unroll
+              for (int hf = 0; hf < 2; ++hf)
+                *reinterpret_cast<float2*>(ws_out + (row0 + 16 * mt + 8 * hf) * kD + 8 * nt + 2 * tig) =
+                    make_float2(S[mt][nt][2 * hf], S[mt][nt][2 * hf + 1]);
+          if (tig == 0) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) ws_out[kD * kD + row0 + 8 * j] = Ptot[j];
           }
         }
-      }
-      if (!last) {
-        tmem_wait_st();
+      } else if (!last) {
+        // X_{i+1} -> buffer (i+1)&1, last read by q~ X of step i-1
+        if (i >= 1) mbar_wait(bar_xf + 8 * ((i + 1) & 1), ((i - 1) >> 1) & 1);
+        // rows row0 + 8j all have (row & 7) == gid: eight slot bases, everything else is immediate
+        uint8_t* sdst = smem + GP_SS + ((i + 1) & 1) * 32768 + row0 * 128 + tig * 4;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          uint8_t* bk = sdst + (((uint32_t)(k ^ gid) & 7) << 4);
+#pragma unroll
+          for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+            for (int hf = 0; hf < 2; ++hf)
+#pragma unroll
+              for (int h2 = 0; h2 < 2; ++h2)
+                *reinterpret_cast<uint32_t*>(bk + (16 * mt + 8 * hf) * 128 + h2 * 16384) =
+                    pack_bf16(S[mt][8 * h2 + k][2 * hf], S[mt][8 * h2 + k][2 * hf + 1]);
+        }
         fence_proxy_async_smem();
-        tc_fence_before();
-        mbar_arrive(bar_x);
-        if (d == 0 && i >= 0) GP_TRACE(i, 3);
+        mbar_arrive(bar_x + 8 * ((i + 1) & 1));   // one barrier per buffer: the state may run a full buffer ahead
+        if (tid == 128 && i >= 0) GP_TRACE(i, 3);
+      } else if (final_dst) {
+#pragma unroll
+        for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+          for (int nt = 0; nt < 16; ++nt)
+#pragma unroll
+            for (int hf = 0; hf < 2; ++hf)
+              *reinterpret_cast<uint32_t*>(final_dst + (row0 + 16 * mt + 8 * hf) * kD + 8 * nt + 2 * tig) =
+                  pack_bf16(S[mt][nt][2 * hf], S[mt][nt][2 * hf + 1]);
       }
-      if (!first) mbar_arrive(bar_ke + 8 * (i % GP_KS));
     }
-  } else if (warp >= 8) {
+  } else {
+    setmaxnreg_dec<112>();
     // ================================================================== q tiles (even / odd steps)
     const int w = (warp - 8) >> 2;
     const int tq = tid - 256 - w * 128;             // 0..127
@@ -287,10 +435,11 @@ __global__ void __launch_bounds__(GP_THREADS, 1) gla_prefill_kernel(const GlaPre
     uint8_t* sQw = smem + GP_SQ + w * 32768 + (qc >> 3) * 16384;
     const uint32_t qo0 = (uint32_t)(qt0 * 128 + (((qc ^ qt0) & 7) << 4)), qo1 = qo0 + 1024;   // (qt0+8)&7 == qt0&7
     const __nv_bfloat16* qp = p.q + (int64_t)(tok_begin + qt0) * p.q_st + (int64_t)h0 * p.q_sh + qc * 8;
+    const int q_steps = summary ? 0 : n_steps;      // the summary pass has no queries
     __nv_bfloat16* op = p.o + (int64_t)(tok_begin + r_t) * p.o_st + (int64_t)(h0 + r_hh) * p.o_sh;
     uint4 qv[16];
     int cnt = 0;
-    for (int i = w - 2; i < n_steps; i += 2) {
+    for (int i = w - 2; i < q_steps; i += 2) {
       const int clen = len - i * GC;
       if (i >= 0) {
         const int st = i % GP_KS;
@@ -321,7 +470,7 @@ __global__ void __launch_bounds__(GP_THREADS, 1) gla_prefill_kernel(const GlaPre
         mbar_arrive(bar_qf + 8 * w);
         if (tq == 0) GP_TRACE(i, 5);
       }
-      if (i + 2 < n_steps) {                        // next tile: in flight under the P conversion and epilogue
+      if (i + 2 < q_steps) {                        // next tile: in flight under the P conversion and epilogue
         const int rem = len - (i + 2) * GC - qt0;   // token qt0 + 8e valid iff 8e < rem
         const __nv_bfloat16* src = qp + (int64_t)(i + 2) * GC * p.q_st;
 #pragma unroll
@@ -374,74 +523,39 @@ __global__ void __launch_bounds__(GP_THREADS, 1) gla_prefill_kernel(const GlaPre
         ++cnt;
       }
     }
-  } else if (warp == 2) {
-    // ================================================================== MMA issuer
-    if (lane == 0) {
-      const uint32_t idesc_a = umma_idesc_bf16(128, 16, 0, 0);
-      const uint32_t idesc_o = umma_idesc_bf16(128, 128, 0, 1);
-      const uint32_t idesc_s = umma_idesc_bf16(128, 128, 1, 1);
-      // descriptors differ from these templates only in the 16-byte-granular start address
-      const uint64_t dk = umma_desc_sw128(0, 16, 1024);          // K-major tiles (q~, k~ as B of A)
-      const uint64_t dmn = umma_desc_sw128(0, 2048, 1024);       // MN-major 16-row tiles (k~ as A of Y, v)
-      const uint64_t dx = umma_desc_sw128(0, 16384, 1024);       // MN-major X (two 64-wide halves)
-      auto issue_a = [&](int i) {                   // A = q~ k~^T
-        const int w = i & 1;
-        const uint32_t qb = (sQ + w * 32768) >> 4, kb = (sT + (i % GP_KS) * GP_STAGE + GP_ST_K) >> 4;
-#pragma unroll 1
-        for (int ks = 0; ks < 8; ++ks)
-          umma_bf16(tA + 16 * w, dk + qb + (ks >> 2) * 1024 + (ks & 3) * 2, dk + kb + (ks >> 2) * 128 + (ks & 3) * 2,
-                    idesc_a, ks > 0);
-        umma_commit(bar_a + 8 * w);
-      };
-      mbar_wait(bar_kf, 0);
-      mbar_wait(bar_qf, 0);
-      tc_fence_after();
-      issue_a(0);
-      for (int i = 0; i < n_steps; ++i) {
-        const int w = i & 1, st = i % GP_KS;
-        const uint32_t kb = (sT + st * GP_STAGE + GP_ST_K) >> 4, vb = (sT + st * GP_STAGE + GP_ST_V) >> 4;
-        GP_TRACE(i, 9);
-        mbar_wait(bar_x, i & 1);
-        tc_fence_after();
-        GP_TRACE(i, 10);
-        umma_bf16(tX, dmn + kb, dmn + vb, idesc_s, 1);   // Y = X + k~^T v
-        umma_commit(bar_s);
-        {                                                // O = q~ X
-          const uint32_t qb = (sQ + w * 32768) >> 4, xb = (sS + w * 32768) >> 4;
-#pragma unroll 1
-          for (int ks = 0; ks < 8; ++ks)
-            umma_bf16(tO + 128 * w, dk + qb + (ks >> 2) * 1024 + (ks & 3) * 2, dx + xb + ks * 128, idesc_o, ks > 0);
-        }
-        // A(i+1) goes ahead of P v (i) only when its operands are already there; otherwise P v (i)
-        // and the epilogue behind it are not held up by the next tile's builder
-        bool a_done = i + 1 >= n_steps;
-        if (!a_done && mbar_test(bar_qf + 8 * (w ^ 1), ((i + 1) >> 1) & 1) &&
-            mbar_test(bar_kf + 8 * ((i + 1) % GP_KS), ((i + 1) / GP_KS) & 1)) {
-          tc_fence_after();
-          issue_a(i + 1);
-          a_done = true;
-        }
-        GP_TRACE(i, 11);
-        mbar_wait(bar_p + 8 * w, (i >> 1) & 1);
-        tc_fence_after();
-        GP_TRACE(i, 12);
-        umma_bf16_ts(tO + 128 * w, tA + 16 * w, dmn + vb, idesc_o, 1);   // O += P v
-        umma_commit(bar_o + 8 * w);
-        if (!a_done) {
-          mbar_wait(bar_kf + 8 * ((i + 1) % GP_KS), ((i + 1) / GP_KS) & 1);
-          mbar_wait(bar_qf + 8 * (w ^ 1), ((i + 1) >> 1) & 1);
-          tc_fence_after();
-          issue_a(i + 1);
-        }
-        umma_commit(bar_ke + 8 * st);
-        GP_TRACE(i, 13);
-      }
-    }
-    __syncwarp();
   }
   tc_fence_before();
   __syncthreads();
   if (warp == 2) tmem_dealloc<512>(tmem);
+}
+
+// Pass 2 of the segmented prefill: per chain, turn the segment summaries (local end state L_p from a
+// zero start, total decay P_p) into segment start states, in place:  S_{p+1} = P_p (.) S_p + L_p,
+// S_0 = the chain's initial state.  Slot p then holds the start state of segment p+1.
+__global__ void __launch_bounds__(256) gla_prefill_scan_kernel(const GlaPrefillParams p) {
+  const int hs = blockIdx.x, n = blockIdx.y;
+  const int seq_len = p.cu[n + 1] - p.cu[n];
+  const int n_seg = (seq_len + p.seg_len - 1) / p.seg_len;
+  if (n_seg <= 1) return;
+  const int slot = p.slot[n], mode = p.init_mode[n];
+  const __nv_bfloat16* init_src = nullptr;
+  if (mode == 1 && slot >= 0) init_src = p.state + (int64_t)slot * p.st_ss + (int64_t)hs * p.st_sh;
+  else if (mode == 2 && p.meta_state) init_src = p.meta_state + (int64_t)hs * p.meta_sh;
+  float* ws = p.ws + (int64_t)(n * p.Hs + hs) * p.n_segs * GP_WS_ELEMS;
+  const int e0 = (blockIdx.z * 256 + threadIdx.x) * 4;      // 4 consecutive d_v of one d_k row
+  const int row = e0 >> 7;
+  float4 S = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (init_src) {
+    const uint2 u = *reinterpret_cast<const uint2*>(init_src + e0);
+    S = make_float4(bf16_lo(u.x), bf16_hi(u.x), bf16_lo(u.y), bf16_hi(u.y));
+  }
+  for (int sg = 0; sg + 1 < n_seg; ++sg) {
+    float* w = ws + (int64_t)sg * GP_WS_ELEMS;
+    const float P = w[kD * kD + row];
+    const float4 L = *reinterpret_cast<const float4*>(w + e0);
+    S = make_float4(fmaf(P, S.x, L.x), fmaf(P, S.y, L.y), fmaf(P, S.z, L.z), fmaf(P, S.w, L.w));
+    *reinterpret_cast<float4*>(w + e0) = S;
+  }
 }
 
 }  // namespace hymeta
@@ -454,15 +568,29 @@ extern "C" int hymeta_debug_set_gla_trace(void* buf) {
 }
 #endif
 
-extern "C" int hymeta_gla_prefill_varlen(
+extern "C" size_t hymeta_gla_prefill_workspace_bytes(int N, int Hs, int max_seqlen, int seg_len) {
+  if (seg_len <= 0 || N <= 0 || Hs <= 0 || max_seqlen <= seg_len) return 0;
+  const size_t n_segs = ((size_t)max_seqlen + seg_len - 1) / seg_len;
+  return (size_t)N * Hs * n_segs * GP_WS_ELEMS * sizeof(float);
+}
+
+extern "C" int hymeta_gla_prefill_varlen_seg(
     const void* q, const void* k, const void* v, const void* g, void* o, void* state,
     const void* meta_state, const int32_t* cu_seqlens, const int32_t* slot_idx,
     const int32_t* init_mode, int N, int T, int H, int Hk, int Hv, int Hs, int D, int64_t q_st, int64_t q_sh,
     int64_t k_st, int64_t k_sh, int64_t v_st, int64_t v_sh, int64_t g_st, int64_t g_sh, int64_t o_st,
     int64_t o_sh, int64_t st_ss, int64_t st_sh, int64_t meta_sh, int g_is_fp32, float scale,
-    int write_state, int max_seqlen, void* stream) {
-  (void)max_seqlen;
+    int write_state, int max_seqlen, int seg_len, void* workspace, size_t workspace_bytes, void* stream) {
   if (N == 0) return HYMETA_OK;
+  if (seg_len < 0 || seg_len % GC) return HYMETA_ERR_INVALID_ARG;
+  int n_segs = 1;
+  if (seg_len > 0 && max_seqlen > seg_len) {
+    n_segs = (max_seqlen + seg_len - 1) / seg_len;
+    if (n_segs > 65535) return HYMETA_ERR_UNSUPPORTED;
+    if (!workspace || workspace_bytes < hymeta_gla_prefill_workspace_bytes(N, Hs, max_seqlen, seg_len) ||
+        ((uintptr_t)workspace % 16))
+      return HYMETA_ERR_INVALID_ARG;
+  } else seg_len = 0;
   if (N < 0 || T < 0 || H <= 0 || Hk <= 0 || Hv <= 0 || Hs <= 0 || !cu_seqlens || !slot_idx || !init_mode || !state)
     return HYMETA_ERR_INVALID_ARG;
   if (T > 0 && (!q || !k || !v || !g || !o)) return HYMETA_ERR_INVALID_ARG;
@@ -481,15 +609,56 @@ extern "C" int hymeta_gla_prefill_varlen(
   p.q_st = q_st; p.q_sh = q_sh; p.k_st = k_st; p.k_sh = k_sh; p.v_st = v_st; p.v_sh = v_sh;
   p.g_st = g_st; p.g_sh = g_sh; p.o_st = o_st; p.o_sh = o_sh; p.st_ss = st_ss; p.st_sh = st_sh;
   p.meta_sh = meta_sh;
+  p.seg_len = seg_len; p.n_segs = n_segs; p.pass = 0; p.ws = (float*)workspace;
+  // TMA maps: raw g / k rows ([16 tokens][128 channels] boxes) and v (SWIZZLE_128B 64-wide halves)
+  const int64_t tvec[] = {k_st, k_sh, g_st * (g_is_fp32 ? 2 : 1), g_sh * (g_is_fp32 ? 2 : 1)};
+  for (int64_t s : tvec)
+    if (s % 8) return HYMETA_ERR_INVALID_ARG;   // TMA needs 16-byte multiples
+  CUtensorMap tmG, tmK, tmV;
+  memset(&tmG, 0, sizeof(tmG)); tmK = tmV = tmG;
+  if (T > 0) {   // with no tokens every chain is empty and the maps are never dereferenced
+    const uint64_t dk[3] = {(uint64_t)kD, (uint64_t)Hk, (uint64_t)T};
+    const uint64_t dv[3] = {(uint64_t)kD, (uint64_t)Hv, (uint64_t)T};
+    const int64_t sg[3] = {1, g_sh, g_st}, sk[3] = {1, k_sh, k_st}, sv[3] = {1, v_sh, v_st};
+    const uint32_t braw[3] = {(uint32_t)kD, 1, (uint32_t)GC}, bv[3] = {64, 1, (uint32_t)GC};
+    int rc;
+    if ((rc = make_tmap(&tmG, g, g_is_fp32 ? 4 : 2, 3, dk, sg, braw, false))) return rc;
+    if ((rc = make_tmap(&tmK, k, 2, 3, dk, sk, braw, false))) return rc;
+    if ((rc = make_tmap(&tmV, v, 2, 3, dv, sv, bv, true))) return rc;
+  }
   static bool attr_set = false;
   if (!attr_set) {
     cudaFuncSetAttribute(gla_prefill_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, GP_SMEM);
     cudaFuncSetAttribute(gla_prefill_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, GP_SMEM);
     attr_set = true;
   }
-  dim3 grid(Hs, N);
-  if (g_is_fp32) gla_prefill_kernel<true><<<grid, GP_THREADS, GP_SMEM, (cudaStream_t)stream>>>(p);
-  else gla_prefill_kernel<false><<<grid, GP_THREADS, GP_SMEM, (cudaStream_t)stream>>>(p);
-  count_launch();
+  auto launch = [&](int pass, int segs) {
+    p.pass = pass;
+    dim3 grid(Hs, N, segs);
+    if (g_is_fp32) gla_prefill_kernel<true><<<grid, GP_THREADS, GP_SMEM, (cudaStream_t)stream>>>(p, tmG, tmK, tmV);
+    else gla_prefill_kernel<false><<<grid, GP_THREADS, GP_SMEM, (cudaStream_t)stream>>>(p, tmG, tmK, tmV);
+    count_launch();
+  };
+  if (n_segs == 1) launch(0, 1);
+  else {
+    // (1) per-segment summaries from a zero start, (2) scan into segment start states, (3) outputs
+    launch(1, n_segs - 1);
+    gla_prefill_scan_kernel<<<dim3(Hs, N, kD * kD / 1024), 256, 0, (cudaStream_t)stream>>>(p);
+    count_launch();
+    launch(3, n_segs);
+  }
   return check_launch();
+}
+
+extern "C" int hymeta_gla_prefill_varlen(
+    const void* q, const void* k, const void* v, const void* g, void* o, void* state,
+    const void* meta_state, const int32_t* cu_seqlens, const int32_t* slot_idx,
+    const int32_t* init_mode, int N, int T, int H, int Hk, int Hv, int Hs, int D, int64_t q_st, int64_t q_sh,
+    int64_t k_st, int64_t k_sh, int64_t v_st, int64_t v_sh, int64_t g_st, int64_t g_sh, int64_t o_st,
+    int64_t o_sh, int64_t st_ss, int64_t st_sh, int64_t meta_sh, int g_is_fp32, float scale,
+    int write_state, int max_seqlen, void* stream) {
+  return hymeta_gla_prefill_varlen_seg(q, k, v, g, o, state, meta_state, cu_seqlens, slot_idx, init_mode, N, T,
+                                       H, Hk, Hv, Hs, D, q_st, q_sh, k_st, k_sh, v_st, v_sh, g_st, g_sh, o_st,
+                                       o_sh, st_ss, st_sh, meta_sh, g_is_fp32, scale, write_state, max_seqlen,
+                                       0, nullptr, 0, stream);
 }

@@ -54,7 +54,8 @@ swa_prefill_kernel(const SwaPrefillParams p, const __grid_constant__ CUtensorMap
                    const __grid_constant__ CUtensorMap tmQ2, const __grid_constant__ CUtensorMap tmMK,
                    const __grid_constant__ CUtensorMap tmMV) {
   extern __shared__ __align__(1024) uint8_t smem[];
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);   // warp-uniform for the compiler
   const int h = blockIdx.x, hkv = h / (p.H / p.Hkv);
   const int qp = p.n_qpairs - 1 - blockIdx.y;   // long pairs first
   const int n = blockIdx.z;
@@ -128,7 +129,7 @@ swa_prefill_kernel(const SwaPrefillParams p, const __grid_constant__ CUtensorMap
 
   if (warp == 8) {
     // ================================================================== TMA producer
-    if (lane == 0) {
+    if (elect_one_sync()) {
       const CUtensorMap* tq = meta_q ? &tmQ2 : &tmQ;
       tma_prefetch_desc(tq); tma_prefetch_desc(&tmK); tma_prefetch_desc(&tmV);
       const int nq = qt[1].on ? 2 : 1;
@@ -164,7 +165,7 @@ swa_prefill_kernel(const SwaPrefillParams p, const __grid_constant__ CUtensorMap
     __syncwarp();
   } else if (warp == 9) {
     // ================================================================== MMA issuer
-    if (lane == 0) {
+    if (elect_one_sync()) {
       const uint32_t idesc_s = umma_idesc_bf16(PF_BM, PF_BN, 0, 0);
       const uint32_t idesc_o = umma_idesc_bf16(PF_BM, kD, 0, 1);
       auto issue_s = [&](int i, int t) {   // S_i = Q_i K(t)^T

@@ -19,6 +19,10 @@ __device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(bar), "r"(bytes)
                : "memory");
 }
+// adds to the pending transaction count without arriving
+__device__ __forceinline__ void mbar_expect_tx_only(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.expect_tx.relaxed.cta.shared::cta.b64 [%0], %1;" :: "r"(bar), "r"(bytes) : "memory");
+}
 __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(bar) : "memory");
 }
@@ -43,6 +47,23 @@ __device__ __forceinline__ bool mbar_test(uint32_t bar, uint32_t parity) {
       : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
   return ok != 0;
 }
+
+// one lane of a converged warp (ptxas then knows a single thread issues what follows)
+__device__ __forceinline__ bool elect_one_sync() {
+  uint32_t pred;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "elect.sync _|p, 0xffffffff;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(pred));
+  return pred != 0;
+}
+
+// register re-allocation between warpgroups (all 4 warps of an aligned warpgroup execute it)
+template <int N>
+__device__ __forceinline__ void setmaxnreg_inc() { asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" :: "n"(N)); }
+template <int N>
+__device__ __forceinline__ void setmaxnreg_dec() { asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" :: "n"(N)); }
 
 // ------------------------------------------------------------------------------------ fences
 __device__ __forceinline__ void fence_proxy_async_smem() {
@@ -237,5 +258,8 @@ PFN_encodeTiled get_encode_tiled();
 // (strides[0] ignored, must be 1).  box = tile extents.  SWIZZLE_128B needs box[0]*2 == 128 bytes.
 int make_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims,
                    const int64_t* strides_elems, const uint32_t* box, bool swizzle128);
+// same for 2-byte (bf16) or 4-byte (fp32) elements
+int make_tmap(CUtensorMap* out, const void* base, int elem_bytes, int rank, const uint64_t* dims,
+              const int64_t* strides_elems, const uint32_t* box, bool swizzle128);
 
 }  // namespace hymeta

@@ -71,7 +71,7 @@ def gla_decode(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, g: torch.Tenso
 def gla_prefill_varlen(q, k, v, g, state, cu_seqlens, slot_idx, init_mode,
                        meta_state: Optional[torch.Tensor] = None, scale: Optional[float] = None,
                        write_state: bool = True, max_seqlen: Optional[int] = None,
-                       out: Optional[torch.Tensor] = None) -> torch.Tensor:
+                       out: Optional[torch.Tensor] = None, seg_len: Optional[int] = None) -> torch.Tensor:
     """q [T,H,D]; k,g [T,Hk,D]; v [T,Hv,D]; state [slots,Hs,D,D]; cu_seqlens [N+1], slot_idx [N],
     init_mode [N] int32 device tensors.  Returns o [T,H,D] bf16; writes final states."""
     T, H, D = q.shape
@@ -90,15 +90,54 @@ def gla_prefill_varlen(q, k, v, g, state, cu_seqlens, slot_idx, init_mode,
         out = torch.empty(T, H, D, dtype=q.dtype, device=q.device)
     if scale is None:
         scale = D ** -0.5
-    check(lib().hymeta_gla_prefill_varlen(
+    msl = int(max_seqlen if max_seqlen is not None else T)
+    if seg_len is None:
+        seg_len = gla_prefill_seg_len(N * Hs, msl, q.device)
+    ws, ws_bytes = None, 0
+    if seg_len:
+        ws_bytes = lib().hymeta_gla_prefill_workspace_bytes(N, Hs, msl, seg_len)
+        if ws_bytes:
+            ws = _gla_workspace(q.device, ws_bytes)
+    check(lib().hymeta_gla_prefill_varlen_seg(
         _ptr(q), _ptr(k), _ptr(v), _ptr(g), _ptr(out), _ptr(state), _ptr(meta_state),
         _ptr(cu_seqlens), _ptr(slot_idx), _ptr(init_mode), N, T, H, Hk, Hv, Hs, D,
         q.stride(0), q.stride(1), k.stride(0), k.stride(1), v.stride(0), v.stride(1),
         g.stride(0), g.stride(1), out.stride(0), out.stride(1), state.stride(0), state.stride(1),
         0 if meta_state is None else meta_state.stride(0),
-        int(g.dtype == torch.float32), float(scale), int(write_state),
-        int(max_seqlen if max_seqlen is not None else T), _stream()), "hymeta_gla_prefill_varlen")
+        int(g.dtype == torch.float32), float(scale), int(write_state), msl,
+        int(seg_len or 0), _ptr(ws), ws_bytes, _stream()), "hymeta_gla_prefill_varlen_seg")
     return out
+
+
+_SM_COUNT = {}
+_WS = {}
+
+
+def _gla_workspace(device, nbytes: int) -> torch.Tensor:
+    """Grow-only fp32 scratch per device (the C ABI never allocates)."""
+    key = (device.type, device.index)
+    w = _WS.get(key)
+    if w is None or w.numel() * 4 < nbytes:
+        w = torch.empty((nbytes + 3) // 4, dtype=torch.float32, device=device)
+        _WS[key] = w
+    return w
+
+
+def gla_prefill_seg_len(chains: int, max_seqlen: int, device=None, min_seg: int = 256) -> int:
+    """Segment length for the sequence-parallel prefill, or 0 for the single-pass form.  One CTA per
+    SM walks one chain, so segmenting pays only when there are fewer chains than SMs; the summary
+    pass re-reads k/v/g (~18% extra traffic), so whole waves of full sequences are left alone."""
+    dev = torch.cuda.current_device() if device is None or device.index is None else device.index
+    sms = _SM_COUNT.get(dev)
+    if sms is None:
+        sms = _SM_COUNT[dev] = torch.cuda.get_device_properties(dev).multi_processor_count
+    if chains <= 0 or chains >= sms or max_seqlen < 2 * min_seg:
+        return 0
+    n_segs = min(-(-2 * sms // chains), max_seqlen // min_seg)
+    if n_segs <= 1:
+        return 0
+    seg = -(-max_seqlen // n_segs)
+    return -(-seg // 16) * 16
 
 
 # ----------------------------------------------------------------------------------- a4
