@@ -183,6 +183,30 @@ int hymeta_swa_meta_decode_paged(const void* q, const void* k_cache, const void*
                                  int64_t mk_st, int64_t mk_sh, int64_t mv_st, int64_t mv_sh,
                                  void* stream);
 
+/* a8 + a9 fused: the same decode with (1) the step's paged-KV write folded in --
+ * replaces reshape_and_cache_flash (meta_attention.py:790-799) followed by the decode call
+ * (:954-981): new_k/new_v [B, Hkv, D] are the K/V of the token at position cache_seqlens[b]-1; the
+ * kernel stores them to cache[block_tables[b, p / block_size], p % block_size] and attends to them
+ * from registers, so the pages need not hold that row yet (null: the pages already hold it) -- and
+ * (2) the split-K combine folded into the split kernel: `tickets` is
+ * hymeta_swa_decode_ticket_bytes(B, H, Hkv) bytes of int32, ZERO before the first call; the kernel
+ * leaves it zero (null: separate combine launch).  One launch per layer-step instead of three. */
+size_t hymeta_swa_decode_ticket_bytes(int B, int H, int Hkv);
+int hymeta_swa_meta_decode_paged_fused(const void* q, void* k_cache, void* v_cache,
+                                       const int32_t* block_tables, const int32_t* cache_seqlens,
+                                       const void* meta_k, const void* meta_v, void* out,
+                                       void* workspace, size_t workspace_bytes,
+                                       int B, int H, int Hkv, int D, int M, int block_size,
+                                       int num_blocks, int max_blocks, int64_t bt_stride,
+                                       int window_left, float scale,
+                                       int64_t q_sb, int64_t q_sh, int64_t o_sb, int64_t o_sh,
+                                       int64_t kc_sblk, int64_t kc_stok, int64_t kc_sh,
+                                       int64_t vc_sblk, int64_t vc_stok, int64_t vc_sh,
+                                       int64_t mk_st, int64_t mk_sh, int64_t mv_st, int64_t mv_sh,
+                                       const void* new_k, const void* new_v,
+                                       int64_t nk_sb, int64_t nk_sh, int64_t nv_sb, int64_t nv_sh,
+                                       int32_t* tickets, void* stream);
+
 /* ------------------------------------------------------------------------------------------------
  * a7  SWA + meta-prefix varlen prefill -- replaces metatoken_flash_attn_varlen_func
  *     (vllm_hymeta/attention/fa_kernel_metatoken.py:329-374 -> :198-285: two flash-attn

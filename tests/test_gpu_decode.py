@@ -222,3 +222,83 @@ def test_swa_decode_ignores_uninitialised_rows(ops, bs):
     out = ops.swa_meta_decode_paged(q.to(DEV), kc.to(DEV), vc.to(DEV), tables.to(DEV),
                                     torch.tensor(lens, dtype=torch.int32, device=DEV), None, None, wl)
     assert_close(out, ref, "swa decode with NaN garbage")
+
+
+# ------------------------------------------------------------------------------- a8 + a9 fused (f3)
+@pytest.mark.parametrize("case", CASES + [([1, 64, 65, 128, 129, 0, 4097], 256, 4096, 0, 28, 4),
+                                           ([700, 40000, 3], 256, -1, 128, 28, 4)])
+def test_swa_decode_fused_write_and_combine(ops, case):
+    """reshape_and_cache_flash + decode in ONE launch (meta_attention.py:790-799 + :954-981): the
+    new token's K/V come as arguments, the pages do not hold them yet (NaN there).  Must be
+    bit-identical to kv_write_paged followed by the two-launch decode, and the pages bit-exact."""
+    lens, bs, wl, M, H, Hkv = case
+    D, B = 128, len(lens)
+    kc, vc, tables, keys, vals = make_paged(lens, Hkv, D, bs, seed=3 * len(lens) + bs,
+                                            max_blocks=max(1, (max(lens) + bs - 1) // bs) + 2)
+    gen = torch.Generator().manual_seed(11)
+    q = torch.randn(B, H, D, generator=gen).bfloat16().to(DEV)
+    k2 = v2 = None
+    if M:
+        k2 = torch.randn(M, Hkv, D, generator=gen).bfloat16().to(DEV)
+        v2 = torch.randn(M, Hkv, D, generator=gen).bfloat16().to(DEV)
+    nk = torch.randn(B, Hkv, D, generator=gen).bfloat16()
+    nv = torch.randn(B, Hkv, D, generator=gen).bfloat16()
+    slot = torch.full((B,), -1, dtype=torch.int64)
+    nan = torch.tensor(float("nan")).bfloat16()
+    for i, L in enumerate(lens):
+        if L > 0:
+            p = L - 1
+            slot[i] = int(tables[i, p // bs]) * bs + p % bs
+            kc[tables[i, p // bs], p % bs] = nan       # the fused kernel must not rely on this row
+            vc[tables[i, p // bs], p % bs] = nan
+    d_lens = torch.tensor(lens, dtype=torch.int32, device=DEV)
+    d_tab = tables.to(DEV)
+    # reference sequence: separate write, then split + combine launches
+    kc_a, vc_a = kc.to(DEV), vc.to(DEV)
+    ops.kv_write_paged(nk.to(DEV), nv.to(DEV), kc_a, vc_a, slot.to(DEV))
+    out_a = ops.swa_meta_decode_paged(q, kc_a, vc_a, d_tab, d_lens, k2, v2, wl, fused_combine=False)
+    # fused: one launch
+    kc_b, vc_b = kc.to(DEV), vc.to(DEV)
+    n0 = ops.launch_count()
+    out_b = ops.swa_meta_decode_paged(q, kc_b, vc_b, d_tab, d_lens, k2, v2, wl,
+                                      new_k=nk.to(DEV), new_v=nv.to(DEV))
+    assert ops.launch_count() - n0 == 1
+    torch.cuda.synchronize()
+    assert torch.equal(out_a.view(torch.int16), out_b.view(torch.int16))
+    assert torch.equal(kc_a.view(torch.int16), kc_b.view(torch.int16))
+    assert torch.equal(vc_a.view(torch.int16), vc_b.view(torch.int16))
+    # and against the oracle (fp32 dense softmax over the gathered pages)
+    ref = oswa.swa_meta_decode_paged(q.cpu(), kc_a.cpu(), vc_a.cpu(), tables, lens,
+                                     None if k2 is None else k2.cpu(), None if v2 is None else v2.cpu(),
+                                     wl, out_dtype=torch.float32)
+    assert_close(out_b, ref, "fused swa decode")
+    # tickets are restored: a second fused call gives the same bits
+    out_c = ops.swa_meta_decode_paged(q, kc_b, vc_b, d_tab, d_lens, k2, v2, wl,
+                                      new_k=nk.to(DEV), new_v=nv.to(DEV))
+    assert torch.equal(out_c.view(torch.int16), out_b.view(torch.int16))
+
+
+def test_swa_decode_fused_graph_capture(ops):
+    lens, bs, wl, H, Hkv, D = [300, 0, 5000, 77], 256, 4096, 28, 4, 128
+    B = len(lens)
+    kc, vc, tables, _, _ = make_paged(lens, Hkv, D, bs, seed=5)
+    gen = torch.Generator().manual_seed(3)
+    q = torch.randn(B, H, D, generator=gen).bfloat16().to(DEV)
+    nk = torch.randn(B, Hkv, D, generator=gen).bfloat16().to(DEV)
+    nv = torch.randn(B, Hkv, D, generator=gen).bfloat16().to(DEV)
+    d_lens = torch.tensor(lens, dtype=torch.int32, device=DEV)
+    kc, vc, d_tab = kc.to(DEV), vc.to(DEV), tables.to(DEV)
+    out = torch.empty(B, H, D, dtype=torch.bfloat16, device=DEV)
+    ops.swa_meta_decode_paged(q, kc, vc, d_tab, d_lens, None, None, wl, out=out, new_k=nk, new_v=nv)
+    eager = out.clone()
+    st = torch.cuda.Stream()
+    with torch.cuda.stream(st):
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph, stream=st):
+            ops.swa_meta_decode_paged(q, kc, vc, d_tab, d_lens, None, None, wl, out=out, new_k=nk, new_v=nv)
+    out.zero_()
+    for _ in range(3):
+        graph.replay()
+    torch.cuda.synchronize()
+    assert torch.equal(out.view(torch.int16), eager.view(torch.int16))
+    assert out[1].abs().max().item() == 0          # zero-length (padded) request

@@ -85,13 +85,16 @@ def bench_gla_decode(B, H=28, Hkv=4, D=128, layout="compact", gdt=torch.bfloat16
           f"({alg/t/1e9/PEAK:.2%} of measured {PEAK:.0f})  alg={alg/1e6:.1f} MB  [graph of {nrot} rotating buffers]")
 
 
-def bench_swa_decode(B, ctx, H=28, Hkv=4, D=128, bs=256, wl=4096, M=0, flush=None):
+def bench_swa_decode(B, ctx, H=28, Hkv=4, D=128, bs=256, wl=4096, M=0, flush=None, ragged=False):
+    """ragged: lengths ~ U[1024, ctx] (config 4: 1000 seqs, <= 9K), else all == ctx."""
     dev = "cuda"
     nblk = (ctx + bs - 1) // bs
     nb = B * nblk + 1
     kv = torch.randn(2, nb, bs, Hkv, D, device=dev).bfloat16()
     tables = torch.randperm(nb - 1, device=dev).to(torch.int32).view(B, nblk)
     lens = torch.full((B,), ctx, dtype=torch.int32, device=dev)
+    if ragged:
+        lens = torch.randint(1024, ctx + 1, (B,), generator=torch.Generator().manual_seed(0)).to(torch.int32).to(dev)
     q = torch.randn(B, H, D, device=dev).bfloat16()
     mk = mv = None
     if M:
@@ -100,9 +103,9 @@ def bench_swa_decode(B, ctx, H=28, Hkv=4, D=128, bs=256, wl=4096, M=0, flush=Non
     out = torch.empty(B, H, D, device=dev, dtype=torch.bfloat16)
     t = timeit(lambda: ops.swa_meta_decode_paged(q, kv[0], kv[1], tables, lens, mk, mv, wl, out=out),
                flush=flush)
-    nk = min(ctx, wl + 1) if wl >= 0 else ctx
-    alg = B * (Hkv * 2 * D * 2 * nk + H * 2 * D * 2) + Hkv * 2 * D * 2 * M
-    print(f"swa_decode B={B} ctx={ctx} wl={wl} M={M}: {t*1e6:8.1f} us  {alg/t/1e9:8.1f} GB/s "
+    nk = (lens.clamp(max=wl + 1) if wl >= 0 else lens).sum().item()
+    alg = Hkv * 2 * D * 2 * nk + B * H * 2 * D * 2 + Hkv * 2 * D * 2 * M
+    print(f"swa_decode B={B} ctx={'<=' if ragged else ''}{ctx} wl={wl} M={M}: {t*1e6:8.1f} us  {alg/t/1e9:8.1f} GB/s "
           f"({alg/t/1e9/PEAK:.2%})  alg={alg/1e6:.1f} MB")
 
 
@@ -171,6 +174,7 @@ if __name__ == "__main__":
         bench_swa_decode(64, 8192, flush=flush)
         bench_swa_decode(64, 8704, M=128, wl=4095, flush=flush)
         bench_swa_decode(1000, 5000, flush=flush)
+        bench_swa_decode(1000, 9216, flush=flush, ragged=True)     # config 4
         bench_swa_decode(8, 8192, flush=flush)
         bench_swa_decode(1, 8192, flush=flush)
     if a.which in ("all", "swa_prefill"):

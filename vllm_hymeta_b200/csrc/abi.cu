@@ -1,5 +1,6 @@
 // Library-level entry points: version, status strings, launch accounting.
 #include <atomic>
+#include <cstdlib>
 
 #include "common.cuh"
 
@@ -7,6 +8,13 @@ namespace hymeta {
 thread_local int g_last_cuda_error = 0;
 static std::atomic<int64_t> g_launches{0};
 void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+bool pdl_enabled() {
+  static const bool on = [] {
+    const char* s = getenv("HYMETA_PDL");
+    return !(s && s[0] == '0');
+  }();
+  return on;
+}
 }  // namespace hymeta
 
 extern "C" int hymeta_abi_version(void) { return HYMETA_ABI_VERSION; }

@@ -22,6 +22,29 @@ inline int check_launch() {
   return HYMETA_OK;
 }
 
+// ---- programmatic dependent launch (PDL) ------------------------------------------------------
+// The decode step is a chain of short kernels (kv write -> split-K -> combine -> next layer ...);
+// launched with programmaticStreamSerialization the next kernel's CTAs are scheduled while the
+// previous grid drains and block in griddepcontrol.wait until it has completed and flushed.  Every
+// PDL-launched kernel executes pdl_wait() before its first global access (and before any early
+// return, so completion stays transitive along the chain).  HYMETA_PDL=0 disables the attribute.
+bool pdl_enabled();
+template <typename... KArgs, typename... Args>
+inline void launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                       Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
+  cfg.attrs = attr; cfg.numAttrs = 1;
+  cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+
 // ---- small device helpers ---------------------------------------------------------------------
 __device__ __forceinline__ float bf16_lo(uint32_t x) { return __uint_as_float(x << 16); }
 __device__ __forceinline__ float bf16_hi(uint32_t x) { return __uint_as_float(x & 0xffff0000u); }

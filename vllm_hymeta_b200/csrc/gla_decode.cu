@@ -63,7 +63,8 @@ constexpr int GD_STAGE = GD_RAW_G + 512;          // 35840 B per stage
 constexpr int GD_THREADS = 256;
 constexpr int GD_SQ = GD_NS * GD_STAGE;           // s_q  [128][8] f32  (scaled, fp32)
 constexpr int GD_SKG = GD_SQ + kD * 8 * 4;        // s_kg [128] {k bf16x2, exp(g)}
-constexpr int GD_SMEM = GD_SKG + kD * 8;
+constexpr int GD_SLOT = GD_SKG + kD * 8;          // slot ring [8] int
+constexpr int GD_SMEM = GD_SLOT + 32;
 
 // Persistent, software-pipelined: CTA c handles items c, c+grid, ... (item = one (request,
 // state-head) 128x128 state with its small operands).  Item i+2 streams into a 3-stage
@@ -82,22 +83,28 @@ __global__ void __launch_bounds__(GD_THREADS, 2) gla_decode_kernel(const GlaDeco
   const int c = lane & 15, rg = lane >> 4;          // 16-byte column chunk / row inside a warp instr
   const int G = p.H / p.Hs;
   const int gs = gridDim.x;
+  pdl_wait();
+  pdl_launch_dependents();
   const int gs_b = gs / p.Hs, gs_h = gs % p.Hs;     // item stride decomposed: no per-item division
 
-  struct Item { int b, hs, slot; };
+  // Item bookkeeping without registers held across the loop: (b, hs) of items k, k+2, k+4 advance
+  // incrementally; the slot index of item k+4 is fetched with a 4-byte cp.async into a small ring
+  // in the same commit group as item k+2's operands, so it is visible (wait_group + barrier) two
+  // iterations before issue() needs it and no thread ever stalls on the slot_idx load.
+  int* s_slot = reinterpret_cast<int*>(smem + GD_SLOT);
+  struct Item { int b, hs; };
   auto advance = [&](Item x) -> Item {              // item + gs
     x.b += gs_b; x.hs += gs_h;
     if (x.hs >= p.Hs) { x.hs -= p.Hs; ++x.b; }
-    x.slot = x.b < p.B ? p.slot_idx[x.b] : -1;
     return x;
   };
   // small-operand copy role of this thread: one 16-byte chunk (or none)
   //   tid <  128: q head tid/16, rows 8*(tid%16)..   128..143: k   144..159: v   160..191: g
-  auto issue = [&](const Item& x, int stage) {
-    if (x.slot >= 0) {
+  auto issue = [&](const Item& x, int slot, int stage) {
+    if (slot >= 0) {
       const uint32_t sb = ring + stage * GD_STAGE;
       {  // this thread's 8 chunks of the state
-        const __nv_bfloat16* src = p.state + (int64_t)x.slot * p.st_ss + (int64_t)x.hs * p.st_sh +
+        const __nv_bfloat16* src = p.state + (int64_t)slot * p.st_ss + (int64_t)x.hs * p.st_sh +
                                    (warp * 16 + rg) * kD + c * 8;
         const uint32_t dst = sb + (warp * 16 + rg) * 256 + c * 16;
 #pragma unroll
@@ -119,28 +126,40 @@ __global__ void __launch_bounds__(GD_THREADS, 2) gla_decode_kernel(const GlaDeco
         else cp_async16(sb + GD_RAW_G + (tid - 160) * 16, reinterpret_cast<const __nv_bfloat16*>(p.g) + off + (tid - 160) * 8, true);
       }
     }
-    cp_async_commit();
+  };
+  auto fetch_slot = [&](const Item& x, int j) {     // one thread: slot of item j -> ring entry j & 7
+    if (x.b < p.B) cp_async4(smem_u32(s_slot + (j & 7)), p.slot_idx + x.b);
+    else s_slot[j & 7] = -1;
   };
 
   Item cur_i;
   cur_i.b = blockIdx.x / p.Hs; cur_i.hs = blockIdx.x % p.Hs;
-  cur_i.slot = p.slot_idx[cur_i.b];
-  Item n1 = advance(cur_i), n2 = advance(n1), n3 = advance(n2);
-  issue(cur_i, 0);
-  issue(n1, 1);
+  Item i2 = advance(advance(cur_i)), i4 = advance(advance(i2));
+  if (tid < 4) {                                     // slots of items 0..3, once, synchronously
+    Item x = cur_i;
+    for (int j = 0; j < tid; ++j) x = advance(x);
+    s_slot[tid] = x.b < p.B ? p.slot_idx[x.b] : -1;
+  }
+  __syncthreads();
+  issue(cur_i, s_slot[0], 0);
+  cp_async_commit();
+  issue(advance(cur_i), s_slot[1], 1);
+  cp_async_commit();
 
   for (int k = 0; cur_i.b < p.B; ++k) {
     const int stage = k % GD_NS;
-    const Item n4 = advance(n3);                     // slot prefetched two iterations before its use
     cp_async_wait<1>();                              // own chunks of item k have landed ...
     __syncthreads();                                 // ... and everyone else's; item k-1 is fully consumed
-    issue(n2, (k + 2) % GD_NS);                      // refill the stage item k-1 used
+    issue(i2, s_slot[(k + 2) & 7], (k + 2) % GD_NS);  // refill the stage item k-1 used
+    if (tid == GD_THREADS - 1) fetch_slot(i4, k + 4);
+    cp_async_commit();
+    const int cur_slot = s_slot[k & 7];
     const int h0 = cur_i.hs * G;
     __nv_bfloat16* op = p.o + cur_i.b * p.o_sb + (int64_t)(h0 + (tid >> 7)) * p.o_sh + (tid & 127);
-    if (cur_i.slot < 0) {   // PAD slot (CUDA-graph padding): skip, emit zeros (CTA-uniform branch)
+    if (cur_slot < 0) {   // PAD slot (CUDA-graph padding): skip, emit zeros (CTA-uniform branch)
 #pragma unroll 1
       for (int hh = tid >> 7; hh < G; hh += 2, op += 2 * p.o_sh) *op = __float2bfloat16(0.f);
-      cur_i = n1; n1 = n2; n2 = n3; n3 = n4;
+      cur_i = advance(cur_i); i2 = advance(i2); i4 = advance(i4);
       continue;
     }
     uint8_t* sbase = smem + stage * GD_STAGE;
@@ -165,7 +184,7 @@ __global__ void __launch_bounds__(GD_THREADS, 2) gla_decode_kernel(const GlaDeco
     }
     const uint4 vraw = *reinterpret_cast<const uint4*>(sbase + GD_RAW_V + c * 16);
     const uint32_t vv[4] = {vraw.x, vraw.y, vraw.z, vraw.w};
-    __nv_bfloat16* sp = p.state + (int64_t)cur_i.slot * p.st_ss + (int64_t)cur_i.hs * p.st_sh +
+    __nv_bfloat16* sp = p.state + (int64_t)cur_slot * p.st_ss + (int64_t)cur_i.hs * p.st_sh +
                         (warp * 16 + rg) * kD + c * 8;
     const uint32_t st_base = ring + stage * GD_STAGE + (warp * 16 + rg) * 256 + c * 16;
     __syncwarp();
@@ -248,7 +267,7 @@ __global__ void __launch_bounds__(GD_THREADS, 2) gla_decode_kernel(const GlaDeco
       }
     }
     // no barrier here: the next iteration's top barrier orders these reads before the refill
-    cur_i = n1; n1 = n2; n2 = n3; n3 = n4;
+    cur_i = advance(cur_i); i2 = advance(i2); i4 = advance(i4);
   }
   cp_async_wait<0>();
 }
@@ -263,8 +282,8 @@ static void launch_gla_decode(const GlaDecodeParams& p, bool g_fp32, cudaStream_
     cudaFuncSetAttribute(gla_decode_kernel<GT, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, GD_SMEM);
     attr_set = true;
   }
-  if (g_fp32) gla_decode_kernel<GT, true><<<grid, GD_THREADS, GD_SMEM, st>>>(p, (int)n_items);
-  else gla_decode_kernel<GT, false><<<grid, GD_THREADS, GD_SMEM, st>>>(p, (int)n_items);
+  if (g_fp32) launch_pdl(gla_decode_kernel<GT, true>, dim3(grid), dim3(GD_THREADS), GD_SMEM, st, p, (int)n_items);
+  else launch_pdl(gla_decode_kernel<GT, false>, dim3(grid), dim3(GD_THREADS), GD_SMEM, st, p, (int)n_items);
 }
 
 }  // namespace hymeta

@@ -11,6 +11,8 @@ kv_write_kernel(const __nv_bfloat16* __restrict__ key, const __nv_bfloat16* __re
                 int64_t key_st, int64_t key_sh, int64_t val_st, int64_t val_sh, int64_t kc_sblk,
                 int64_t kc_stok, int64_t kc_sh, int64_t vc_sblk, int64_t vc_stok, int64_t vc_sh) {
   constexpr int CPR = kD / 8;  // 16-byte chunks per head row
+  pdl_wait();
+  pdl_launch_dependents();
   const int64_t total = (int64_t)T * Hkv * CPR;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
        i += (int64_t)gridDim.x * blockDim.x) {
@@ -70,7 +72,7 @@ extern "C" int hymeta_kv_write_paged(const void* key, const void* value, void* k
     if (s % 8) return HYMETA_ERR_INVALID_ARG;  // 16-byte vector access
   const int64_t total = (int64_t)T * Hkv * (kD / 8);
   const int blocks = (int)((total + 255) / 256 < 148 * 16 ? (total + 255) / 256 : 148 * 16);
-  kv_write_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(
+  launch_pdl(kv_write_kernel, dim3(blocks), dim3(256), 0, (cudaStream_t)stream,
       (const __nv_bfloat16*)key, (const __nv_bfloat16*)value, (__nv_bfloat16*)k_cache,
       (__nv_bfloat16*)v_cache, slot_mapping, T, Hkv, block_size, key_st, key_sh, val_st, val_sh,
       kc_sblk, kc_stok, kc_sh, vc_sblk, vc_stok, vc_sh);

@@ -42,7 +42,88 @@ struct SwaDecodeParams {
   int B, H, Hkv, M, block_size, window_left, n_splits, tps, n_hgroups, box_rows;
   float scale_log2;
   int64_t bt_stride, q_sb, q_sh, o_sb, o_sh;
+  // fused paged-KV write of the step's new token (position L-1): null = the pages already hold it
+  const __nv_bfloat16 *new_k, *new_v;
+  __nv_bfloat16 *k_cache, *v_cache;
+  int64_t nk_sb, nk_sh, nv_sb, nv_sh, kc_sblk, kc_stok, kc_sh, vc_sblk, vc_stok, vc_sh;
+  // fused combine: one ticket per (request, kv-head group); null = separate combine kernel
+  int* tickets;
 };
+
+__device__ __forceinline__ float ldcg_f32(const float* p) {
+  float v;
+  asm volatile("ld.global.cg.f32 %0, [%1];" : "=f"(v) : "l"(p));
+  return v;
+}
+
+__device__ __forceinline__ float4 ldcg_f32x4(const float* p) {
+  float4 v;
+  asm volatile("ld.global.cg.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+  return v;
+}
+
+// Split-K combine for the `ng` q-heads h0.. of one (request, kv-head group), run by 128 threads of
+// whichever split CTA finishes last (ticket), or by the combine kernel.  Partials written by other
+// CTAs are read through L2 (ld.cg).  Latency-lean: all lse values are fetched in one round trip,
+// warp w then owns heads w, w+4, ... and keeps every partial-output load of a head in flight at
+// once (lane = 4 columns).  Splits are summed in index order: the result does not depend on which
+// CTA runs it.  s_buf: ng * n_splits floats.
+__device__ __forceinline__ void swa_combine_heads(const SwaDecodeParams& p, int b, int h0, int ng, int tid,
+                                                  float* s_buf) {
+  const int lane = tid & 31, warp = tid >> 5, ns = p.n_splits;
+  const int64_t base0 = ((int64_t)b * p.H + h0) * ns;
+  const int total = ng * ns;
+  for (int i = tid; i < total; i += 128) s_buf[i] = ldcg_f32(p.part_lse + base0 + i);
+  asm volatile("bar.sync 1, 128;" ::: "memory");
+  for (int r = warp; r < ng; r += 4) {
+    float* w = s_buf + r * ns;
+    float mx = -INFINITY;
+    for (int s = lane; s < ns; s += 32) mx = fmaxf(mx, w[s]);
+#pragma unroll
+    for (int o = 16; o; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    float sum = 0.f;
+    for (int s = lane; s < ns; s += 32) {
+      const float e = mx == -INFINITY ? 0.f : exp2f(w[s] - mx);
+      w[s] = e;
+      sum += e;
+    }
+#pragma unroll
+    for (int o = 16; o; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+    __syncwarp();
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    const float* po = p.part_o + (base0 + (int64_t)r * ns) * kD + lane * 4;
+#pragma unroll 8
+    for (int s = 0; s < ns; ++s) {
+      const float e = w[s];
+      float4 o = make_float4(0.f, 0.f, 0.f, 0.f);     // empty splits never wrote their partial
+      if (e != 0.f) o = ldcg_f32x4(po + (int64_t)s * kD);
+      acc.x = fmaf(e, o.x, acc.x); acc.y = fmaf(e, o.y, acc.y);
+      acc.z = fmaf(e, o.z, acc.z); acc.w = fmaf(e, o.w, acc.w);
+    }
+    const float inv = sum > 0.f ? 1.f / sum : 0.f;
+    uint2 pk;
+    pk.x = pack_bf16(acc.x * inv, acc.y * inv);
+    pk.y = pack_bf16(acc.z * inv, acc.w * inv);
+    *reinterpret_cast<uint2*>(p.out + b * p.o_sb + (int64_t)(h0 + r) * p.o_sh + lane * 4) = pk;
+  }
+}
+
+// Ticket: the partials of this CTA are written; returns true in the CTA that arrives last for its
+// (request, kv-head group) -- every other split's partials are then visible to it.  128 threads.
+__device__ __forceinline__ bool swa_take_ticket(const SwaDecodeParams& p, int b, int tid, int* s_flag) {
+  __threadfence();                                         // publish this thread's partial stores
+  asm volatile("bar.sync 1, 128;" ::: "memory");
+  if (tid == 0) {
+    int* t = p.tickets + (int64_t)b * gridDim.y + blockIdx.y;
+    const int old = atomicAdd(t, 1);
+    const int last = old == (int)gridDim.x - 1;
+    if (last) *t = 0;                                      // restore for the next launch
+    *s_flag = last;
+    __threadfence();
+  }
+  asm volatile("bar.sync 1, 128;" ::: "memory");
+  return *s_flag != 0;
+}
 
 // Q tile: [16 rows][128] bf16, 16-byte chunks XOR-swizzled per row (ldmatrix conflict free)
 __device__ __forceinline__ uint32_t swz_q(int r, int c) { return (uint32_t)(r * 256 + ((c ^ (r & 7)) << 4)); }
@@ -62,6 +143,8 @@ swa_decode_split_kernel(const SwaDecodeParams p, const __grid_constant__ CUtenso
   const uint32_t bar_full = sbase + SD_BAR, bar_empty = bar_full + 8 * NST;
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  pdl_wait();                 // seqlens / pages / q come from the kernels ahead in the stream
+  pdl_launch_dependents();
   const int split = blockIdx.x;
   const int hkv = blockIdx.y / p.n_hgroups, hg = blockIdx.y % p.n_hgroups;
   const int b = blockIdx.z;
@@ -85,8 +168,16 @@ swa_decode_split_kernel(const SwaDecodeParams p, const __grid_constant__ CUtenso
   const int64_t part_base = ((int64_t)b * p.H + h0) * p.n_splits + split;  // + row * n_splits
   if (n_tiles == 0) {
     if (tid < ng) p.part_lse[part_base + (int64_t)tid * p.n_splits] = -INFINITY;
+    if (p.tickets && tid < 128) {
+      float* s_buf = reinterpret_cast<float*>(smem + SD_K);
+      if (swa_take_ticket(p, b, tid, reinterpret_cast<int*>(smem + SD_Q)))
+        swa_combine_heads(p, b, h0, ng, tid, s_buf);
+    }
     return;
   }
+  // the step's new token (fused paged-KV write): it lives in tile (L-1)/TK of exactly one real split
+  const int new_it = (p.new_k && !is_meta) ? (L - 1) / TK - t0 : -1;
+  const bool use_new = new_it >= 0 && new_it < n_tiles;
 
   if (tid == 0) {
 #pragma unroll
@@ -159,11 +250,34 @@ swa_decode_split_kernel(const SwaDecodeParams p, const __grid_constant__ CUtenso
   for (int ks = 0; ks < 8; ++ks)
     ldmatrix_x4(qa[ks][0], qa[ks][1], qa[ks][2], qa[ks][3], sQ + swz_q((lm & 1) * 8 + lr, 2 * ks + (lm >> 1)));
 
+  // new-token row: warp (r / 16) patches smem row r = (L-1) % TK of the last tile with new_k/new_v
+  // (lanes 0-15: K chunks, 16-31: V chunks) and, for head group 0, writes the row to its page
+  const int new_r = (L - 1) % TK;
+  const bool new_mine = use_new && warp == (new_r >> 4);
+  uint4 new_x = make_uint4(0, 0, 0, 0);
+  if (new_mine) {
+    const __nv_bfloat16* src = lane < 16 ? p.new_k + b * p.nk_sb + (int64_t)hkv * p.nk_sh
+                                         : p.new_v + b * p.nv_sb + (int64_t)hkv * p.nv_sh;
+    new_x = ldg_nc_v4(src + (lane & 15) * 8);
+    if (hg == 0) {
+      const int pos = L - 1;
+      const int64_t blk = p.block_tables[(int64_t)b * p.bt_stride + pos / p.block_size];
+      const int off = pos % p.block_size;
+      __nv_bfloat16* dst = lane < 16 ? p.k_cache + blk * p.kc_sblk + off * p.kc_stok + (int64_t)hkv * p.kc_sh
+                                     : p.v_cache + blk * p.vc_sblk + off * p.vc_stok + (int64_t)hkv * p.vc_sh;
+      stg_v4(dst + (lane & 15) * 8, new_x);
+    }
+  }
+
   for (int it = 0; it < n_tiles; ++it) {
     const int st = it % NST;
     mbar_wait(bar_full + 8 * st, (it / NST) & 1);
     const uint32_t kst = sK + st * TILE_BYTES, vst = sV + st * TILE_BYTES;
     const int pos0 = (t0 + it) * TK + 16 * warp;
+    if (new_mine && it == new_it) {
+      *reinterpret_cast<uint4*>(smem + (lane < 16 ? SD_K : SD_V) + st * TILE_BYTES + swz_t(new_r, lane & 15)) = new_x;
+      __syncwarp();
+    }
 
     if (pos0 < vlo || pos0 + 16 > vhi) {
       // rows outside [vlo, vhi) may hold uninitialised / recycled cache bytes (NaN patterns):
@@ -281,26 +395,22 @@ swa_decode_split_kernel(const SwaDecodeParams p, const __grid_constant__ CUtenso
     p.part_o[pi * kD + tid] = acc / lt;
     if (tid == 0) p.part_lse[pi] = mm + log2f(lt);
   }
+  if (p.tickets) {
+    asm volatile("bar.sync 1, 128;" ::: "memory");        // sM / sL / sO fully consumed
+    float* s_buf = reinterpret_cast<float*>(smem + SD_K);   // ring is idle: 96 KB >= 16 heads x 1024 splits
+    if (swa_take_ticket(p, b, tid, reinterpret_cast<int*>(smem + SD_Q)))
+      swa_combine_heads(p, b, h0, ng, tid, s_buf);
+  }
 }
 
-// out[b,h,:] = sum_s w_s part_o[b,h,s,:],  w_s = 2^(lse_s - max) / sum  (grid (H, B), 128 threads)
+// Separate combine launch (tickets == null): the same routine, grid (Hkv * head_groups, B), 128 threads
 __global__ void __launch_bounds__(128) swa_decode_combine_kernel(const SwaDecodeParams p) {
-  const int h = blockIdx.x, b = blockIdx.y, d = threadIdx.x;
-  const int64_t base = ((int64_t)b * p.H + h) * p.n_splits;
-  float mm = -INFINITY;
-  for (int s = 0; s < p.n_splits; ++s) mm = fmaxf(mm, p.part_lse[base + s]);
-  float acc = 0.f, wsum = 0.f;
-  if (mm != -INFINITY) {
-    for (int s = 0; s < p.n_splits; ++s) {
-      const float ls = p.part_lse[base + s];
-      if (ls == -INFINITY) continue;
-      const float w = exp2f(ls - mm);
-      wsum += w;
-      acc += w * p.part_o[(base + s) * kD + d];
-    }
-    acc /= wsum;
-  }
-  p.out[b * p.o_sb + h * p.o_sh + d] = __float2bfloat16_rn(acc);
+  extern __shared__ float s_comb[];
+  pdl_wait();
+  pdl_launch_dependents();
+  const int hkv = blockIdx.x / p.n_hgroups, hg = blockIdx.x % p.n_hgroups, b = blockIdx.y;
+  const int G = p.H / p.Hkv;
+  swa_combine_heads(p, b, hkv * G + hg * 16, min(16, G - hg * 16), threadIdx.x, s_comb);
 }
 
 struct SwaDecodePlan { int n_splits, tps, n_hgroups; size_t bytes; };
@@ -320,15 +430,23 @@ static SwaDecodePlan plan_swa_decode(int B, int H, int Hkv, int max_blocks, int 
   if (max_keys < 1) max_keys = 1;
   const int max_tiles = (int)((max_keys + TK - 1) / TK) + 1;  // +1: window start not tile aligned
   const long units = (long)B * Hkv * pl.n_hgroups;
-  // CTAs of ~8 tiles (256 KB of K/V) keep the tail of the last wave short; fewer tiles per CTA
-  // only when the batch alone cannot fill 148 SMs x 2 CTAs a few times over
-  static const int tps_env = env_int("HYMETA_SWA_DEC_TPS", 0);   // tuning knob (0 = heuristic)
-  long tps = tps_env > 0 ? tps_env : 8;
+  // Tiles per CTA, from B200 sweeps (tools/ab_swa_decode.py, B = 1 .. 256 inside a CUDA graph): every
+  // wave of CTAs pays ~2 tile-times of ramp / drain that the co-resident CTA does not hide (the
+  // CTAs of a wave start and end in lock-step), so the best plan is ONE wave of long CTAs: as many
+  // splits as it takes to fill the 2 x 148 CTA slots, never CTAs shorter than 8 tiles (256 KB of
+  // K/V), and a single split per (request, kv-head) once the batch fills the machine by itself.
+  // Config 2 (256 units): 87.7 us per layer-step with one 66-tile CTA per unit against 104.7 us
+  // with nine 8-tile splits.
+  static const int tps_env = env_int("HYMETA_SWA_DEC_TPS", 0);   // tuning knob (0 = rule above)
+  long tps = tps_env;
   if (tps_env <= 0) {
-    const long want = 148L * 2 * 4;   // >= 4 waves of CTAs
-    while (tps > 1 && units * ((max_tiles + tps - 1) / tps) < want) tps >>= 1;
+    long ns = 296 / (units > 0 ? units : 1);
+    if (ns > max_tiles / 8) ns = max_tiles / 8;
+    if (ns < 1) ns = 1;
+    tps = (max_tiles + ns - 1) / ns;
   }
   if (tps > max_tiles) tps = max_tiles;
+  while ((max_tiles + tps - 1) / tps > 1024) tps *= 2;   // the combine keeps 16 x n_splits weights in smem
   pl.tps = (int)tps;
   pl.n_splits = (max_tiles + pl.tps - 1) / pl.tps + (M > 0 ? 1 : 0);
   pl.bytes = (size_t)B * H * pl.n_splits * (kD + 1) * sizeof(float);
@@ -345,14 +463,15 @@ extern "C" size_t hymeta_swa_decode_workspace_bytes(int B, int H, int Hkv, int D
   return plan_swa_decode(B, H, Hkv, max_blocks, block_size, window_left, M).bytes;
 }
 
-extern "C" int hymeta_swa_meta_decode_paged(
-    const void* q, const void* k_cache, const void* v_cache, const int32_t* block_tables,
+extern "C" int hymeta_swa_meta_decode_paged_fused(
+    const void* q, void* k_cache, void* v_cache, const int32_t* block_tables,
     const int32_t* cache_seqlens, const void* meta_k, const void* meta_v, void* out, void* workspace,
     size_t workspace_bytes, int B, int H, int Hkv, int D, int M, int block_size, int num_blocks,
     int max_blocks, int64_t bt_stride, int window_left, float scale, int64_t q_sb, int64_t q_sh,
     int64_t o_sb, int64_t o_sh, int64_t kc_sblk, int64_t kc_stok, int64_t kc_sh, int64_t vc_sblk,
     int64_t vc_stok, int64_t vc_sh, int64_t mk_st, int64_t mk_sh, int64_t mv_st, int64_t mv_sh,
-    void* stream) {
+    const void* new_k, const void* new_v, int64_t nk_sb, int64_t nk_sh, int64_t nv_sb, int64_t nv_sh,
+    int32_t* tickets, void* stream) {
   if (B == 0) return HYMETA_OK;
   if (!q || !k_cache || !v_cache || !block_tables || !cache_seqlens || !out || !workspace || B < 0 ||
       H <= 0 || Hkv <= 0 || M < 0 || block_size <= 0 || max_blocks < 0 || num_blocks <= 0)
@@ -365,6 +484,10 @@ extern "C" int hymeta_swa_meta_decode_paged(
                              M ? mk_st : 0, M ? mk_sh : 0, M ? mv_st : 0, M ? mv_sh : 0};
   for (int64_t s : strides)
     if (s % 8) return HYMETA_ERR_INVALID_ARG;
+  if ((new_k == nullptr) != (new_v == nullptr)) return HYMETA_ERR_INVALID_ARG;
+  if (new_k && ((nk_sb % 8) || (nk_sh % 8) || (nv_sb % 8) || (nv_sh % 8) ||
+                (((uintptr_t)new_k | (uintptr_t)new_v) & 15)))
+    return HYMETA_ERR_INVALID_ARG;
   const SwaDecodePlan pl = plan_swa_decode(B, H, Hkv, max_blocks, block_size, window_left, M);
   if (workspace_bytes < pl.bytes) return HYMETA_ERR_WORKSPACE;
 
@@ -378,6 +501,12 @@ extern "C" int hymeta_swa_meta_decode_paged(
   p.box_rows = block_size % 64 == 0 ? 64 : (block_size % 32 == 0 ? 32 : 16);
   p.scale_log2 = scale * 1.4426950408889634f;
   p.bt_stride = bt_stride; p.q_sb = q_sb; p.q_sh = q_sh; p.o_sb = o_sb; p.o_sh = o_sh;
+  p.new_k = (const __nv_bfloat16*)new_k; p.new_v = (const __nv_bfloat16*)new_v;
+  p.k_cache = (__nv_bfloat16*)k_cache; p.v_cache = (__nv_bfloat16*)v_cache;
+  p.nk_sb = nk_sb; p.nk_sh = nk_sh; p.nv_sb = nv_sb; p.nv_sh = nv_sh;
+  p.kc_sblk = kc_sblk; p.kc_stok = kc_stok; p.kc_sh = kc_sh;
+  p.vc_sblk = vc_sblk; p.vc_stok = vc_stok; p.vc_sh = vc_sh;
+  p.tickets = tickets;
 
   // tensor maps: [D, Hkv, block_size, num_blocks] over the paged caches, [D, Hkv, M, 1] over meta
   CUtensorMap tmK, tmV, tmMK, tmMV;
@@ -403,12 +532,36 @@ extern "C" int hymeta_swa_meta_decode_paged(
   if (!attr_set) {
     cudaFuncSetAttribute(swa_decode_split_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                          SWA_DEC_SMEM);
+    cudaFuncSetAttribute(swa_decode_combine_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                         16 * 1025 * (int)sizeof(float));
     attr_set = true;
   }
   cudaStream_t st = (cudaStream_t)stream;
   dim3 grid(pl.n_splits, Hkv * pl.n_hgroups, B);
-  swa_decode_split_kernel<<<grid, SD_THREADS, SWA_DEC_SMEM, st>>>(p, tmK, tmV, tmMK, tmMV);
-  swa_decode_combine_kernel<<<dim3(H, B), 128, 0, st>>>(p);
-  count_launch(2);
+  launch_pdl(swa_decode_split_kernel, grid, dim3(SD_THREADS), SWA_DEC_SMEM, st, p, tmK, tmV, tmMK, tmMV);
+  if (!tickets)
+    launch_pdl(swa_decode_combine_kernel, dim3(Hkv * pl.n_hgroups, B), dim3(128),
+               (size_t)16 * pl.n_splits * sizeof(float), st, p);
+  count_launch(tickets ? 1 : 2);
   return check_launch();
+}
+
+extern "C" size_t hymeta_swa_decode_ticket_bytes(int B, int H, int Hkv) {
+  if (B <= 0 || H <= 0 || Hkv <= 0 || H % Hkv) return 0;
+  return (size_t)B * Hkv * ((H / Hkv + 15) / 16) * sizeof(int32_t);
+}
+
+extern "C" int hymeta_swa_meta_decode_paged(
+    const void* q, const void* k_cache, const void* v_cache, const int32_t* block_tables,
+    const int32_t* cache_seqlens, const void* meta_k, const void* meta_v, void* out, void* workspace,
+    size_t workspace_bytes, int B, int H, int Hkv, int D, int M, int block_size, int num_blocks,
+    int max_blocks, int64_t bt_stride, int window_left, float scale, int64_t q_sb, int64_t q_sh,
+    int64_t o_sb, int64_t o_sh, int64_t kc_sblk, int64_t kc_stok, int64_t kc_sh, int64_t vc_sblk,
+    int64_t vc_stok, int64_t vc_sh, int64_t mk_st, int64_t mk_sh, int64_t mv_st, int64_t mv_sh,
+    void* stream) {
+  return hymeta_swa_meta_decode_paged_fused(
+      q, const_cast<void*>(k_cache), const_cast<void*>(v_cache), block_tables, cache_seqlens, meta_k,
+      meta_v, out, workspace, workspace_bytes, B, H, Hkv, D, M, block_size, num_blocks, max_blocks,
+      bt_stride, window_left, scale, q_sb, q_sh, o_sb, o_sh, kc_sblk, kc_stok, kc_sh, vc_sblk, vc_stok,
+      vc_sh, mk_st, mk_sh, mv_st, mv_sh, nullptr, nullptr, 0, 0, 0, 0, nullptr, stream);
 }

@@ -216,11 +216,31 @@ def _workspace(nbytes: int, device) -> torch.Tensor:
     return ws
 
 
+_tickets: dict = {}
+
+
+def _ticket_buffer(nbytes: int, device) -> torch.Tensor:
+    """Zero-initialised int32 tickets of the fused split-K combine (the kernel restores zero)."""
+    t = _tickets.get(device.index)
+    if t is None or t.numel() * 4 < nbytes:
+        if torch.cuda.is_current_stream_capturing():
+            raise RuntimeError("ticket buffer must be sized before CUDA-graph capture "
+                               "(run one eager step first)")
+        t = torch.zeros(max((nbytes + 3) // 4, 4096), dtype=torch.int32, device=device)
+        _tickets[device.index] = t
+    return t
+
+
 def swa_meta_decode_paged(q, k_cache, v_cache, block_tables, cache_seqlens, meta_k, meta_v,
                           window_left: int, scale: Optional[float] = None,
-                          out: Optional[torch.Tensor] = None) -> torch.Tensor:
+                          out: Optional[torch.Tensor] = None,
+                          new_k: Optional[torch.Tensor] = None, new_v: Optional[torch.Tensor] = None,
+                          fused_combine: bool = True) -> torch.Tensor:
     """q [B,H,D]; caches [nb,bs,Hkv,D]; block_tables [B,max_blocks] int32; cache_seqlens [B]
-    int32; meta_k/meta_v [M,Hkv,D] or None.  Returns out [B,H,D]."""
+    int32; meta_k/meta_v [M,Hkv,D] or None.  Returns out [B,H,D].
+    new_k/new_v [B,Hkv,D]: K/V of the token at position cache_seqlens[b]-1; the kernel writes them to
+    their page (reshape_and_cache_flash folded in) and attends to them -- no separate kv_write_paged.
+    fused_combine: the split-K partials are merged by the last split CTA (one launch, not two)."""
     B, H, D = q.shape
     Hkv, bs = k_cache.shape[2], k_cache.shape[1]
     M = 0 if meta_k is None else meta_k.shape[0]
@@ -231,6 +251,13 @@ def swa_meta_decode_paged(q, k_cache, v_cache, block_tables, cache_seqlens, meta
     if M:
         _req(meta_k, "meta_k", torch.bfloat16)
         _req(meta_v, "meta_v", torch.bfloat16)
+    if (new_k is None) != (new_v is None):
+        raise ValueError("new_k and new_v must be given together")
+    if new_k is not None:
+        _req(new_k, "new_k", torch.bfloat16)
+        _req(new_v, "new_v", torch.bfloat16)
+        if new_k.shape != (B, Hkv, D) or new_v.shape != (B, Hkv, D):
+            raise ValueError("new_k/new_v must be [B, Hkv, D]")
     if out is None:
         out = torch.empty(B, H, D, dtype=q.dtype, device=q.device)
     if scale is None:
@@ -238,7 +265,9 @@ def swa_meta_decode_paged(q, k_cache, v_cache, block_tables, cache_seqlens, meta
     max_blocks = block_tables.shape[1]
     nbytes = lib().hymeta_swa_decode_workspace_bytes(B, H, Hkv, D, max_blocks, bs, window_left, M)
     ws = _workspace(nbytes, q.device)
-    check(lib().hymeta_swa_meta_decode_paged(
+    tickets = _ticket_buffer(lib().hymeta_swa_decode_ticket_bytes(B, H, Hkv), q.device) \
+        if fused_combine and B > 0 else None
+    check(lib().hymeta_swa_meta_decode_paged_fused(
         _ptr(q), _ptr(k_cache), _ptr(v_cache), _ptr(block_tables), _ptr(cache_seqlens),
         _ptr(meta_k), _ptr(meta_v), _ptr(out), _ptr(ws), ws.numel(),
         B, H, Hkv, D, M, bs, k_cache.shape[0], max_blocks, block_tables.stride(0), int(window_left),
@@ -247,8 +276,12 @@ def swa_meta_decode_paged(q, k_cache, v_cache, block_tables, cache_seqlens, meta
         k_cache.stride(0), k_cache.stride(1), k_cache.stride(2),
         v_cache.stride(0), v_cache.stride(1), v_cache.stride(2),
         meta_k.stride(0) if M else 0, meta_k.stride(1) if M else 0,
-        meta_v.stride(0) if M else 0, meta_v.stride(1) if M else 0, _stream()),
-        "hymeta_swa_meta_decode_paged")
+        meta_v.stride(0) if M else 0, meta_v.stride(1) if M else 0,
+        _ptr(new_k), _ptr(new_v),
+        new_k.stride(0) if new_k is not None else 0, new_k.stride(1) if new_k is not None else 0,
+        new_v.stride(0) if new_v is not None else 0, new_v.stride(1) if new_v is not None else 0,
+        _ptr(tickets), _stream()),
+        "hymeta_swa_meta_decode_paged_fused")
     return out
 
 
