@@ -261,7 +261,7 @@ def test_swa_decode_fused_write_and_combine(ops, case):
     kc_b, vc_b = kc.to(DEV), vc.to(DEV)
     n0 = ops.launch_count()
     out_b = ops.swa_meta_decode_paged(q, kc_b, vc_b, d_tab, d_lens, k2, v2, wl,
-                                      new_k=nk.to(DEV), new_v=nv.to(DEV))
+                                      new_k=nk.to(DEV), new_v=nv.to(DEV), fused_combine=True)
     assert ops.launch_count() - n0 == 1
     torch.cuda.synchronize()
     assert torch.equal(out_a.view(torch.int16), out_b.view(torch.int16))
@@ -274,7 +274,7 @@ def test_swa_decode_fused_write_and_combine(ops, case):
     assert_close(out_b, ref, "fused swa decode")
     # tickets are restored: a second fused call gives the same bits
     out_c = ops.swa_meta_decode_paged(q, kc_b, vc_b, d_tab, d_lens, k2, v2, wl,
-                                      new_k=nk.to(DEV), new_v=nv.to(DEV))
+                                      new_k=nk.to(DEV), new_v=nv.to(DEV), fused_combine=True)
     assert torch.equal(out_c.view(torch.int16), out_b.view(torch.int16))
 
 

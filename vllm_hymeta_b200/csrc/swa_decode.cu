@@ -167,8 +167,13 @@ swa_decode_split_kernel(const SwaDecodeParams p, const __grid_constant__ CUtenso
   const int n_tiles = max(0, t1 - t0);
   const int64_t part_base = ((int64_t)b * p.H + h0) * p.n_splits + split;  // + row * n_splits
   if (n_tiles == 0) {
+    if (p.n_splits == 1) {     // single split: this CTA owns the output rows (no visible key: zeros)
+      if (tid < 128)
+        for (int r = 0; r < ng; ++r) p.out[b * p.o_sb + (int64_t)(h0 + r) * p.o_sh + tid] = __float2bfloat16(0.f);
+      return;
+    }
     if (tid < ng) p.part_lse[part_base + (int64_t)tid * p.n_splits] = -INFINITY;
-    if (p.tickets && tid < 128) {
+    if (p.tickets && tid < 128) {   // (n_splits > 1 here)
       float* s_buf = reinterpret_cast<float*>(smem + SD_K);
       if (swa_take_ticket(p, b, tid, reinterpret_cast<int*>(smem + SD_Q)))
         swa_combine_heads(p, b, h0, ng, tid, s_buf);
@@ -381,8 +386,10 @@ swa_decode_split_kernel(const SwaDecodeParams p, const __grid_constant__ CUtenso
   for (int r = 0; r < ng; ++r) {
     const float mm = fmaxf(fmaxf(sM[r], sM[16 + r]), fmaxf(sM[32 + r], sM[48 + r]));
     const int64_t pi = part_base + (int64_t)r * p.n_splits;
+    __nv_bfloat16* orow = p.out + b * p.o_sb + (int64_t)(h0 + r) * p.o_sh;
     if (mm == -INFINITY) {
-      if (tid == 0) p.part_lse[pi] = -INFINITY;
+      if (p.n_splits == 1) orow[tid] = __float2bfloat16(0.f);
+      else if (tid == 0) p.part_lse[pi] = -INFINITY;
       continue;
     }
     float lt = 0.f, acc = 0.f;
@@ -392,10 +399,11 @@ swa_decode_split_kernel(const SwaDecodeParams p, const __grid_constant__ CUtenso
       lt += wt * sL[w * 16 + r];
       acc += wt * sO[(w * 16 + r) * OS + tid];
     }
+    if (p.n_splits == 1) { orow[tid] = __float2bfloat16_rn(acc / lt); continue; }   // final: no combine pass
     p.part_o[pi * kD + tid] = acc / lt;
     if (tid == 0) p.part_lse[pi] = mm + log2f(lt);
   }
-  if (p.tickets) {
+  if (p.tickets && p.n_splits > 1) {
     asm volatile("bar.sync 1, 128;" ::: "memory");        // sM / sL / sO fully consumed
     float* s_buf = reinterpret_cast<float*>(smem + SD_K);   // ring is idle: 96 KB >= 16 heads x 1024 splits
     if (swa_take_ticket(p, b, tid, reinterpret_cast<int*>(smem + SD_Q)))
@@ -539,10 +547,10 @@ extern "C" int hymeta_swa_meta_decode_paged_fused(
   cudaStream_t st = (cudaStream_t)stream;
   dim3 grid(pl.n_splits, Hkv * pl.n_hgroups, B);
   launch_pdl(swa_decode_split_kernel, grid, dim3(SD_THREADS), SWA_DEC_SMEM, st, p, tmK, tmV, tmMK, tmMV);
-  if (!tickets)
+  if (!tickets && pl.n_splits > 1)
     launch_pdl(swa_decode_combine_kernel, dim3(Hkv * pl.n_hgroups, B), dim3(128),
                (size_t)16 * pl.n_splits * sizeof(float), st, p);
-  count_launch(tickets ? 1 : 2);
+  count_launch(tickets || pl.n_splits == 1 ? 1 : 2);
   return check_launch();
 }
 

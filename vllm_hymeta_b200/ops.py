@@ -235,12 +235,15 @@ def swa_meta_decode_paged(q, k_cache, v_cache, block_tables, cache_seqlens, meta
                           window_left: int, scale: Optional[float] = None,
                           out: Optional[torch.Tensor] = None,
                           new_k: Optional[torch.Tensor] = None, new_v: Optional[torch.Tensor] = None,
-                          fused_combine: bool = True) -> torch.Tensor:
+                          fused_combine: bool = False) -> torch.Tensor:
     """q [B,H,D]; caches [nb,bs,Hkv,D]; block_tables [B,max_blocks] int32; cache_seqlens [B]
     int32; meta_k/meta_v [M,Hkv,D] or None.  Returns out [B,H,D].
     new_k/new_v [B,Hkv,D]: K/V of the token at position cache_seqlens[b]-1; the kernel writes them to
     their page (reshape_and_cache_flash folded in) and attends to them -- no separate kv_write_paged.
-    fused_combine: the split-K partials are merged by the last split CTA (one launch, not two)."""
+    fused_combine: the split-K partials are merged by the last split CTA to finish instead of a
+    second launch (bit-identical; measured no faster on B200, so off by default).  With a single
+    split per (request, kv-head) -- the plan whenever the batch fills the GPU -- the split kernel
+    writes the final rows itself and there is no combine at all."""
     B, H, D = q.shape
     Hkv, bs = k_cache.shape[2], k_cache.shape[1]
     M = 0 if meta_k is None else meta_k.shape[0]
