@@ -155,6 +155,32 @@ int hymeta_kv_write_paged(const void* key, const void* value, void* k_cache, voi
                           int64_t vc_sblk, int64_t vc_stok, int64_t vc_sh, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
+ * f3  Fused SWA prologue: NeoX rotary embedding of q and k + paged-KV write + meta-K/V capture --
+ *     replaces, in one launch, HymetaRotaryEmbedding.forward -> ops.rotary_embedding
+ *     (vllm_hymeta/models/modeling_hymeta.py:220-234, called at :762), the position shift and
+ *     meta-position concat (:1314-1324), reshape_and_cache_flash (meta_attention.py:790-799)
+ *     and the two meta_fattn_cache copy_ calls (modeling_hymeta.py:776-792).
+ * q_in [T,H,D], k_in,v_in [T,Hkv,D] (views of the qkv_proj output); q_out,k_out may alias the
+ * inputs (the reference op is in place).  cos_sin_cache: the module's bf16 table [max_pos, D]
+ * = [cos(pos*inv_freq) | sin(pos*inv_freq)] (modeling_hymeta.py:210-218, cache_dtype bf16 :1187).
+ * Arithmetic = the reference op instantiated for bf16: each product and the add/sub rounded to
+ * bf16 (bit-exact against torch bf16 arithmetic).
+ * Tokens t < n_meta are the meta tokens of the first pass: position t, k/v rows stored into
+ * meta_k/meta_v [n_meta,Hkv,D] instead of pages.  Token t >= n_meta: position
+ * positions[t-n_meta] + pos_offset (pos_offset = num_meta_tokens, :1314), rotated k and v stored
+ * at slot_mapping[t-n_meta] (< 0: not cached).  k_cache == null (profiling run): rotate only.
+ * ---------------------------------------------------------------------------------------------- */
+int hymeta_rope_kv_write_paged(
+    const void* q_in, const void* k_in, const void* v_in, void* q_out, void* k_out,
+    const void* cos_sin_cache, int max_pos, const int64_t* positions, int64_t pos_offset,
+    void* k_cache, void* v_cache, const int64_t* slot_mapping, void* meta_k, void* meta_v,
+    int n_meta, int T, int H, int Hkv, int D, int block_size,
+    int64_t qi_st, int64_t qi_sh, int64_t ki_st, int64_t ki_sh, int64_t vi_st, int64_t vi_sh,
+    int64_t qo_st, int64_t qo_sh, int64_t ko_st, int64_t ko_sh,
+    int64_t kc_sblk, int64_t kc_stok, int64_t kc_sh, int64_t vc_sblk, int64_t vc_stok,
+    int64_t vc_sh, int64_t mk_st, int64_t mk_sh, int64_t mv_st, int64_t mv_sh, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
  * a8  SWA + meta-prefix paged decode -- replaces metatoken_flash_attn_with_kvcache
  *     (vllm_hymeta/attention/fa_kernel_metatoken.py:287-326 -> :124-194 -> :26-106,
  *      i.e. flash_attn fwd_kvcache + meta pass + _update_out_and_lse in ONE pass).

@@ -192,6 +192,42 @@ def rope_neox(x: torch.Tensor, positions: torch.Tensor, theta: float = 1e6) -> t
     return x * cos + torch.cat([-x2, x1], -1) * sin
 
 
+def rope_cos_sin_cache(D: int, max_pos: int, base: float, dtype=torch.bfloat16) -> torch.Tensor:
+    """HymetaRotaryEmbedding._compute_cos_sin_cache (vllm_hymeta/models/modeling_hymeta.py:205-218):
+    [max_pos, D] = [cos | sin] of t * inv_freq, fp32 then cast to cache_dtype (bf16, :1187)."""
+    inv_freq = 1.0 / (base ** (torch.arange(0, D, 2, dtype=torch.float) / D))
+    freqs = torch.einsum("i,j -> ij", torch.arange(max_pos, dtype=torch.float), inv_freq)
+    return torch.cat((freqs.cos(), freqs.sin()), dim=-1).to(dtype)
+
+
+def rope_neox_table(x: torch.Tensor, positions: torch.Tensor, cos_sin: torch.Tensor) -> torch.Tensor:
+    """vLLM's rotary_embedding op (vllm==0.10.0 csrc/pos_encoding_kernels.cu, NeoX branch; call
+    site modeling_hymeta.py:230) in the dtype of ``x``: x' = x*cos - y*sin, y' = y*cos + x*sin with
+    x = head[:D/2], y = head[D/2:], every product and sum rounded to x.dtype (c10::BFloat16
+    operators round after each operation; torch CPU bf16 arithmetic does the same).  x [T,H,D]."""
+    D = x.shape[-1]
+    cs = cos_sin[positions.long()].to(x.dtype)
+    cos, sin = cs[:, None, : D // 2], cs[:, None, D // 2:]
+    a, b = x[..., : D // 2], x[..., D // 2:]
+    return torch.cat([a * cos - b * sin, b * cos + a * sin], -1)
+
+
+def rope_kv_prologue(q, k, v, cos_sin, positions, pos_offset, k_cache, v_cache, slot_mapping,
+                     meta_k=None, meta_v=None, n_meta=0):
+    """The SWA layer prologue around the attention call (modeling_hymeta.py:1314-1324 positions,
+    :762 rotary, :776-792 meta capture, meta_attention.py:790-799 page write), restated step by
+    step.  Returns rotated (q, k); caches / meta_k / meta_v are updated in place."""
+    T = q.shape[0]
+    pos = torch.cat([torch.arange(n_meta, dtype=torch.int64), positions[: T - n_meta] + pos_offset])
+    q, k = rope_neox_table(q, pos, cos_sin), rope_neox_table(k, pos, cos_sin)
+    if n_meta:
+        meta_k[:n_meta].copy_(k[:n_meta])
+        meta_v[:n_meta].copy_(v[:n_meta])
+    if k_cache is not None:
+        kv_write_paged(k[n_meta:], v[n_meta:], k_cache, v_cache, slot_mapping)
+    return q, k
+
+
 def synth_swa_inputs(T: int, H: int, Hkv: int, D: int, seed: int, M: int = 0,
                      pos_offset: int = 0, dtype=torch.bfloat16, theta: float = 1e6):
     """q,k,v ~ N(0,1), RoPE with positions M + t; meta K/V ~ N(0,1)."""

@@ -261,3 +261,65 @@ def test_flash_attention_backend_warmup_then_decode(ops):
                                       [L + 1 for L in lens], k3[:M], v3[:M], W - 1,
                                       out_dtype=torch.float32)
     assert_close(out2.view(2, H, D), ref2, "FlashAttention decode pass")
+
+
+# ------------------------------------------------------------------------------------- f3 (fused prologue)
+def test_flash_attention_fused_prologue_equals_unfused(ops):
+    """``forward_fused(qkv, positions)`` == ``rotary_emb(new_positions, q, k)`` + ``forward``
+    (modeling_hymeta.py:757-796 with the :1314-1324 position shift): output, pages and meta
+    caches bit-identical, on the warm-up pass and on a decode pass."""
+    from vllm_hymeta_b200.attention.meta_attention import MetaAttentionMetadataBuilder, SeqData
+    from vllm_hymeta_b200.models.attention import FlashAttention, HymetaRotaryEmbedding
+    from vllm_hymeta_b200.models.hymeta_cache import HymetaCacheParams
+    H, Hkv, M, bs, W = 14, 2, 128, 16, 64
+    lens = [150, 40]
+    nb = 40
+    gen = torch.Generator().manual_seed(77)
+    perm = torch.randperm(nb, generator=gen).tolist()
+    tables = [perm[:11], perm[11:15]]
+    kv_cache = torch.randn(2, nb, bs, Hkv, D, generator=gen).bfloat16()
+    rot = HymetaRotaryEmbedding(D, D, 4096, 10000, True, torch.bfloat16)
+
+    def run(fused):
+        layer = FlashAttention(H, Hkv, D, num_meta_tokens=M, sliding_window=W)
+        cache = kv_cache.to(DEV)
+        layer.attn.bind_kv_cache(cache)
+        meta_fa = torch.zeros(2, M, Hkv, D, dtype=torch.bfloat16, device=DEV)
+        params = HymetaCacheParams(torch.empty(0), torch.empty(0), meta_fa, torch.empty(0))
+        g2 = torch.Generator().manual_seed(78)
+        outs = []
+        for decode in (False, True):
+            b = MetaAttentionMetadataBuilder(block_size=bs, sliding_window=None, device=DEV)
+            for L, bt in zip(lens, tables):
+                b.add(SeqData(False, L + 1, 1, L, bt) if decode else SeqData(True, L, L, 0, bt))
+            md = b.build()
+            T = 2 if decode else M + sum(lens)
+            qkv = torch.randn(T, (H + 2 * Hkv) * D, generator=g2).bfloat16().to(DEV)
+            pos = (torch.tensor(lens) if decode else
+                   torch.cat([torch.arange(L) for L in lens])).to(DEV)
+            if fused:
+                out = layer.forward_fused(qkv, pos, params, md, rot, has_meta_cache=decode)
+            else:
+                q, k, v = qkv.split([H * D, Hkv * D, Hkv * D], dim=-1)
+                new_pos = pos + M
+                if not decode:
+                    new_pos = torch.cat([torch.arange(M, device=DEV), new_pos])
+                q, k = rot(new_pos, q, k)
+                out = layer.forward(q, k, v, params, md, has_meta_cache=decode)
+            torch.cuda.synchronize()
+            outs.append(out.cpu())
+        return outs, cache.cpu(), meta_fa.cpu()
+
+    (a1, a2), ca, ma = run(False)
+    (b1, b2), cb, mb = run(True)
+    assert torch.isfinite(a1.float()).all() and torch.isfinite(a2.float()).all()
+    assert torch.equal(a1, b1) and torch.equal(a2, b2)
+    assert torch.equal(ca, cb) and torch.equal(ma, mb)
+    # and the rotation itself is the oracle's, bit for bit
+    x = torch.randn(33, H * D, generator=gen).bfloat16()
+    kx = torch.randn(33, Hkv * D, generator=gen).bfloat16()
+    p = torch.randint(0, 4096, (33,), generator=gen)
+    rq, rk = rot(p.to(DEV), x.to(DEV), kx.to(DEV))
+    tab = oswa.rope_cos_sin_cache(D, 4096, 10000)
+    assert torch.equal(rq.cpu().view(33, H, D), oswa.rope_neox_table(x.view(33, H, D), p, tab))
+    assert torch.equal(rk.cpu().view(33, Hkv, D), oswa.rope_neox_table(kx.view(33, Hkv, D), p, tab))

@@ -101,6 +101,39 @@ def test_rope_vs_hf(golden):
     close(ke.transpose(0, 1), g["ke"], 1e-5)
 
 
+def test_rope_table_form_vs_hf(golden):
+    """The vLLM-side table formulation (cos|sin cache + x*cos - y*sin) equals the reference's HF
+    rotary (golden, fp32) when evaluated in fp32; in bf16 it stays within bf16 rounding of it."""
+    g = golden("rope.npz")
+    pos = T(g["pos"]).long()
+    table = swa.rope_cos_sin_cache(128, int(pos.max()) + 1, 1e6, dtype=torch.float32)
+    for x, ref in ((g["q"], g["qe"]), (g["k"], g["ke"])):
+        x = T(x).transpose(0, 1).contiguous()
+        close(swa.rope_neox_table(x, pos, table).transpose(0, 1), ref, 1e-5)
+        lo = swa.rope_neox_table(x.bfloat16(), pos, table.bfloat16()).float().transpose(0, 1)
+        assert (lo - T(ref)).abs().max() <= 2.0 ** -6 * T(ref).abs().max()
+
+
+def test_rope_kv_prologue_semantics():
+    """Prologue restatement: meta rows captured, positions shifted by M, pages hold rotated k."""
+    torch.manual_seed(3)
+    Tn, M, H, Hkv, D, bs = 150, 16, 4, 2, 128, 16
+    q, k, v = (torch.randn(Tn, h, D).bfloat16() for h in (H, Hkv, Hkv))
+    table = swa.rope_cos_sin_cache(D, 4096, 10000.0)
+    positions = torch.arange(Tn - M) + 7
+    cache = torch.zeros(2, 12, bs, Hkv, D, dtype=torch.bfloat16)
+    slots = torch.randperm(12 * bs)[: Tn - M]
+    slots[3] = -1
+    mk, mv = torch.zeros(M, Hkv, D).bfloat16(), torch.zeros(M, Hkv, D).bfloat16()
+    qo, ko = swa.rope_kv_prologue(q, k, v, table, positions, M, cache[0], cache[1], slots, mk, mv, M)
+    assert torch.equal(qo[:M], swa.rope_neox_table(q[:M], torch.arange(M), table))
+    assert torch.equal(ko[M:], swa.rope_neox_table(k[M:], positions + M, table))
+    assert torch.equal(mk, ko[:M]) and torch.equal(mv, v[:M])
+    s = int(slots[0])
+    assert torch.equal(cache[0, s // bs, s % bs], ko[M]) and torch.equal(cache[1, s // bs, s % bs], v[M])
+    assert cache[0].flatten(0, 1)[torch.tensor(sorted(set(range(12 * bs)) - set(slots.tolist())))].abs().sum() == 0
+
+
 def test_decode_step_matches_recurrence():
     """Faithful (bf16-rounding) decode steps track the fp32 recurrence (SURVEY 8c drift)."""
     torch.manual_seed(0)

@@ -408,8 +408,10 @@ class MetaAttentionImpl(AttentionImpl):
         if output_scale is not None:
             raise NotImplementedError("fused output quantization is not supported in MetaAttention.")
         window_size = self.sliding_window
-        if kv_cache.numel() > 0 and key is not None and value is not None:
-            # store the new keys/values in the paged cache first (:790-799)
+        if (kv_cache.numel() > 0 and key is not None and value is not None
+                and not getattr(layer, "kv_already_written", False)):
+            # store the new keys/values in the paged cache first (:790-799); skipped when the
+            # fused RoPE prologue (ops.rope_kv_write_paged) already stored them
             ops.kv_write_paged(key, value, kv_cache[0], kv_cache[1], attn_metadata.slot_mapping.flatten())
         (num_prefill_query_tokens, num_prefill_kv_tokens,
          num_decode_query_tokens) = get_num_prefill_decode_query_kv_tokens(attn_metadata)

@@ -18,6 +18,37 @@ from ..attention.meta_attention import MetaAttentionBackend, MetaAttentionImpl
 from .hymeta_cache import HymetaCacheParams
 
 
+class HymetaRotaryEmbedding:
+    """Reference ``HymetaRotaryEmbedding`` (modeling_hymeta.py:184-234): same constructor, same
+    bf16 cos|sin table, ``forward(positions, query, key)`` rotating in place -- on the sm_100a
+    kernel instead of ``ops.rotary_embedding``.  NeoX style, rotary_dim == head_size only (every
+    reference config, :1181-1188)."""
+
+    def __init__(self, head_size: int, rotary_dim: int, max_position: int, base: float,
+                 is_neox_style: bool = True, cache_dtype: torch.dtype = torch.bfloat16):
+        if not is_neox_style or rotary_dim != head_size:
+            raise NotImplementedError("only NeoX-style full-head rotary is on the Hymeta path")
+        if cache_dtype != torch.bfloat16:
+            raise NotImplementedError("cos_sin_cache is bf16 on the Hymeta path (:1187)")
+        self.head_size, self.rotary_dim = head_size, rotary_dim
+        self.max_position_embeddings, self.base = max_position, base
+        self.is_neox_style, self.cache_dtype = is_neox_style, cache_dtype
+        from .. import ops
+        self.cos_sin_cache = ops.rope_cos_sin_cache(head_size, max_position, base, dtype=cache_dtype)
+
+    def forward(self, positions: torch.Tensor, query: torch.Tensor, key: torch.Tensor):
+        """query [T, H*D], key [T, Hkv*D] (any row stride); rotated in place and returned."""
+        from .. import ops
+        if self.cos_sin_cache.device != positions.device:
+            self.cos_sin_cache = self.cos_sin_cache.to(positions.device)
+        D = self.head_size
+        ops.rope_kv_write_paged(query.view(query.shape[0], -1, D), key.view(key.shape[0], -1, D),
+                                None, self.cos_sin_cache, positions)
+        return query, key
+
+    __call__ = forward
+
+
 class MetaAttention:
     """Reference models/attention.py:25-283 without the vLLM config plumbing: same ``forward``
     arguments; ``attn_metadata`` is passed explicitly instead of through vLLM's forward context."""
@@ -36,6 +67,7 @@ class MetaAttention:
         self.use_output = self.attn_backend.accept_output_buffer
         self.layer_name = prefix
         self.kv_cache = torch.tensor([])          # replaced by bind_kv_cache (reference :170-176)
+        self.kv_already_written = False           # set per call by FlashAttention.forward_fused
 
     def bind_kv_cache(self, kv_cache: torch.Tensor) -> None:
         self.kv_cache = kv_cache
@@ -88,3 +120,39 @@ class FlashAttention:
             v2 = kv_caches.meta_fattn_cache[1]
         return self.attn.forward(q1, k1, v1, query2=q2, key2=k2, value2=v2,
                                  attn_metadata=attn_metadata)
+
+    def forward_fused(self, qkv: torch.Tensor, positions: torch.Tensor, kv_caches: HymetaCacheParams,
+                      attn_metadata, rotary_emb: HymetaRotaryEmbedding,
+                      has_meta_cache: Optional[bool] = False,
+                      is_vllm_testing: bool = False) -> torch.Tensor:
+        """Same result as ``rotary_emb(new_positions, q, k)`` + ``forward`` (modeling_hymeta.py:
+        757-796, positions shifted as :1314-1324) with the prologue in ONE launch:
+        RoPE of q and k in place inside ``qkv`` [T, (H+2Hkv)*D] (the raw ``qkv_proj`` output),
+        rotated k + v stored into their pages, and on the warm-up pass the first M rows stored into
+        ``meta_fattn_cache`` instead.  ``positions`` are the raw (unshifted) positions of the
+        non-meta rows."""
+        from .. import ops
+        M, H, Hkv, D = self.num_meta_tokens, self.num_heads, self.num_kv_heads, self.head_dim
+        T = qkv.shape[0]
+        q, k, v = qkv.split([self.q_size, self.kv_size, self.kv_size], dim=-1)
+        first = (not has_meta_cache) and M > 0 and (not is_vllm_testing)
+        n_meta = M if first else 0
+        kv_cache = self.attn.kv_cache
+        paged = kv_cache.numel() > 0
+        if rotary_emb.cos_sin_cache.device != qkv.device:
+            rotary_emb.cos_sin_cache = rotary_emb.cos_sin_cache.to(qkv.device)
+        ops.rope_kv_write_paged(
+            q.view(T, H, D), k.view(T, Hkv, D), v.view(T, Hkv, D), rotary_emb.cos_sin_cache,
+            positions, M, kv_cache[0] if paged else None, kv_cache[1] if paged else None,
+            attn_metadata.slot_mapping.flatten() if paged else None,
+            kv_caches.meta_fattn_cache[0] if first else None,
+            kv_caches.meta_fattn_cache[1] if first else None, n_meta)
+        q2 = q[:M].reshape(M, H, D) if first else None
+        k2 = kv_caches.meta_fattn_cache[0] if M > 0 else None
+        v2 = kv_caches.meta_fattn_cache[1] if M > 0 else None
+        self.attn.kv_already_written = paged
+        try:
+            return self.attn.forward(q[n_meta:], k[n_meta:], v[n_meta:], query2=q2, key2=k2,
+                                     value2=v2, attn_metadata=attn_metadata)
+        finally:
+            self.attn.kv_already_written = False

@@ -203,6 +203,74 @@ def kv_write_paged(key, value, k_cache, v_cache, slot_mapping) -> None:
         v_cache.stride(0), v_cache.stride(1), v_cache.stride(2), _stream()), "hymeta_kv_write_paged")
 
 
+# ----------------------------------------------------------------------------------- f3
+def rope_cos_sin_cache(head_dim: int, max_position: int, base: float, device=None,
+                       dtype=torch.bfloat16) -> torch.Tensor:
+    """The table HymetaRotaryEmbedding builds (modeling_hymeta.py:205-218): fp32
+    [cos(t*inv_freq) | sin(t*inv_freq)] cast to ``dtype``; [max_position, head_dim]."""
+    inv_freq = 1.0 / (base ** (torch.arange(0, head_dim, 2, dtype=torch.float) / head_dim))
+    freqs = torch.einsum("i,j -> ij", torch.arange(max_position, dtype=torch.float), inv_freq)
+    return torch.cat((freqs.cos(), freqs.sin()), dim=-1).to(dtype).to(device)
+
+
+def rope_kv_write_paged(q, k, v, cos_sin_cache, positions, pos_offset=0, k_cache=None, v_cache=None,
+                        slot_mapping=None, meta_k=None, meta_v=None, n_meta=0, q_out=None,
+                        k_out=None):
+    """NeoX RoPE of q [T,H,D] and k [T,Hkv,D] (in place unless q_out/k_out are given), rotated
+    k and v [T,Hkv,D] written to their pages, the first ``n_meta`` tokens captured into
+    meta_k/meta_v instead -- one launch.  Returns (q_out, k_out)."""
+    T, H, D = q.shape
+    Hkv = k.shape[1]
+    q_out = q if q_out is None else q_out
+    k_out = k if k_out is None else k_out
+    if v is None:                       # rotate only (HymetaRotaryEmbedding.forward)
+        if n_meta > 0 or (k_cache is not None and k_cache.numel() > 0):
+            raise ValueError("v is required when pages or meta rows are written")
+        v = k                           # never dereferenced: no destination for value rows
+    for n, t in (("q", q), ("k", k), ("v", v), ("q_out", q_out), ("k_out", k_out),
+                 ("cos_sin_cache", cos_sin_cache)):
+        _req(t, n, torch.bfloat16)
+    if k.shape[0] != T or v.shape != k.shape or q_out.shape != q.shape or k_out.shape != k.shape:
+        raise ValueError("q/k/v/q_out/k_out shapes disagree")
+    if cos_sin_cache.dim() != 2 or cos_sin_cache.shape[1] != D or not cos_sin_cache.is_contiguous():
+        raise ValueError("cos_sin_cache must be a contiguous [max_position, head_dim] table")
+    if T > n_meta:
+        _req(positions, "positions", torch.int64)
+        if positions.numel() < T - n_meta:
+            raise ValueError("positions shorter than the number of non-meta tokens")
+    paged = k_cache is not None and k_cache.numel() > 0
+    if paged:
+        _req(k_cache, "k_cache", torch.bfloat16)
+        _req(v_cache, "v_cache", torch.bfloat16)
+        _req(slot_mapping, "slot_mapping", torch.int64)
+        if slot_mapping.numel() < T - n_meta:
+            raise ValueError("slot_mapping shorter than the number of non-meta tokens")
+        kc = (k_cache.stride(0), k_cache.stride(1), k_cache.stride(2))
+        vc = (v_cache.stride(0), v_cache.stride(1), v_cache.stride(2))
+        bs = k_cache.shape[1]
+    else:
+        kc = vc = (0, 0, 0)
+        bs = 0
+    if n_meta > 0:
+        _req(meta_k, "meta_k", torch.bfloat16)
+        _req(meta_v, "meta_v", torch.bfloat16)
+        if meta_k.shape[0] < n_meta or meta_v.shape[0] < n_meta:
+            raise ValueError("meta_k/meta_v hold fewer rows than n_meta")
+        mk, mv = (meta_k.stride(0), meta_k.stride(1)), (meta_v.stride(0), meta_v.stride(1))
+    else:
+        mk = mv = (0, 0)
+    check(lib().hymeta_rope_kv_write_paged(
+        _ptr(q), _ptr(k), _ptr(v), _ptr(q_out), _ptr(k_out), _ptr(cos_sin_cache),
+        cos_sin_cache.shape[0], _ptr(positions) if T > n_meta else None, int(pos_offset),
+        _ptr(k_cache) if paged else None, _ptr(v_cache) if paged else None,
+        _ptr(slot_mapping) if paged else None,
+        _ptr(meta_k) if n_meta > 0 else None, _ptr(meta_v) if n_meta > 0 else None,
+        n_meta, T, H, Hkv, D, bs, q.stride(0), q.stride(1), k.stride(0), k.stride(1),
+        v.stride(0), v.stride(1), q_out.stride(0), q_out.stride(1), k_out.stride(0),
+        k_out.stride(1), *kc, *vc, *mk, *mv, _stream()), "hymeta_rope_kv_write_paged")
+    return q_out, k_out
+
+
 # ----------------------------------------------------------------------------------- a8
 def _workspace(nbytes: int, device) -> torch.Tensor:
     key = device.index        # one workspace per device: calls on one device are stream-ordered by the caller
