@@ -36,7 +36,8 @@ typedef enum {
   HYMETA_ERR_UNSUPPORTED = -2,   /* head size / group size / block size not supported  -> ValueError        */
   HYMETA_ERR_WORKSPACE = -3,     /* workspace too small                                -> ValueError        */
   HYMETA_ERR_CUDA = -4,          /* launch failed; see hymeta_last_cuda_error()        -> RuntimeError      */
-  HYMETA_ERR_NO_DEVICE = -5      /* no sm_100 device / driver entry point missing      -> RuntimeError      */
+  HYMETA_ERR_NO_DEVICE = -5,     /* no sm_100 device / driver entry point missing      -> RuntimeError      */
+  HYMETA_ERR_NO_SLOT = -6        /* more live sequences than max_num_seqs state slots  -> RuntimeError      */
 } hymeta_status;
 
 int hymeta_abi_version(void);
@@ -271,6 +272,38 @@ int hymeta_state_zero_slots(void* state, const int32_t* slots, int n, int L,
                             int64_t st_sl, int64_t st_ss, int64_t slot_elems, void* stream);
 int hymeta_state_copy_slot(void* state, int from_slot, int to_slot, int L,
                            int64_t st_sl, int64_t st_ss, int64_t slot_elems, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * f4  Host-side state-slot manager -- replaces the bookkeeping of vLLM 0.10.0's ConstantSizeCache
+ *     inherited by HymetaCacheManager / GLACacheManager (vllm_hymeta/models/hymeta_cache.py:24-63,
+ *     vllm_hymeta/model_for_7B/gla_cache.py:17-32; mapping read at modeling_hymeta.py:1206-1208)
+ *     and batches the per-request slot clearing of modeling_hymeta.py:1202-1227.  No CUDA calls.
+ * prepare(): releases `finished`, then resolves the n (request id, sequence id) pairs of the run
+ * in batch order into slots_out (-1 = PAD_SLOT_ID for a request finished before it ran).  A new
+ * request pops the BACK of the free list (reference order); its slot is appended to new_slots
+ * (zero these with hymeta_state_zero_slots).  A new sequence of a live request forks the
+ * request's first sequence: (copy_from[i], copy_to[i]) pairs to pass to hymeta_state_copy_slot, in
+ * order.  copy_from/copy_to/new_slots need room for n entries.  HYMETA_ERR_NO_SLOT when the free
+ * list runs dry (earlier pairs of the call stay assigned, as in the reference).
+ * slot_of(): slot or -1.  free_list(): copies up to cap entries, returns the full count.
+ * Not thread-safe per manager (one Python thread per worker).
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct hymeta_slot_mgr hymeta_slot_mgr;
+hymeta_slot_mgr* hymeta_slot_mgr_create(int max_slots);
+void hymeta_slot_mgr_destroy(hymeta_slot_mgr* mgr);
+int hymeta_slot_mgr_release(hymeta_slot_mgr* mgr, const char* const* finished, int n_finished);
+int hymeta_slot_mgr_prepare(hymeta_slot_mgr* mgr, const char* const* req_ids,
+                            const int64_t* seq_ids, int n, const char* const* finished,
+                            int n_finished, int32_t* slots_out, int32_t* copy_from,
+                            int32_t* copy_to, int* n_copies, int32_t* new_slots, int* n_new);
+int hymeta_slot_mgr_free_count(const hymeta_slot_mgr* mgr);
+int hymeta_slot_mgr_free_list(const hymeta_slot_mgr* mgr, int32_t* out, int cap);
+int hymeta_slot_mgr_slot_of(const hymeta_slot_mgr* mgr, const char* req_id, int64_t seq_id);
+int hymeta_slot_mgr_live_count(const hymeta_slot_mgr* mgr);
+/* Enumerate live (request id, sequence id, slot) triples; ids NUL-separated, one per triple.
+ * Returns the triple count, *ids_bytes = bytes the ids need; writes only within the capacities. */
+int hymeta_slot_mgr_live(const hymeta_slot_mgr* mgr, char* ids_buf, size_t ids_cap,
+                         size_t* ids_bytes, int64_t* seq_ids, int32_t* slots, int cap);
 
 /* Built-in self test of the tcgen05 / TMA building blocks (descriptor encodings, swizzles).
  * Runs small GEMMs on the current device and compares with a CUDA-core result.

@@ -152,3 +152,74 @@ def test_plugin_entry_points_do_not_touch_cuda():
     assert P.get_attn_backend_cls(None, 128, None, None, 256, False, False) == \
         "vllm_hymeta_b200.attention.meta_attention.MetaAttentionBackend"
     assert not torch.cuda.is_initialized()
+
+
+# ------------------------------------------------------------------------------------- f4 (native slot manager)
+def test_native_slot_manager_matches_python_spec_on_random_traces():
+    """The C++ manager behind the C ABI (csrc/slot_mgr.cu) against the Python restatement of
+    ConstantSizeCache on random admit / fork / finish traces: same slots, same fork copies in the
+    same order, same free list, same live map -- bit-exact."""
+    import random
+    from vllm_hymeta_b200.slot_cache import NativeSlotAllocator
+    rng = random.Random(0)
+    for trial in range(20):
+        cap = rng.choice([1, 4, 17, 64])
+        py, nat = SlotAllocator(cap), NativeSlotAllocator(cap)
+        live, next_id = {}, 0
+        for step in range(60):
+            finished = [r for r in list(live) if rng.random() < 0.2]
+            for r in finished:
+                live.pop(r)
+            if rng.random() < 0.15:
+                finished.append(f"ghost-{step}")              # finished but never seen
+            batch = {r: list(s) for r, s in live.items() if rng.random() < 0.8}
+            for _ in range(rng.randint(0, 3)):                # admit
+                batch[f"req-{next_id}"] = [next_id * 10]
+                next_id += 1
+            for r in list(batch):                             # fork siblings
+                if rng.random() < 0.15:
+                    batch[r].append(batch[r][-1] + 1)
+            if rng.random() < 0.1 and batch:                  # finished before it ever ran
+                finished.append(next(iter(batch)))
+            pc, nc_ = [], []
+            err_py = err_nat = None
+            try:
+                sp = py.prepare(batch, finished, lambda a, b: pc.append((a, b)))
+            except RuntimeError as e:
+                err_py = str(e)
+            try:
+                sn = nat.prepare(batch, finished, lambda a, b: nc_.append((a, b)))
+            except RuntimeError as e:
+                err_nat = str(e)
+            assert (err_py is None) == (err_nat is None), (trial, step, err_py, err_nat)
+            assert pc == nc_
+            assert py.free_cache_indices == nat.free_cache_indices
+            assert py.cache_indices_mapping == nat.cache_indices_mapping
+            assert sorted(py.live()) == sorted(nat.live())
+            if err_py is not None:
+                break
+            assert sp == sn
+            for r, seqs in batch.items():
+                if r not in finished:
+                    live[r] = seqs
+            live = {r: s for r, s in live.items() if r in py.cache_indices_mapping}
+
+
+def test_native_slot_manager_batch_outputs_and_errors():
+    from vllm_hymeta_b200.slot_cache import NativeSlotAllocator
+    a = NativeSlotAllocator(3)
+    slots, copies, new = a.prepare_batch({"a": [0], "b": [1]}, [])
+    assert slots == [2, 1] and copies == [] and new == [2, 1]
+    slots, copies, new = a.prepare_batch({"a": [0, 5], "b": [1]}, [])
+    assert slots == [2, 0, 1] and copies == [(2, 0)] and new == []
+    assert a.slot_of("a", 5) == 0 and a.free_cache_indices == []
+    with pytest.raises(RuntimeError):
+        a.prepare_batch({"c": [9]}, [])
+    with pytest.raises(KeyError):
+        a.slot_of("zz", 0)
+    slots, _, new = a.prepare_batch({"c": [9]}, ["a", "c2"])
+    assert slots == [0] and new == [0] and a.free_cache_indices == [2]   # LIFO: a's 2 then 0 freed
+    a.release(["b", "c"])
+    assert sorted(a.free_cache_indices) == [0, 1, 2] and a.live() == []
+    assert a.prepare_batch({}, []) == ([], [], [])
+    assert a.prepare_batch({"x": [1]}, ["x"])[0] == [PAD_SLOT_ID]

@@ -37,6 +37,15 @@ SIGNATURES = {
     "hymeta_state_zero_slots": (_i, [_p, _p, _i, _i, _i64, _i64, _i64, _p]),
     "hymeta_state_copy_slot": (_i, [_p, _i, _i, _i, _i64, _i64, _i64, _p]),
     "hymeta_selftest_umma": (_i, [_p]),
+    "hymeta_slot_mgr_create": (_p, [_i]),
+    "hymeta_slot_mgr_destroy": (None, [_p]),
+    "hymeta_slot_mgr_release": (_i, [_p, _p, _i]),
+    "hymeta_slot_mgr_prepare": (_i, [_p, _p, _p, _i, _p, _i] + [_p] * 6),
+    "hymeta_slot_mgr_free_count": (_i, [_p]),
+    "hymeta_slot_mgr_free_list": (_i, [_p, _p, _i]),
+    "hymeta_slot_mgr_slot_of": (_i, [_p, C.c_char_p, _i64]),
+    "hymeta_slot_mgr_live_count": (_i, [_p]),
+    "hymeta_slot_mgr_live": (_i, [_p, _p, _sz, _p, _p, _p, _i]),
 }
 
 _lib = None

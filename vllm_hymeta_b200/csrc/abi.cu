@@ -27,6 +27,7 @@ extern "C" const char* hymeta_status_string(int status) {
     case HYMETA_ERR_WORKSPACE: return "workspace too small";
     case HYMETA_ERR_CUDA: return "CUDA launch failed";
     case HYMETA_ERR_NO_DEVICE: return "no sm_100 device or driver entry point unavailable";
+    case HYMETA_ERR_NO_SLOT: return "no free state slot: more live sequences than max_num_seqs";
     default: return "unknown status";
   }
 }

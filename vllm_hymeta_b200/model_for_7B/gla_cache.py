@@ -8,7 +8,7 @@ from typing import List
 
 import torch
 
-from ..slot_cache import PAD_SLOT_ID, SlotAllocator
+from ..slot_cache import PAD_SLOT_ID, NativeSlotAllocator
 
 
 def _empty():
@@ -24,7 +24,7 @@ class GLACacheParams:
         return GLACacheParams(self.gla_cache[layer_idx, ...], self.state_indices_tensor)
 
 
-class GLACacheManager(SlotAllocator):
+class GLACacheManager(NativeSlotAllocator):
 
     def __init__(self, dtype, cache_shape, device="cuda"):
         super().__init__(cache_shape[1])

@@ -16,7 +16,7 @@ from typing import List
 
 import torch
 
-from ..slot_cache import PAD_SLOT_ID, SlotAllocator
+from ..slot_cache import PAD_SLOT_ID, NativeSlotAllocator
 
 
 def _empty():
@@ -38,7 +38,7 @@ class HymetaCacheParams:
                                  self.state_indices_tensor)
 
 
-class HymetaCacheManager(SlotAllocator):
+class HymetaCacheManager(NativeSlotAllocator):
 
     def __init__(self, dtype, cache_shape, meta_linear_cache_shape, meta_fattn_cache_shape,
                  device="cuda"):

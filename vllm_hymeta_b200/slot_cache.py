@@ -64,3 +64,102 @@ class SlotAllocator:
 
     def live(self) -> List[Tuple[str, int, int]]:
         return [(r, s, sl) for r, m in self.cache_indices_mapping.items() for s, sl in m.items()]
+
+
+class NativeSlotAllocator:
+    """Same contract as :class:`SlotAllocator`, bookkeeping in the C++ manager behind the C ABI
+    (``hymeta_slot_mgr_*``, csrc/slot_mgr.cu).  ``prepare_batch`` resolves a whole run
+    in one native call and returns the fork copies and the freshly admitted slots so the caller
+    batches the device work (one zero-fill launch per batch instead of one per request per layer,
+    reference modeling_hymeta.py:1202-1227)."""
+
+    def __init__(self, max_batch_size: int):
+        import ctypes as C
+        from ._lib import lib
+        self._C, self._lib = C, lib()
+        self.max_batch_size = max_batch_size
+        self.last_new_slots: List[int] = []      # slots admitted by the latest prepare()
+        self._h = self._lib.hymeta_slot_mgr_create(max_batch_size)
+        if not self._h:
+            raise ValueError("max_batch_size must be >= 0")
+
+    def __del__(self):
+        h, self._h = getattr(self, "_h", None), None
+        if h:
+            self._lib.hymeta_slot_mgr_destroy(h)
+
+    def _ids(self, ids):
+        arr = (self._C.c_char_p * len(ids))(*[i.encode() for i in ids])
+        return arr
+
+    def prepare_batch(self, request_ids_to_seq_ids: Dict[str, List[int]],
+                      finished_requests_ids: List[str]):
+        """-> (slots, [(from, to) forks in order], [new slots])."""
+        C = self._C
+        reqs = [r for r, seqs in request_ids_to_seq_ids.items() for _ in seqs]
+        seqs = [s for ss in request_ids_to_seq_ids.values() for s in ss]
+        n = len(reqs)
+        slots, cf, ct, new = ((C.c_int32 * max(n, 1))() for _ in range(4))
+        nc, nn = C.c_int(0), C.c_int(0)
+        st = self._lib.hymeta_slot_mgr_prepare(
+            self._h, self._ids(reqs), (C.c_int64 * max(n, 1))(*seqs), n,
+            self._ids(finished_requests_ids), len(finished_requests_ids), slots, cf, ct,
+            C.byref(nc), new, C.byref(nn))
+        if st == -6:
+            # pairs resolved before the free list ran dry stay assigned (as in the reference):
+            # hand their forks / new slots to the caller with the error
+            e = RuntimeError("no free state slot: more live sequences than max_num_seqs")
+            e.copies, e.new_slots = list(zip(cf[:nc.value], ct[:nc.value])), list(new[:nn.value])
+            raise e
+        if st != 0:
+            raise ValueError(f"hymeta_slot_mgr_prepare: status {st}")
+        return (list(slots[:n]), list(zip(cf[:nc.value], ct[:nc.value])), list(new[:nn.value]))
+
+    def prepare(self, request_ids_to_seq_ids: Dict[str, List[int]], finished_requests_ids: List[str],
+                copy_fn) -> List[int]:
+        try:
+            slots, copies, self.last_new_slots = self.prepare_batch(request_ids_to_seq_ids,
+                                                                    finished_requests_ids)
+        except RuntimeError as e:
+            for src, dst in getattr(e, "copies", []):
+                copy_fn(src, dst)
+            self.last_new_slots = getattr(e, "new_slots", [])
+            raise
+        for src, dst in copies:
+            copy_fn(src, dst)
+        return slots
+
+    def release(self, finished_requests_ids: List[str]) -> None:
+        self._lib.hymeta_slot_mgr_release(self._h, self._ids(finished_requests_ids),
+                                          len(finished_requests_ids))
+
+    def slot_of(self, req_id: str, seq_id: int) -> int:
+        s = self._lib.hymeta_slot_mgr_slot_of(self._h, req_id.encode(), seq_id)
+        if s < 0:
+            raise KeyError((req_id, seq_id))
+        return s
+
+    @property
+    def free_cache_indices(self) -> List[int]:
+        n = self._lib.hymeta_slot_mgr_free_count(self._h)
+        buf = (self._C.c_int32 * max(n, 1))()
+        self._lib.hymeta_slot_mgr_free_list(self._h, buf, n)
+        return list(buf[:n])
+
+    def live(self) -> List[Tuple[str, int, int]]:
+        C = self._C
+        need = C.c_size_t(0)
+        n = self._lib.hymeta_slot_mgr_live(self._h, None, 0, C.byref(need), None, None, 0)
+        ids = C.create_string_buffer(max(need.value, 1))
+        seqs, slots = (C.c_int64 * max(n, 1))(), (C.c_int32 * max(n, 1))()
+        self._lib.hymeta_slot_mgr_live(self._h, ids, need.value, C.byref(need), seqs, slots, n)
+        names = ids.raw[:need.value].split(b"\0")[:n]
+        return [(names[i].decode(), int(seqs[i]), int(slots[i])) for i in range(n)]
+
+    @property
+    def cache_indices_mapping(self) -> Dict[str, Dict[int, int]]:
+        """Snapshot in the shape the model reads (modeling_hymeta.py:1206-1208)."""
+        out: Dict[str, Dict[int, int]] = {}
+        for r, s, sl in self.live():
+            out.setdefault(r, {})[s] = sl
+        return out
