@@ -286,14 +286,15 @@ int hymeta_state_copy_slot(void* state, int from_slot, int to_slot, int L,
  * order.  copy_from/copy_to/new_slots need room for n entries.  HYMETA_ERR_NO_SLOT when the free
  * list runs dry (earlier pairs of the call stay assigned, as in the reference).
  * slot_of(): slot or -1.  free_list(): copies up to cap entries, returns the full count.
+ * Id lists (req_ids, finished) are PACKED: n NUL-terminated strings back to back.
  * Not thread-safe per manager (one Python thread per worker).
  * ---------------------------------------------------------------------------------------------- */
 typedef struct hymeta_slot_mgr hymeta_slot_mgr;
 hymeta_slot_mgr* hymeta_slot_mgr_create(int max_slots);
 void hymeta_slot_mgr_destroy(hymeta_slot_mgr* mgr);
-int hymeta_slot_mgr_release(hymeta_slot_mgr* mgr, const char* const* finished, int n_finished);
-int hymeta_slot_mgr_prepare(hymeta_slot_mgr* mgr, const char* const* req_ids,
-                            const int64_t* seq_ids, int n, const char* const* finished,
+int hymeta_slot_mgr_release(hymeta_slot_mgr* mgr, const char* finished, int n_finished);
+int hymeta_slot_mgr_prepare(hymeta_slot_mgr* mgr, const char* req_ids,
+                            const int64_t* seq_ids, int n, const char* finished,
                             int n_finished, int32_t* slots_out, int32_t* copy_from,
                             int32_t* copy_to, int* n_copies, int32_t* new_slots, int* n_new);
 int hymeta_slot_mgr_free_count(const hymeta_slot_mgr* mgr);

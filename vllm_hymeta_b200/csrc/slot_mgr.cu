@@ -25,10 +25,11 @@ struct hymeta_slot_mgr {
 };
 
 namespace {
-void release_ids(hymeta_slot_mgr* m, const char* const* ids, int n) {
-  for (int i = 0; i < n; ++i) {
-    if (!ids[i]) continue;
-    auto it = m->map.find(ids[i]);
+// ids arrive packed: n NUL-terminated strings back to back (one marshalling step on the caller's side)
+inline const char* next_id(const char* p) { return p + strlen(p) + 1; }
+void release_ids(hymeta_slot_mgr* m, const char* ids, int n) {
+  for (int i = 0; i < n; ++i, ids = next_id(ids)) {
+    auto it = m->map.find(ids);
     if (it == m->map.end()) continue;
     for (auto& kv : it->second) m->free_list.push_back(kv.second);
     m->map.erase(it);
@@ -47,15 +48,15 @@ extern "C" hymeta_slot_mgr* hymeta_slot_mgr_create(int max_slots) {
 
 extern "C" void hymeta_slot_mgr_destroy(hymeta_slot_mgr* m) { delete m; }
 
-extern "C" int hymeta_slot_mgr_release(hymeta_slot_mgr* m, const char* const* finished,
+extern "C" int hymeta_slot_mgr_release(hymeta_slot_mgr* m, const char* finished,
                                        int n_finished) {
   if (!m || n_finished < 0 || (n_finished > 0 && !finished)) return HYMETA_ERR_INVALID_ARG;
   release_ids(m, finished, n_finished);
   return HYMETA_OK;
 }
 
-extern "C" int hymeta_slot_mgr_prepare(hymeta_slot_mgr* m, const char* const* req_ids,
-                                       const int64_t* seq_ids, int n, const char* const* finished,
+extern "C" int hymeta_slot_mgr_prepare(hymeta_slot_mgr* m, const char* req_ids,
+                                       const int64_t* seq_ids, int n, const char* finished,
                                        int n_finished, int32_t* slots_out, int32_t* copy_from,
                                        int32_t* copy_to, int* n_copies, int32_t* new_slots,
                                        int* n_new) {
@@ -65,12 +66,12 @@ extern "C" int hymeta_slot_mgr_prepare(hymeta_slot_mgr* m, const char* const* re
     return HYMETA_ERR_INVALID_ARG;
   release_ids(m, finished, n_finished);
   std::unordered_set<std::string> done;
-  for (int i = 0; i < n_finished; ++i)
-    if (finished[i]) done.insert(finished[i]);
+  const char* f = finished;
+  for (int i = 0; i < n_finished; ++i, f = next_id(f)) done.insert(f);
   int nc = 0, nn = 0;
-  for (int i = 0; i < n; ++i) {
-    if (!req_ids[i]) return HYMETA_ERR_INVALID_ARG;
-    const std::string r(req_ids[i]);
+  const char* rp = req_ids;
+  for (int i = 0; i < n; ++i, rp = next_id(rp)) {
+    const std::string r(rp);
     if (!done.empty() && done.count(r)) {  // finished before it ever ran
       slots_out[i] = -1;
       continue;

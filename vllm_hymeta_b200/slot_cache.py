@@ -8,6 +8,7 @@ zero-fill, slot copy) goes through the C-ABI kernels.
 """
 from __future__ import annotations
 
+from array import array
 from typing import Dict, List, Tuple
 
 PAD_SLOT_ID = -1      # vllm.attention.backends.utils.PAD_SLOT_ID
@@ -88,23 +89,28 @@ class NativeSlotAllocator:
         if h:
             self._lib.hymeta_slot_mgr_destroy(h)
 
-    def _ids(self, ids):
-        arr = (self._C.c_char_p * len(ids))(*[i.encode() for i in ids])
-        return arr
+    @staticmethod
+    def _ids(ids) -> bytes:
+        """Packed id list: NUL-terminated strings back to back (one encode for the batch)."""
+        return ("\0".join(ids) + "\0").encode() if ids else b"\0"
 
     def prepare_batch(self, request_ids_to_seq_ids: Dict[str, List[int]],
                       finished_requests_ids: List[str]):
         """-> (slots, [(from, to) forks in order], [new slots])."""
         C = self._C
         reqs = [r for r, seqs in request_ids_to_seq_ids.items() for _ in seqs]
-        seqs = [s for ss in request_ids_to_seq_ids.values() for s in ss]
+        seqs = array("q", [s for ss in request_ids_to_seq_ids.values() for s in ss])
         n = len(reqs)
-        slots, cf, ct, new = ((C.c_int32 * max(n, 1))() for _ in range(4))
+        out = array("i", bytes(16 * max(n, 1)))           # slots | copy_from | copy_to | new
+        base, _ = out.buffer_info()
+        slots, cf, ct, new = (base + 4 * i * max(n, 1) for i in range(4))
         nc, nn = C.c_int(0), C.c_int(0)
         st = self._lib.hymeta_slot_mgr_prepare(
-            self._h, self._ids(reqs), (C.c_int64 * max(n, 1))(*seqs), n,
+            self._h, self._ids(reqs), seqs.buffer_info()[0], n,
             self._ids(finished_requests_ids), len(finished_requests_ids), slots, cf, ct,
             C.byref(nc), new, C.byref(nn))
+        m = max(n, 1)
+        slots, cf, ct, new = (out[i * m:(i + 1) * m] for i in range(4))
         if st == -6:
             # pairs resolved before the free list ran dry stay assigned (as in the reference):
             # hand their forks / new slots to the caller with the error
@@ -113,7 +119,7 @@ class NativeSlotAllocator:
             raise e
         if st != 0:
             raise ValueError(f"hymeta_slot_mgr_prepare: status {st}")
-        return (list(slots[:n]), list(zip(cf[:nc.value], ct[:nc.value])), list(new[:nn.value]))
+        return (slots[:n].tolist(), list(zip(cf[:nc.value], ct[:nc.value])), new[:nn.value].tolist())
 
     def prepare(self, request_ids_to_seq_ids: Dict[str, List[int]], finished_requests_ids: List[str],
                 copy_fn) -> List[int]:
