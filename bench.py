@@ -366,10 +366,22 @@ def run_gpu(args):
     }
     for kk in kernels.values():
         kk["frac"] = kk["achieved"] / kk["peak"]
+    # DRAM bytes per launch from the committed `ncu --set full` captures (profiles/traffic.json)
+    traffic = {}
+    try:
+        with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "traffic.json")) as f:
+            traffic = json.load(f)
+    except OSError:
+        pass
+    for name, kk in kernels.items():
+        kk["traffic"] = traffic.get(name, {}).get("bytes_per_launch")
     dom = max(kernels, key=lambda x: kernels[x]["share"])
     roofline = {"kernel": dom, "bound": kernels[dom]["bound"], "achieved": kernels[dom]["achieved"],
                 "peak": kernels[dom]["peak"], "unit": kernels[dom]["unit"], "frac": kernels[dom]["frac"],
-                "traffic": None, "peak_source": f"{peaks['src']} (MEASURED_PEAKS.json, sustained)",
+                "traffic": traffic.get(dom, {}).get("bytes_per_launch"),
+                "traffic_source": traffic.get(dom, {}).get("source"),
+                "algorithmic_bytes_per_launch": swa_dec_bytes if dom == "swa_decode" else None,
+                "peak_source": f"{peaks['src']} (MEASURED_PEAKS.json, sustained)",
                 "note": "the decode figure is one fused launch per layer-step (paged-KV write + split-K + combine)"}
 
     # ---- e2e: the same step through the public ops with HOST buffers (pinned), copies timed

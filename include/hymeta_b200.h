@@ -117,6 +117,31 @@ int hymeta_gla_prefill_varlen_seg(const void* q, const void* k, const void* v, c
                                   size_t workspace_bytes, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
+ * f2  GLA kernels with the 7B per-head g_norm fused as epilogue -- additionally replaces
+ *     `o = self.g_norm(o)` (vllm_hymeta/model_for_7B/gla_attention.py:177 RMSNorm(head_dim, eps),
+ *     applied at :210 after fused_chunk_gla and :233 after my_fused_recurrent_gla).
+ * Same arguments as hymeta_gla_decode / hymeta_gla_prefill_varlen_seg plus gnorm_weight
+ * ([D] bf16, 16-byte aligned; null = no norm, identical to the plain entry points) and gnorm_eps.
+ * Arithmetic = vLLM's rms_norm op on the bf16 kernel output: x = bf16(o); rstd =
+ * rsqrt(mean(x^2) + eps) in fp32; y = bf16(bf16(x * rstd) * w).
+ * ---------------------------------------------------------------------------------------------- */
+int hymeta_gla_decode_gnorm(const void* q, const void* k, const void* v, const void* g, void* o,
+                            void* state, const int32_t* slot_idx, int B, int H, int Hk, int Hv,
+                            int Hs, int D, int64_t q_sb, int64_t q_sh, int64_t k_sb, int64_t k_sh,
+                            int64_t v_sb, int64_t v_sh, int64_t g_sb, int64_t g_sh,
+                            int64_t o_sb, int64_t o_sh, int64_t st_ss, int64_t st_sh,
+                            int g_is_fp32, float scale, const void* gnorm_weight, float gnorm_eps,
+                            void* stream);
+int hymeta_gla_prefill_varlen_seg_gnorm(
+    const void* q, const void* k, const void* v, const void* g, void* o, void* state,
+    const void* meta_state, const int32_t* cu_seqlens, const int32_t* slot_idx,
+    const int32_t* init_mode, int N, int T, int H, int Hk, int Hv, int Hs, int D, int64_t q_st,
+    int64_t q_sh, int64_t k_st, int64_t k_sh, int64_t v_st, int64_t v_sh, int64_t g_st,
+    int64_t g_sh, int64_t o_st, int64_t o_sh, int64_t st_ss, int64_t st_sh, int64_t meta_sh,
+    int g_is_fp32, float scale, int write_state, int max_seqlen, int seg_len, void* workspace,
+    size_t workspace_bytes, const void* gnorm_weight, float gnorm_eps, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
  * a4  GLA feature map + gate pre-processing -- replaces the eager torch elementwise chain between
  *     qkv_proj and the GLA kernels:
  *       70B  vllm_hymeta/models/modeling_hymeta.py:598-629 (relu(q); sigmoid(float(k)); clamp or

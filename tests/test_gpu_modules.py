@@ -323,3 +323,62 @@ def test_flash_attention_fused_prologue_equals_unfused(ops):
     tab = oswa.rope_cos_sin_cache(D, 4096, 10000)
     assert torch.equal(rq.cpu().view(33, H, D), oswa.rope_neox_table(x.view(33, H, D), p, tab))
     assert torch.equal(rk.cpu().view(33, Hkv, D), oswa.rope_neox_table(kx.view(33, Hkv, D), p, tab))
+
+
+# ------------------------------------------------------------------------------------- f2 (g_norm epilogue)
+def _assert_ulp_close(got, ref, what, max_frac=0.02):
+    """Same bf16 arithmetic up to the fp32 summation order of the variance and rsqrt rounding: a
+    flipped first rounding (x * rstd) is one bf16 ulp, which the multiplication by w can turn into
+    two ulps of the result -- every element within that, all but a small fraction bit-identical."""
+    got, ref = got.float().cpu(), ref.float().cpu()
+    assert torch.isfinite(got).all(), what
+    diff = (got - ref).abs()
+    assert (diff <= 2.0 ** -6 * ref.abs() + 1e-30).all(), f"{what}: more than two bf16 ulps apart"
+    frac = (diff > 0).float().mean().item()
+    assert frac <= max_frac, f"{what}: {frac:.3%} of elements differ"
+
+
+@pytest.mark.parametrize("H,Hkv,gdt", [(28, 4, torch.bfloat16), (7, 1, torch.bfloat16),
+                                        (8, 8, torch.float32), (6, 2, torch.bfloat16)])
+def test_gnorm_epilogue_decode(ops, H, Hkv, gdt):
+    """Fused g_norm == the kernel's own bf16 output followed by the reference RMSNorm arithmetic
+    (gla_attention.py:233), and the state update is bit-identical with and without the epilogue."""
+    B = 37
+    gen = torch.Generator().manual_seed(H)
+    q = torch.randn(B, H, D, generator=gen).relu().bfloat16().to(DEV)
+    k = torch.randn(B, Hkv, D, generator=gen).relu().bfloat16().to(DEV)
+    v = torch.randn(B, Hkv, D, generator=gen).bfloat16().to(DEV)
+    g = (-torch.rand(B, Hkv, D, generator=gen) * 0.1).to(gdt).to(DEV)
+    w = (1 + 0.1 * torch.randn(D, generator=gen)).bfloat16()
+    state = (torch.randn(B + 2, Hkv, D, D, generator=gen) * 0.2).bfloat16()
+    slots = torch.randperm(B + 2, generator=gen)[:B].to(torch.int32)
+    slots[3] = -1
+    s_a, s_b = state.to(DEV), state.to(DEV)
+    plain = ops.gla_decode(q, k, v, g, s_a, slots.to(DEV))
+    fused = ops.gla_decode(q, k, v, g, s_b, slots.to(DEV), gnorm_weight=w.to(DEV), gnorm_eps=1e-6)
+    torch.cuda.synchronize()
+    assert torch.equal(s_a, s_b)
+    _assert_ulp_close(fused, ogla.rms_norm_head(plain.cpu(), w, 1e-6), f"decode g_norm H={H}/{Hkv}")
+    assert (fused[3] == 0).all()                                  # PAD slot row stays zero
+
+
+@pytest.mark.parametrize("lens,seg_len", [([100, 333, 16, 1], 0), ([1500], 256)])
+def test_gnorm_epilogue_prefill(ops, lens, seg_len):
+    H, Hkv, T, N = 28, 4, sum(lens), len(lens)
+    q, k, v, g = ogla.synth_gla_inputs(T, H, Hkv, D, "7b", seed=T)
+    gen = torch.Generator().manual_seed(3)
+    w = (1 + 0.1 * torch.randn(D, generator=gen)).bfloat16()
+    cu = [0]
+    for L in lens:
+        cu.append(cu[-1] + L)
+    i32 = lambda x: torch.tensor(x, dtype=torch.int32, device=DEV)
+    args = [x.to(DEV) for x in (q, k, v, g)]
+    s_a = torch.zeros(N, Hkv, D, D, dtype=torch.bfloat16, device=DEV)
+    s_b = torch.zeros_like(s_a)
+    kw = dict(max_seqlen=max(lens), seg_len=seg_len)
+    plain = ops.gla_prefill_varlen(*args, s_a, i32(cu), i32(list(range(N))), i32([0] * N), **kw)
+    fused = ops.gla_prefill_varlen(*args, s_b, i32(cu), i32(list(range(N))), i32([0] * N),
+                                   gnorm_weight=w.to(DEV), gnorm_eps=1e-6, **kw)
+    torch.cuda.synchronize()
+    assert torch.equal(s_a, s_b)
+    _assert_ulp_close(fused, ogla.rms_norm_head(plain.cpu(), w, 1e-6), f"prefill g_norm {lens}")

@@ -141,6 +141,60 @@ def bench_swa_prefill(N, T, H=28, Hkv=4, D=128, wl=4096, M=0, iters=5):
           f"({fl/t/1e12/TPEAK:.2%} of sustained {TPEAK:.0f})  {N*T/t/1e6:.2f} Mtok/s")
 
 
+def bench_rope_kv(T, H=28, Hkv=4, D=128, bs=256, flush=None):
+    """Fused SWA prologue (f3): RoPE(q,k) in place + paged write of rotated k and v, against the
+    three launches it replaces here (rotate-only launch + kv_write_paged)."""
+    dev = "cuda"
+    nb = (T + bs - 1) // bs
+    kv = torch.zeros(2, nb, bs, Hkv, D, device=dev, dtype=torch.bfloat16)
+    qkv = torch.randn(T, (H + 2 * Hkv) * D, device=dev).bfloat16()
+    q, k, v = (x.view(T, -1, D) for x in qkv.split([H * D, Hkv * D, Hkv * D], dim=-1))
+    table = ops.rope_cos_sin_cache(D, 16384, 1e6, device=dev)
+    pos = torch.randint(0, 16000, (T,), device=dev)
+    slots = torch.randperm(nb * bs, device=dev)[:T].to(torch.int64)
+    t = timeit(lambda: ops.rope_kv_write_paged(q, k, v, table, pos, 128, kv[0], kv[1], slots), flush=flush)
+    def unfused():
+        ops.rope_kv_write_paged(q, k, None, table, pos, 128)
+        ops.kv_write_paged(k, v, kv[0], kv[1], slots)
+    t2 = timeit(unfused, flush=flush)
+    # q, k read + written, v read, k and v written to pages, cos|sin row + position + slot per token
+    alg = T * ((H + Hkv) * D * 2 * 2 + Hkv * D * 2 + 2 * Hkv * D * 2 + D * 2 + 16)
+    print(f"rope_kv_write T={T}: {t*1e6:8.1f} us  {alg/t/1e9:8.1f} GB/s ({alg/t/1e9/PEAK:.2%})   "
+          f"[rotate + kv_write as two launches: {t2*1e6:8.1f} us]")
+
+
+def bench_gla_gnorm(N, T, B, H=28, Hkv=4, D=128):
+    """g_norm epilogue (f2): fused vs kernel + separate torch RMSNorm pass."""
+    dev = "cuda"
+    w = torch.ones(D, device=dev, dtype=torch.bfloat16)
+    q = torch.randn(N * T, H, D, device=dev).bfloat16().relu()
+    k = torch.randn(N * T, Hkv, D, device=dev).bfloat16().relu()
+    v = torch.randn(N * T, Hkv, D, device=dev).bfloat16()
+    g = (torch.nn.functional.logsigmoid(torch.randn(N * T, Hkv, D, device=dev)) / 16).bfloat16()
+    state = torch.zeros(max(N, B), Hkv, D, D, device=dev, dtype=torch.bfloat16)
+    cu = (torch.arange(N + 1, device=dev) * T).to(torch.int32)
+    slots = torch.arange(max(N, B), device=dev, dtype=torch.int32)
+    init = torch.zeros(N, device=dev, dtype=torch.int32)
+    out = torch.empty(N * T, H, D, device=dev, dtype=torch.bfloat16)
+
+    def norm(x):
+        xf = x.float()
+        return w * (xf * torch.rsqrt(xf.pow(2).mean(-1, keepdim=True) + 1e-6)).to(x.dtype)
+    run = lambda **kw: ops.gla_prefill_varlen(q, k, v, g, state, cu, slots[:N], init, max_seqlen=T, out=out, **kw)
+    t0 = timeit(lambda: run(), iters=5, warmup=2)
+    t1 = timeit(lambda: run(gnorm_weight=w), iters=5, warmup=2)
+    t2 = timeit(lambda: norm(run()), iters=5, warmup=2)
+    print(f"gla_prefill N={N} T={T} g_norm: plain {t0*1e3:.3f} ms | fused epilogue {t1*1e3:.3f} ms | "
+          f"kernel + torch RMSNorm {t2*1e3:.3f} ms")
+    dq, dk, dv, dg, do = q[:B], k[:B], v[:B], g[:B], out[:B]
+    drun = lambda **kw: ops.gla_decode(dq, dk, dv, dg, state, slots[:B], out=do, **kw)
+    t0 = timeit(lambda: drun(), iters=50)
+    t1 = timeit(lambda: drun(gnorm_weight=w), iters=50)
+    t2 = timeit(lambda: norm(drun()), iters=50)
+    print(f"gla_decode B={B} g_norm (eager launches): plain {t0*1e6:.1f} us | fused epilogue {t1*1e6:.1f} us | "
+          f"kernel + torch RMSNorm {t2*1e6:.1f} us")
+
+
 def bench_gla_prefill(N, T, H=28, Hkv=4, D=128, gdt=torch.bfloat16, iters=5):
     dev = "cuda"
     q = torch.randn(N * T, H, D, device=dev).bfloat16().relu()
@@ -185,6 +239,11 @@ if __name__ == "__main__":
         bench_gla_prefill(64, 8192)
         bench_gla_prefill(8, 32768)
         bench_gla_prefill(1, 32768, H=7, Hkv=1, gdt=torch.float32)
+    if a.which in ("all", "gnorm"):
+        bench_gla_gnorm(64, 8192, 64)
+    if a.which in ("all", "rope_kv"):
+        bench_rope_kv(64, flush=flush)
+        bench_rope_kv(524288, flush=flush)
     if a.which in ("all", "kv_write"):
         bench_kv_write(64)
         bench_kv_write(524288, flush=flush)

@@ -24,6 +24,9 @@ SIGNATURES = {
     "hymeta_gla_prefill_varlen": (_i, [_p] * 10 + [_i] * 7 + [_i64] * 13 + [_i, _f, _i, _i, _p]),
     "hymeta_gla_prefill_workspace_bytes": (_sz, [_i] * 4),
     "hymeta_gla_prefill_varlen_seg": (_i, [_p] * 10 + [_i] * 7 + [_i64] * 13 + [_i, _f, _i, _i, _i, _p, _sz, _p]),
+    "hymeta_gla_decode_gnorm": (_i, [_p] * 7 + [_i] * 6 + [_i64] * 12 + [_i, _f, _p, _f, _p]),
+    "hymeta_gla_prefill_varlen_seg_gnorm": (_i, [_p] * 10 + [_i] * 7 + [_i64] * 13 +
+                                            [_i, _f, _i, _i, _i, _p, _sz, _p, _f, _p]),
     "hymeta_gla_gate_70b": (_i, [_p] * 6 + [_i] * 5 + [_i64] * 10 + [_f, _p]),
     "hymeta_gla_gate_7b": (_i, [_p] * 6 + [_i] * 4 + [_i64] * 12 + [_f, _p]),
     "hymeta_kv_write_paged": (_i, [_p] * 5 + [_i] * 4 + [_i64] * 10 + [_p]),

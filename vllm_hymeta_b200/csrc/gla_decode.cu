@@ -31,6 +31,8 @@ struct GlaDecodeParams {
   uint32_t kmagic, vmagic;   // (hs * magic) >> 16 == hs / (Hs/Hk) resp. hs / (Hs/Hv), checked on the host
   int64_t q_sb, q_sh, k_sb, k_sh, v_sb, v_sh, g_sb, g_sh, o_sb, o_sh, st_ss, st_sh;
   float scale;
+  const __nv_bfloat16* gnorm_w;   // per-head RMSNorm weight [128] of the 7B g_norm epilogue, or null
+  float gnorm_eps;
 };
 
 typedef unsigned long long u64;
@@ -73,9 +75,10 @@ constexpr int GD_SMEM = GD_SLOT + 32;
 // operands warp-locally (each warp only needs q/k/g of its own 16 d_k rows), runs the FFMA2 main
 // loop out of shared memory and stores the new state straight from registers.
 // GT >= G = H/Hs: q-heads served per state (accumulators per lane: GT x 8 columns).
-template <int GT, bool GF32>
+template <int GT, bool GF32, bool GN>
 __global__ void __launch_bounds__(GD_THREADS, 2) gla_decode_kernel(const GlaDecodeParams p, const int n_items) {
   extern __shared__ __align__(128) uint8_t smem[];
+  __shared__ float s_norm[16];                      // g_norm epilogue: [parity][half-CTA][warp] sums of squares
   float (*s_q)[8] = reinterpret_cast<float (*)[8]>(smem + GD_SQ);
   uint2* s_kg = reinterpret_cast<uint2*>(smem + GD_SKG);
   const uint32_t ring = smem_u32(smem);
@@ -258,11 +261,29 @@ __global__ void __launch_bounds__(GD_THREADS, 2) gla_decode_kernel(const GlaDeco
     __syncthreads();
     {
       const float* rp = s_red + (tid >> 7) * kD + (tid & 127);
+      const float gw = GN ? __bfloat162float(p.gnorm_w[tid & 127]) : 0.f;
+      int it = 0;
 #pragma unroll 1
-      for (int hh = tid >> 7; hh < G; hh += 2, op += 2 * p.o_sh, rp += 2 * kD) {
+      for (int hh = tid >> 7; hh < G; hh += 2, op += 2 * p.o_sh, rp += 2 * kD, ++it) {
         float x = 0.f;
 #pragma unroll
         for (int w = 0; w < 8; ++w) x += rp[w * GT * kD];
+        if (GN) {
+          // 7B g_norm (model_for_7B/gla_attention.py:177,233): vLLM RMSNorm over the head's 128
+          // outputs of the bf16-rounded o: y = bf16(bf16(o * rstd) * w).  The 128 threads of this
+          // half-CTA hold one head; 4 warp sums meet in smem behind a 128-thread named barrier
+          // (buffers alternate per iteration, so one barrier per head is enough).
+          const float xb = round_bf16(x);
+          float ss = xb * xb;
+#pragma unroll
+          for (int off = 16; off > 0; off >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, off);
+          float* sn = s_norm + (it & 1) * 8 + (tid >> 7) * 4;
+          if (lane == 0) sn[(tid >> 5) & 3] = ss;
+          if (tid >> 7) asm volatile("bar.sync 2, 128;" ::: "memory");
+          else asm volatile("bar.sync 1, 128;" ::: "memory");
+          const float tot = (sn[0] + sn[1]) + (sn[2] + sn[3]);
+          x = round_bf16(xb * rsqrtf(tot * (1.f / kD) + p.gnorm_eps)) * gw;
+        }
         *op = __float2bfloat16_rn(x);
       }
     }
@@ -278,24 +299,34 @@ static void launch_gla_decode(const GlaDecodeParams& p, bool g_fp32, cudaStream_
   const int grid = (int)(n_items < 2 * 148 ? n_items : 2 * 148);
   static bool attr_set = false;
   if (!attr_set) {
-    cudaFuncSetAttribute(gla_decode_kernel<GT, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, GD_SMEM);
-    cudaFuncSetAttribute(gla_decode_kernel<GT, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, GD_SMEM);
+    cudaFuncSetAttribute(gla_decode_kernel<GT, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, GD_SMEM);
+    cudaFuncSetAttribute(gla_decode_kernel<GT, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, GD_SMEM);
+    cudaFuncSetAttribute(gla_decode_kernel<GT, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, GD_SMEM);
+    cudaFuncSetAttribute(gla_decode_kernel<GT, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, GD_SMEM);
     attr_set = true;
   }
-  if (g_fp32) launch_pdl(gla_decode_kernel<GT, true>, dim3(grid), dim3(GD_THREADS), GD_SMEM, st, p, (int)n_items);
-  else launch_pdl(gla_decode_kernel<GT, false>, dim3(grid), dim3(GD_THREADS), GD_SMEM, st, p, (int)n_items);
+  const dim3 gr(grid), bl(GD_THREADS);
+  const int n = (int)n_items;
+  if (p.gnorm_w) {
+    if (g_fp32) launch_pdl(gla_decode_kernel<GT, true, true>, gr, bl, GD_SMEM, st, p, n);
+    else launch_pdl(gla_decode_kernel<GT, false, true>, gr, bl, GD_SMEM, st, p, n);
+  } else {
+    if (g_fp32) launch_pdl(gla_decode_kernel<GT, true, false>, gr, bl, GD_SMEM, st, p, n);
+    else launch_pdl(gla_decode_kernel<GT, false, false>, gr, bl, GD_SMEM, st, p, n);
+  }
 }
 
 }  // namespace hymeta
 
 using namespace hymeta;
 
-extern "C" int hymeta_gla_decode(const void* q, const void* k, const void* v, const void* g, void* o,
+extern "C" int hymeta_gla_decode_gnorm(const void* q, const void* k, const void* v, const void* g, void* o,
                                  void* state, const int32_t* slot_idx, int B, int H, int Hk, int Hv,
                                  int Hs, int D, int64_t q_sb, int64_t q_sh, int64_t k_sb, int64_t k_sh,
                                  int64_t v_sb, int64_t v_sh, int64_t g_sb, int64_t g_sh,
                                  int64_t o_sb, int64_t o_sh, int64_t st_ss, int64_t st_sh,
-                                 int g_is_fp32, float scale, void* stream) {
+                                 int g_is_fp32, float scale, const void* gnorm_weight, float gnorm_eps,
+                                 void* stream) {
   if (B == 0) return HYMETA_OK;
   if (!q || !k || !v || !g || !o || !state || !slot_idx || B < 0 || H <= 0 || Hk <= 0 || Hv <= 0 || Hs <= 0)
     return HYMETA_ERR_INVALID_ARG;
@@ -312,7 +343,8 @@ extern "C" int hymeta_gla_decode(const void* q, const void* k, const void* v, co
   if (B > 65535) return HYMETA_ERR_UNSUPPORTED;
   GlaDecodeParams p{(const __nv_bfloat16*)q, (const __nv_bfloat16*)k, (const __nv_bfloat16*)v, g,
                     (__nv_bfloat16*)o, (__nv_bfloat16*)state, slot_idx, B, H, Hk, Hv, Hs, 0u, 0u,
-                    q_sb, q_sh, k_sb, k_sh, v_sb, v_sh, g_sb, g_sh, o_sb, o_sh, st_ss, st_sh, scale};
+                    q_sb, q_sh, k_sb, k_sh, v_sb, v_sh, g_sb, g_sh, o_sb, o_sh, st_ss, st_sh, scale,
+                    (const __nv_bfloat16*)gnorm_weight, gnorm_eps};
   auto magic = [&](int div) -> uint32_t {   // exact for hs < Hs <= 4096 (verified below)
     const uint32_t m = (65536u + div - 1) / div;
     for (int x = 0; x < Hs; ++x)
@@ -331,4 +363,15 @@ extern "C" int hymeta_gla_decode(const void* q, const void* k, const void* v, co
   else launch_gla_decode<8>(p, f, st);
   count_launch();
   return check_launch();
+}
+
+extern "C" int hymeta_gla_decode(const void* q, const void* k, const void* v, const void* g, void* o,
+                                 void* state, const int32_t* slot_idx, int B, int H, int Hk, int Hv,
+                                 int Hs, int D, int64_t q_sb, int64_t q_sh, int64_t k_sb, int64_t k_sh,
+                                 int64_t v_sb, int64_t v_sh, int64_t g_sb, int64_t g_sh,
+                                 int64_t o_sb, int64_t o_sh, int64_t st_ss, int64_t st_sh,
+                                 int g_is_fp32, float scale, void* stream) {
+  return hymeta_gla_decode_gnorm(q, k, v, g, o, state, slot_idx, B, H, Hk, Hv, Hs, D, q_sb, q_sh, k_sb,
+                                 k_sh, v_sb, v_sh, g_sb, g_sh, o_sb, o_sh, st_ss, st_sh, g_is_fp32,
+                                 scale, nullptr, 0.f, stream);
 }

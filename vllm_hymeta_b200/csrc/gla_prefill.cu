@@ -56,6 +56,8 @@ struct GlaPrefillParams {
   float* ws;                   // [N*Hs][n_segs][GP_WS_ELEMS] fp32: local end state + total decay per segment
   float scale;
   int64_t q_st, q_sh, k_st, k_sh, v_st, v_sh, g_st, g_sh, o_st, o_sh, st_ss, st_sh, meta_sh;
+  const __nv_bfloat16* gnorm_w;   // per-head RMSNorm weight [128] of the 7B g_norm epilogue, or null
+  float gnorm_eps;
 };
 
 __device__ __forceinline__ void tmem_st8(uint32_t taddr, const uint32_t (&r)[8]) {
@@ -75,7 +77,7 @@ __device__ long long* g_gla_trace = nullptr;   // [steps][16] clock64 stamps of 
 #define GP_EXP 0   // timing experiments of tools/trace_gla_prefill.py (bit mask); 0 in the product build
 #endif
 
-template <bool GF32>
+template <bool GF32, bool GN>
 __global__ void __launch_bounds__(GP_THREADS, 1)
 gla_prefill_kernel(const GlaPrefillParams p, const __grid_constant__ CUtensorMap tmG,
                    const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV) {
@@ -505,10 +507,37 @@ gla_prefill_kernel(const GlaPrefillParams p, const __grid_constant__ CUtensorMap
         {
           const bool live = r_hh < G && r_t < clen;
           __nv_bfloat16* dst = op + (int64_t)i * GC * p.o_st;
+          // 7B g_norm epilogue (model_for_7B/gla_attention.py:177,210): vLLM RMSNorm over the row's
+          // 128 outputs of the bf16-rounded o, y = bf16(bf16(o * rstd) * w).  The thread owns the
+          // whole row, so this is a first TMEM pass for the sum of squares and no exchange.
+          float rstd = 0.f;
+          if (GN) {
+            float ss = 0.f;
+#pragma unroll 1
+            for (int cc = 0; cc < 4; ++cc) {
+              float t[32];
+              tmem_ld32(tOw + 32 * cc, t);
+#pragma unroll
+              for (int j = 0; j < 32; ++j) { const float xb = round_bf16(t[j]); ss = fmaf(xb, xb, ss); }
+            }
+            rstd = rsqrtf(ss * (1.f / kD) + p.gnorm_eps);
+          }
 #pragma unroll 1
           for (int cc = 0; cc < ((GP_EXP & 1) ? 0 : 4); ++cc) {
             float t[32];
             tmem_ld32(tOw + 32 * cc, t);
+            if (GN) {
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                const uint4 w4 = *reinterpret_cast<const uint4*>(p.gnorm_w + 32 * cc + 8 * j);
+                const uint32_t* wp = &w4.x;
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                  t[8 * j + 2 * e] = round_bf16(round_bf16(t[8 * j + 2 * e]) * rstd) * bf16_lo(wp[e]);
+                  t[8 * j + 2 * e + 1] = round_bf16(round_bf16(t[8 * j + 2 * e + 1]) * rstd) * bf16_hi(wp[e]);
+                }
+              }
+            }
             if (live) {
 #pragma unroll
               for (int j = 0; j < 4; ++j) {
@@ -574,13 +603,14 @@ extern "C" size_t hymeta_gla_prefill_workspace_bytes(int N, int Hs, int max_seql
   return (size_t)N * Hs * n_segs * GP_WS_ELEMS * sizeof(float);
 }
 
-extern "C" int hymeta_gla_prefill_varlen_seg(
+extern "C" int hymeta_gla_prefill_varlen_seg_gnorm(
     const void* q, const void* k, const void* v, const void* g, void* o, void* state,
     const void* meta_state, const int32_t* cu_seqlens, const int32_t* slot_idx,
     const int32_t* init_mode, int N, int T, int H, int Hk, int Hv, int Hs, int D, int64_t q_st, int64_t q_sh,
     int64_t k_st, int64_t k_sh, int64_t v_st, int64_t v_sh, int64_t g_st, int64_t g_sh, int64_t o_st,
     int64_t o_sh, int64_t st_ss, int64_t st_sh, int64_t meta_sh, int g_is_fp32, float scale,
-    int write_state, int max_seqlen, int seg_len, void* workspace, size_t workspace_bytes, void* stream) {
+    int write_state, int max_seqlen, int seg_len, void* workspace, size_t workspace_bytes,
+    const void* gnorm_weight, float gnorm_eps, void* stream) {
   if (N == 0) return HYMETA_OK;
   if (seg_len < 0 || seg_len % GC) return HYMETA_ERR_INVALID_ARG;
   int n_segs = 1;
@@ -609,6 +639,8 @@ extern "C" int hymeta_gla_prefill_varlen_seg(
   p.q_st = q_st; p.q_sh = q_sh; p.k_st = k_st; p.k_sh = k_sh; p.v_st = v_st; p.v_sh = v_sh;
   p.g_st = g_st; p.g_sh = g_sh; p.o_st = o_st; p.o_sh = o_sh; p.st_ss = st_ss; p.st_sh = st_sh;
   p.meta_sh = meta_sh;
+  if (gnorm_weight && ((uintptr_t)gnorm_weight & 15)) return HYMETA_ERR_INVALID_ARG;
+  p.gnorm_w = (const __nv_bfloat16*)gnorm_weight; p.gnorm_eps = gnorm_eps;
   p.seg_len = seg_len; p.n_segs = n_segs; p.pass = 0; p.ws = (float*)workspace;
   // TMA maps: raw g / k rows ([16 tokens][128 channels] boxes) and v (SWIZZLE_128B 64-wide halves)
   const int64_t tvec[] = {k_st, k_sh, g_st * (g_is_fp32 ? 2 : 1), g_sh * (g_is_fp32 ? 2 : 1)};
@@ -628,15 +660,24 @@ extern "C" int hymeta_gla_prefill_varlen_seg(
   }
   static bool attr_set = false;
   if (!attr_set) {
-    cudaFuncSetAttribute(gla_prefill_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, GP_SMEM);
-    cudaFuncSetAttribute(gla_prefill_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, GP_SMEM);
+    cudaFuncSetAttribute(gla_prefill_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, GP_SMEM);
+    cudaFuncSetAttribute(gla_prefill_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, GP_SMEM);
+    cudaFuncSetAttribute(gla_prefill_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, GP_SMEM);
+    cudaFuncSetAttribute(gla_prefill_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, GP_SMEM);
     attr_set = true;
   }
   auto launch = [&](int pass, int segs) {
     p.pass = pass;
     dim3 grid(Hs, N, segs);
-    if (g_is_fp32) gla_prefill_kernel<true><<<grid, GP_THREADS, GP_SMEM, (cudaStream_t)stream>>>(p, tmG, tmK, tmV);
-    else gla_prefill_kernel<false><<<grid, GP_THREADS, GP_SMEM, (cudaStream_t)stream>>>(p, tmG, tmK, tmV);
+    cudaStream_t st = (cudaStream_t)stream;
+    const bool gn = p.gnorm_w != nullptr && pass != 1;   // the summary pass emits no outputs
+    if (g_is_fp32) {
+      if (gn) gla_prefill_kernel<true, true><<<grid, GP_THREADS, GP_SMEM, st>>>(p, tmG, tmK, tmV);
+      else gla_prefill_kernel<true, false><<<grid, GP_THREADS, GP_SMEM, st>>>(p, tmG, tmK, tmV);
+    } else {
+      if (gn) gla_prefill_kernel<false, true><<<grid, GP_THREADS, GP_SMEM, st>>>(p, tmG, tmK, tmV);
+      else gla_prefill_kernel<false, false><<<grid, GP_THREADS, GP_SMEM, st>>>(p, tmG, tmK, tmV);
+    }
     count_launch();
   };
   if (n_segs == 1) launch(0, 1);
@@ -648,6 +689,20 @@ extern "C" int hymeta_gla_prefill_varlen_seg(
     launch(3, n_segs);
   }
   return check_launch();
+}
+
+extern "C" int hymeta_gla_prefill_varlen_seg(
+    const void* q, const void* k, const void* v, const void* g, void* o, void* state,
+    const void* meta_state, const int32_t* cu_seqlens, const int32_t* slot_idx,
+    const int32_t* init_mode, int N, int T, int H, int Hk, int Hv, int Hs, int D, int64_t q_st, int64_t q_sh,
+    int64_t k_st, int64_t k_sh, int64_t v_st, int64_t v_sh, int64_t g_st, int64_t g_sh, int64_t o_st,
+    int64_t o_sh, int64_t st_ss, int64_t st_sh, int64_t meta_sh, int g_is_fp32, float scale,
+    int write_state, int max_seqlen, int seg_len, void* workspace, size_t workspace_bytes, void* stream) {
+  return hymeta_gla_prefill_varlen_seg_gnorm(q, k, v, g, o, state, meta_state, cu_seqlens, slot_idx, init_mode,
+                                             N, T, H, Hk, Hv, Hs, D, q_st, q_sh, k_st, k_sh, v_st, v_sh, g_st,
+                                             g_sh, o_st, o_sh, st_ss, st_sh, meta_sh, g_is_fp32, scale,
+                                             write_state, max_seqlen, seg_len, workspace, workspace_bytes,
+                                             nullptr, 0.f, stream);
 }
 
 extern "C" int hymeta_gla_prefill_varlen(

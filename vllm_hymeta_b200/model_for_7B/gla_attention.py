@@ -7,7 +7,7 @@ method names and argument meaning, on the sm_100a kernels:
 * per-request ``fused_chunk_gla`` loop   -> ONE varlen launch over all prefill requests, slot
   (:179-211)                                states read and written in-kernel (no isnan() host sync)
 * decode (:223-235)                      -> ``ops.gla_decode``
-* ``g_norm`` per-head RMSNorm (:210,233) -> stays a torch op after the kernel
+* ``g_norm`` per-head RMSNorm (:210,233) -> fused into both kernels as their epilogue
 """
 from __future__ import annotations
 
@@ -46,6 +46,15 @@ class GatedLinearAttention:
         w = self.g_norm_weight if self.g_norm_weight is not None else 1.0
         return w * xf.to(dt)
 
+    def _gnorm_w(self, device) -> torch.Tensor:
+        """bf16 [head_dim] weight handed to the kernels' fused g_norm epilogue."""
+        w = self.g_norm_weight
+        if w is None:
+            w = self.g_norm_weight = torch.ones(self.head_dim, dtype=torch.bfloat16, device=device)
+        elif w.dtype != torch.bfloat16 or w.device != device:
+            w = self.g_norm_weight = w.to(device=device, dtype=torch.bfloat16)
+        return w
+
     def _prefill_and_mix_infer(self, q, k, v, gk, kv_cache, state_indices_tensor, attn_metadata):
         T, H, D = q.shape
         out = torch.empty(T, H, D, dtype=q.dtype, device=q.device)
@@ -57,11 +66,12 @@ class GatedLinearAttention:
             mode = torch.full((num_prefills,), ops.INIT_SLOT, dtype=torch.int32, device=q.device)
             ops.gla_prefill_varlen(q[:n_tok], k[:n_tok], v[:n_tok], gk[:n_tok], kv_cache, cu, slots,
                                    mode, max_seqlen=getattr(attn_metadata, "max_query_len", None) or n_tok,
-                                   out=out[:n_tok])
+                                   out=out[:n_tok], gnorm_weight=self._gnorm_w(q.device),
+                                   gnorm_eps=self.norm_eps)
         if attn_metadata.num_decode_tokens > 0:
             self._decode(q, k, v, gk, kv_cache, state_indices_tensor, attn_metadata,
-                         out=out[attn_metadata.num_prefill_tokens:], norm=False)
-        return self.g_norm(out).view(T, H * D)
+                         out=out[attn_metadata.num_prefill_tokens:])
+        return out.view(T, H * D)                  # g_norm already applied by both kernels' epilogues
 
     def _decode(self, q, k, v, gk, kv_cache, state_indices_tensor, attn_metadata, out=None,
                 norm=True):
@@ -69,9 +79,9 @@ class GatedLinearAttention:
         slot_ids = state_indices_tensor[getattr(attn_metadata, "num_prefills", 0):]
         B = q.shape[0] - start
         o = ops.gla_decode(q[start:], k[start:], v[start:], gk[start:], kv_cache,
-                           slot_ids[:B].to(torch.int32), out=out)
-        if norm:
-            o = self.g_norm(o)
+                           slot_ids[:B].to(torch.int32), out=out,
+                           gnorm_weight=self._gnorm_w(q.device) if norm else None,
+                           gnorm_eps=self.norm_eps)
         return o.view(B, -1)
 
     def forward(self, qkv: torch.Tensor, gk: torch.Tensor, kv_caches: GLACacheParams,

@@ -40,9 +40,11 @@ def launch_count() -> int:
 # ----------------------------------------------------------------------------------- a2
 def gla_decode(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, g: torch.Tensor,
                state: torch.Tensor, slot_idx: torch.Tensor, scale: Optional[float] = None,
-               out: Optional[torch.Tensor] = None) -> torch.Tensor:
+               out: Optional[torch.Tensor] = None, gnorm_weight: Optional[torch.Tensor] = None,
+               gnorm_eps: float = 1e-6) -> torch.Tensor:
     """q [B,H,D]; k,g [B,Hk,D]; v [B,Hv,D]; state [slots,Hs,D,D] bf16 (updated in place);
-    slot_idx [B] int32 (-1 = skip).  Returns o [B,H,D] bf16."""
+    slot_idx [B] int32 (-1 = skip).  Returns o [B,H,D] bf16.  gnorm_weight [D] bf16: the 7B
+    per-head ``g_norm`` RMSNorm applied as the kernel's epilogue."""
     B, H, D = q.shape
     Hk, Hv, Hs = k.shape[1], v.shape[1], state.shape[1]
     if g.shape[1] != Hk:
@@ -59,11 +61,16 @@ def gla_decode(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, g: torch.Tenso
         out = torch.empty(B, H, D, dtype=q.dtype, device=q.device)
     if scale is None:
         scale = D ** -0.5
-    check(lib().hymeta_gla_decode(
+    if gnorm_weight is not None:
+        _req(gnorm_weight, "gnorm_weight", torch.bfloat16)
+        if gnorm_weight.numel() != D:
+            raise ValueError("gnorm_weight must hold head_dim elements")
+    check(lib().hymeta_gla_decode_gnorm(
         _ptr(q), _ptr(k), _ptr(v), _ptr(g), _ptr(out), _ptr(state), _ptr(slot_idx),
         B, H, Hk, Hv, Hs, D, q.stride(0), q.stride(1), k.stride(0), k.stride(1), v.stride(0), v.stride(1),
         g.stride(0), g.stride(1), out.stride(0), out.stride(1), state.stride(0), state.stride(1),
-        int(g.dtype == torch.float32), float(scale), _stream()), "hymeta_gla_decode")
+        int(g.dtype == torch.float32), float(scale), _ptr(gnorm_weight), float(gnorm_eps),
+        _stream()), "hymeta_gla_decode")
     return out
 
 
@@ -71,9 +78,12 @@ def gla_decode(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, g: torch.Tenso
 def gla_prefill_varlen(q, k, v, g, state, cu_seqlens, slot_idx, init_mode,
                        meta_state: Optional[torch.Tensor] = None, scale: Optional[float] = None,
                        write_state: bool = True, max_seqlen: Optional[int] = None,
-                       out: Optional[torch.Tensor] = None, seg_len: Optional[int] = None) -> torch.Tensor:
+                       out: Optional[torch.Tensor] = None, seg_len: Optional[int] = None,
+                       gnorm_weight: Optional[torch.Tensor] = None,
+                       gnorm_eps: float = 1e-6) -> torch.Tensor:
     """q [T,H,D]; k,g [T,Hk,D]; v [T,Hv,D]; state [slots,Hs,D,D]; cu_seqlens [N+1], slot_idx [N],
-    init_mode [N] int32 device tensors.  Returns o [T,H,D] bf16; writes final states."""
+    init_mode [N] int32 device tensors.  Returns o [T,H,D] bf16; writes final states.
+    gnorm_weight [D] bf16: the 7B per-head ``g_norm`` RMSNorm applied as the kernel's epilogue."""
     T, H, D = q.shape
     Hk, Hv, Hs = k.shape[1], v.shape[1], state.shape[1]
     if g.shape[1] != Hk:
@@ -98,14 +108,19 @@ def gla_prefill_varlen(q, k, v, g, state, cu_seqlens, slot_idx, init_mode,
         ws_bytes = lib().hymeta_gla_prefill_workspace_bytes(N, Hs, msl, seg_len)
         if ws_bytes:
             ws = _gla_workspace(q.device, ws_bytes)
-    check(lib().hymeta_gla_prefill_varlen_seg(
+    if gnorm_weight is not None:
+        _req(gnorm_weight, "gnorm_weight", torch.bfloat16)
+        if gnorm_weight.numel() != D:
+            raise ValueError("gnorm_weight must hold head_dim elements")
+    check(lib().hymeta_gla_prefill_varlen_seg_gnorm(
         _ptr(q), _ptr(k), _ptr(v), _ptr(g), _ptr(out), _ptr(state), _ptr(meta_state),
         _ptr(cu_seqlens), _ptr(slot_idx), _ptr(init_mode), N, T, H, Hk, Hv, Hs, D,
         q.stride(0), q.stride(1), k.stride(0), k.stride(1), v.stride(0), v.stride(1),
         g.stride(0), g.stride(1), out.stride(0), out.stride(1), state.stride(0), state.stride(1),
         0 if meta_state is None else meta_state.stride(0),
         int(g.dtype == torch.float32), float(scale), int(write_state), msl,
-        int(seg_len or 0), _ptr(ws), ws_bytes, _stream()), "hymeta_gla_prefill_varlen_seg")
+        int(seg_len or 0), _ptr(ws), ws_bytes, _ptr(gnorm_weight), float(gnorm_eps),
+        _stream()), "hymeta_gla_prefill_varlen_seg")
     return out
 
 
