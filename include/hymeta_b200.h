@@ -299,6 +299,27 @@ int hymeta_state_copy_slot(void* state, int from_slot, int to_slot, int L,
                            int64_t st_sl, int64_t st_ss, int64_t slot_elems, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
+ * f1  Branch merge of the 70B hybrid layer -- replaces norm1(out_attn), norm2(out_linear),
+ *     (a + b) / 2 and .to(bfloat16) (vllm_hymeta/models/modeling_hymeta.py:909-919) with
+ *     HymetaRMSNormTP._forward (:151-173) for both branches.
+ * x_attn, x_linear: [T, hidden_local] bf16 (hidden_local = hidden_size / tp_world, the rank's
+ * slice).  hymeta_branch_sumsq writes means_out[0][t], means_out[1][t] = mean over the local
+ * slice of x^2 (fp32, [2][T]).  With tp_world > 1 the caller all-reduces (SUM) that 8*T-byte
+ * buffer across the tensor-parallel group -- the one exchange adjacent to the path (:159-161) --
+ * and passes it as `means`; with tp_world == 1 `means` may be null and the kernel computes it.
+ * hymeta_branch_norm_merge: out[t] = bf16( ( bf16(x_attn*rstd_a) * w_attn
+ *                                          + bf16(x_linear*rstd_l) * w_linear ) / 2 ),
+ * rstd = rsqrt(means / tp_world + eps), w_* = the rank's fp32 weight slice [hidden_local].
+ * `out` [T, hidden_local] bf16 may alias either input.
+ * ---------------------------------------------------------------------------------------------- */
+int hymeta_branch_sumsq(const void* x_attn, const void* x_linear, float* means_out, int T,
+                        int hidden_local, int64_t xa_st, int64_t xl_st, void* stream);
+int hymeta_branch_norm_merge(const void* x_attn, const void* x_linear, const float* means,
+                             const float* w_attn, const float* w_linear, void* out, int T,
+                             int hidden_local, int tp_world, float eps, int64_t xa_st,
+                             int64_t xl_st, int64_t o_st, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
  * f4  Host-side state-slot manager -- replaces the bookkeeping of vLLM 0.10.0's ConstantSizeCache
  *     inherited by HymetaCacheManager / GLACacheManager (vllm_hymeta/models/hymeta_cache.py:24-63,
  *     vllm_hymeta/model_for_7B/gla_cache.py:17-32; mapping read at modeling_hymeta.py:1206-1208)

@@ -232,6 +232,30 @@ def rms_norm_head(x: torch.Tensor, weight: torch.Tensor, eps: float) -> torch.Te
     return weight * (xf * torch.rsqrt(var + eps)).to(dt)
 
 
+def rms_norm_tp(x: torch.Tensor, weight: torch.Tensor, eps: float, tp_world: int = 1,
+                all_reduce=None) -> torch.Tensor:
+    """``HymetaRMSNormTP._forward`` (vllm_hymeta/models/modeling_hymeta.py:151-173) restated:
+    fp32 x, variance = mean over the LOCAL hidden slice, summed over the tensor-parallel ranks by
+    ``all_reduce`` and divided by tp_world, x * rsqrt(var + eps), cast back to the input dtype, times
+    the rank's fp32 weight slice (result promoted to fp32).  PARITY UNPINNED: the class imports vLLM
+    (not importable here) and its HF twin uses fla's RMSNorm (hf_model/modeling_hymeta.py:25,86-87),
+    so this follows the source text only."""
+    orig = x.dtype
+    xf = x.to(torch.float32)
+    var = xf.pow(2).mean(dim=-1, keepdim=True, dtype=torch.float32)
+    if tp_world > 1:
+        var = all_reduce(var) / tp_world
+    xf = xf * torch.rsqrt(var + eps)
+    return xf.to(orig) * weight[: x.shape[-1]]
+
+
+def branch_norm_merge(out_attn, out_linear, w1, w2, eps, tp_world: int = 1, all_reduce=(None, None)):
+    """modeling_hymeta.py:909-919: (norm1(out_attn) + norm2(out_linear)) / 2 -> bfloat16."""
+    a = rms_norm_tp(out_attn, w1, eps, tp_world, all_reduce[0])
+    b = rms_norm_tp(out_linear, w2, eps, tp_world, all_reduce[1])
+    return ((a + b) / 2).to(torch.bfloat16)
+
+
 # ---------------------------------------------------------------- synthetic inputs
 def synth_gla_inputs(T: int, H: int, Hkv: int, D: int, model: str, seed: int,
                      dtype=torch.bfloat16):

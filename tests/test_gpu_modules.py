@@ -326,14 +326,17 @@ def test_flash_attention_fused_prologue_equals_unfused(ops):
 
 
 # ------------------------------------------------------------------------------------- f2 (g_norm epilogue)
-def _assert_ulp_close(got, ref, what, max_frac=0.02):
+def _assert_ulp_close(got, ref, what, max_frac=0.02, floor=0.0):
     """Same bf16 arithmetic up to the fp32 summation order of the variance and rsqrt rounding: a
     flipped first rounding (x * rstd) is one bf16 ulp, which the multiplication by w can turn into
     two ulps of the result -- every element within that, all but a small fraction bit-identical."""
     got, ref = got.float().cpu(), ref.float().cpu()
     assert torch.isfinite(got).all(), what
     diff = (got - ref).abs()
-    assert (diff <= 2.0 ** -6 * ref.abs() + 1e-30).all(), f"{what}: more than two bf16 ulps apart"
+    # floor: magnitude of the addends when the result is a sum that may cancel (branch merge)
+    bad = diff > 2.0 ** -6 * ref.abs().clamp(min=floor) + 1e-30
+    assert not bad.any(), (f"{what}: more than two bf16 ulps apart at {int(bad.sum())} elements, "
+                           f"worst {diff.max().item():.4g}")
     frac = (diff > 0).float().mean().item()
     assert frac <= max_frac, f"{what}: {frac:.3%} of elements differ"
 
@@ -382,3 +385,45 @@ def test_gnorm_epilogue_prefill(ops, lens, seg_len):
     torch.cuda.synchronize()
     assert torch.equal(s_a, s_b)
     _assert_ulp_close(fused, ogla.rms_norm_head(plain.cpu(), w, 1e-6), f"prefill g_norm {lens}")
+
+
+# ------------------------------------------------------------------------------------- f1 (branch merge)
+@pytest.mark.parametrize("T,hidden,tp", [(777, 3584, 1), (64, 3584, 1), (300, 3584, 2), (129, 3584, 4),
+                                         (1, 128, 1)])
+def test_branch_norm_merge(ops, T, hidden, tp):
+    """norm1(out_attn), norm2(out_linear), average, bf16 cast (modeling_hymeta.py:909-919) in one
+    pass; tp > 1 simulates the head shards on one GPU with the cross-shard sum of the per-token
+    means done here (the all-reduce of the real run)."""
+    gen = torch.Generator().manual_seed(T + tp)
+    xa = (torch.randn(T, hidden, generator=gen) * 3).bfloat16()
+    xl = (torch.randn(T, hidden, generator=gen) * 0.2).bfloat16()
+    w1 = 1 + 0.1 * torch.randn(hidden, generator=gen)
+    w2 = 1 + 0.1 * torch.randn(hidden, generator=gen)
+    eps, hl = 1e-6, hidden // tp
+    sl = [slice(r * hl, (r + 1) * hl) for r in range(tp)]
+    tot_a = sum(xa[:, s].float().pow(2).mean(-1, keepdim=True, dtype=torch.float32) for s in sl)
+    tot_l = sum(xl[:, s].float().pow(2).mean(-1, keepdim=True, dtype=torch.float32) for s in sl)
+    d_means = [ops.branch_sumsq(xa[:, s].to(DEV), xl[:, s].to(DEV)) for s in sl]
+    red = sum(d_means)                                     # what dist.all_reduce(SUM) leaves on every rank
+    for r, s in enumerate(sl):
+        ref = ogla.branch_norm_merge(xa[:, s], xl[:, s], w1[s], w2[s], eps, tp,
+                                     (lambda v: tot_a, lambda v: tot_l))
+        got = ops.branch_norm_merge(xa[:, s].to(DEV), xl[:, s].to(DEV), w1[s].to(DEV).contiguous(),
+                                    w2[s].to(DEV).contiguous(), eps, tp_world=tp,
+                                    means=red if tp > 1 else None)
+        torch.cuda.synchronize()
+        # the two normalised addends are O(1) and may cancel: ulps are those of the addends
+        _assert_ulp_close(got, ref, f"branch merge T={T} tp={tp} rank={r}", floor=1.0)
+    # in place over one input
+    x_in = xa[:, sl[0]].to(DEV).contiguous()
+    keep = x_in.clone()
+    ops.branch_norm_merge(x_in, xl[:, sl[0]].to(DEV), w1[sl[0]].to(DEV).contiguous(),
+                          w2[sl[0]].to(DEV).contiguous(), eps, tp_world=tp,
+                          means=red if tp > 1 else None, out=x_in)
+    got2 = ops.branch_norm_merge(keep, xl[:, sl[0]].to(DEV), w1[sl[0]].to(DEV).contiguous(),
+                                 w2[sl[0]].to(DEV).contiguous(), eps, tp_world=tp,
+                                 means=red if tp > 1 else None)
+    torch.cuda.synchronize()
+    assert torch.equal(x_in, got2)
+    with pytest.raises(ValueError):
+        ops.branch_norm_merge(keep, keep, w1[:5].to(DEV), w2[sl[0]].to(DEV).contiguous(), eps)

@@ -163,6 +163,26 @@ def bench_rope_kv(T, H=28, Hkv=4, D=128, bs=256, flush=None):
           f"[rotate + kv_write as two launches: {t2*1e6:8.1f} us]")
 
 
+def bench_branch_merge(T, hidden=3584, flush=None):
+    """f1: norm1 + norm2 + average + bf16 cast in one pass vs the reference's torch op sequence."""
+    dev = "cuda"
+    xa = torch.randn(T, hidden, device=dev).bfloat16()
+    xl = torch.randn(T, hidden, device=dev).bfloat16()
+    w1 = torch.ones(hidden, device=dev)
+    w2 = torch.ones(hidden, device=dev)
+    out = torch.empty_like(xa)
+    t = timeit(lambda: ops.branch_norm_merge(xa, xl, w1, w2, 1e-6, out=out), flush=flush, iters=10)
+
+    def ref_norm(x, w):
+        xf = x.float()
+        xf = xf * torch.rsqrt(xf.pow(2).mean(-1, keepdim=True) + 1e-6)
+        return xf.to(torch.bfloat16) * w
+    t2 = timeit(lambda: ((ref_norm(xa, w1) + ref_norm(xl, w2)) / 2).to(torch.bfloat16), flush=flush, iters=5)
+    alg = T * hidden * 2 * 3
+    print(f"branch_norm_merge T={T} hidden={hidden}: {t*1e6:8.1f} us  {alg/t/1e9:8.1f} GB/s ({alg/t/1e9/PEAK:.2%})   "
+          f"[torch op sequence: {t2*1e6:8.1f} us]")
+
+
 def bench_gla_gnorm(N, T, B, H=28, Hkv=4, D=128):
     """g_norm epilogue (f2): fused vs kernel + separate torch RMSNorm pass."""
     dev = "cuda"
@@ -239,6 +259,9 @@ if __name__ == "__main__":
         bench_gla_prefill(64, 8192)
         bench_gla_prefill(8, 32768)
         bench_gla_prefill(1, 32768, H=7, Hkv=1, gdt=torch.float32)
+    if a.which in ("all", "branch_merge"):
+        bench_branch_merge(64, flush=flush)
+        bench_branch_merge(65536, flush=flush)
     if a.which in ("all", "gnorm"):
         bench_gla_gnorm(64, 8192, 64)
     if a.which in ("all", "rope_kv"):

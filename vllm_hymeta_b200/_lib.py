@@ -40,6 +40,8 @@ SIGNATURES = {
     "hymeta_state_zero_slots": (_i, [_p, _p, _i, _i, _i64, _i64, _i64, _p]),
     "hymeta_state_copy_slot": (_i, [_p, _i, _i, _i, _i64, _i64, _i64, _p]),
     "hymeta_selftest_umma": (_i, [_p]),
+    "hymeta_branch_sumsq": (_i, [_p, _p, _p, _i, _i, _i64, _i64, _p]),
+    "hymeta_branch_norm_merge": (_i, [_p] * 6 + [_i, _i, _i, _f, _i64, _i64, _i64, _p]),
     "hymeta_slot_mgr_create": (_p, [_i]),
     "hymeta_slot_mgr_destroy": (None, [_p]),
     "hymeta_slot_mgr_release": (_i, [_p, _p, _i]),

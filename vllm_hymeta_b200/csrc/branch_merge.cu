@@ -1,0 +1,244 @@
+// Branch merge of the 70B hybrid layer (f1): HymetaRMSNormTP of the SWA branch and of the
+// GLA branch, their average and the bf16 cast -- modeling_hymeta.py:151-173 (norm) and :909-919
+// (norm1(out_attn), norm2(out_linear), (a + b) / 2, .to(bfloat16)) -- in one pass over the two
+// [T, hidden/tp] activations instead of ~10 elementwise torch launches with fp32 intermediates.
+//
+// The norm's variance spans the FULL hidden size, i.e. all tensor-parallel shards:
+//   variance = all_reduce_sum( mean_local(x^2) ) / tp_world                         (:159-161)
+// so the work is split exactly where the exchange sits:
+//   hymeta_branch_sumsq        -> means[2][T] fp32: mean over the local hidden slice of x^2, both branches
+//   (caller: ONE all-reduce of 8*T bytes over NVLink -- torch.distributed / NCCL; skipped at TP=1)
+//   hymeta_branch_norm_merge   -> out = bf16( ( bf16(x1*rstd1)*w1 + bf16(x2*rstd2)*w2 ) / 2 )
+// With means == null the second kernel computes the local means itself (TP=1: one launch).
+// Arithmetic is the reference's: x in fp32, rsqrt(variance + eps) in fp32, the normalised value cast
+// to bf16 BEFORE the fp32 weight multiplies it (x.to(orig_dtype) * weight promotes to fp32), the
+// average in fp32, one final bf16 rounding.  HBM-bound: 2 reads + 1 write of [T, hidden/tp] bf16.
+#include "common.cuh"
+
+namespace hymeta {
+
+// One warp per token row; lanes stride over 16-byte chunks, four independent loads in flight per
+// lane and branch (a 3584-wide row is 14 chunks per lane: without batching the loop is one
+// dependent 16-byte load at a time and the kernel sits at ~55 % of HBM).
+constexpr int BM_B = 4;
+
+__device__ __forceinline__ float sumsq8(const uint4& u, float s) {
+  const uint32_t* p = &u.x;
+#pragma unroll
+  for (int e = 0; e < 4; ++e) {
+    const float a = bf16_lo(p[e]), b = bf16_hi(p[e]);
+    s = fmaf(a, a, s);
+    s = fmaf(b, b, s);
+  }
+  return s;
+}
+
+__device__ __forceinline__ void row_sumsq2(const __nv_bfloat16* r1, const __nv_bfloat16* r2, int chunks,
+                                           int lane, float& s1, float& s2) {
+  s1 = 0.f; s2 = 0.f;
+  for (int c0 = lane; c0 < chunks; c0 += 32 * BM_B) {
+    uint4 a[BM_B], b[BM_B];
+#pragma unroll
+    for (int i = 0; i < BM_B; ++i) {
+      const int c = c0 + 32 * i;
+      a[i] = b[i] = make_uint4(0, 0, 0, 0);
+      if (c < chunks) { a[i] = ldg_v4(r1 + c * 8); b[i] = ldg_v4(r2 + c * 8); }
+    }
+#pragma unroll
+    for (int i = 0; i < BM_B; ++i) { s1 = sumsq8(a[i], s1); s2 = sumsq8(b[i], s2); }
+  }
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) {
+    s1 += __shfl_xor_sync(0xffffffffu, s1, off);
+    s2 += __shfl_xor_sync(0xffffffffu, s2, off);
+  }
+}
+
+__global__ void __launch_bounds__(256)
+branch_sumsq_kernel(const __nv_bfloat16* __restrict__ x1, const __nv_bfloat16* __restrict__ x2,
+                    float* __restrict__ means, int T, int hidden, int64_t x1_st, int64_t x2_st) {
+  const int lane = threadIdx.x & 31, wpb = blockDim.x >> 5;
+  const float inv = 1.f / (float)hidden;
+  for (int t = blockIdx.x * wpb + (threadIdx.x >> 5); t < T; t += gridDim.x * wpb) {
+    float s1, s2;
+    row_sumsq2(x1 + t * x1_st, x2 + t * x2_st, hidden / 8, lane, s1, s2);
+    if (lane == 0) { means[t] = s1 * inv; means[T + t] = s2 * inv; }
+  }
+}
+
+__global__ void __launch_bounds__(256)
+branch_norm_merge_kernel(const __nv_bfloat16* __restrict__ x1, const __nv_bfloat16* __restrict__ x2,
+                         const float* __restrict__ means, const float* __restrict__ w1,
+                         const float* __restrict__ w2, __nv_bfloat16* __restrict__ out, int T,
+                         int hidden, float inv_tp, float eps, int64_t x1_st, int64_t x2_st,
+                         int64_t o_st) {
+  const int lane = threadIdx.x & 31, wpb = blockDim.x >> 5;
+  const int chunks = hidden / 8;
+  const float inv = 1.f / (float)hidden;
+  for (int t = blockIdx.x * wpb + (threadIdx.x >> 5); t < T; t += gridDim.x * wpb) {
+    const __nv_bfloat16* r1 = x1 + t * x1_st;
+    const __nv_bfloat16* r2 = x2 + t * x2_st;
+    float m1, m2;
+    if (means) { m1 = means[t]; m2 = means[T + t]; }
+    else { row_sumsq2(r1, r2, chunks, lane, m1, m2); m1 *= inv; m2 *= inv; }
+    const float rs1 = rsqrtf(m1 * inv_tp + eps), rs2 = rsqrtf(m2 * inv_tp + eps);
+    __nv_bfloat16* o = out + t * o_st;
+    for (int c0 = lane; c0 < chunks; c0 += 32 * BM_B) {
+      uint4 av[BM_B], bv[BM_B];
+#pragma unroll
+      for (int i = 0; i < BM_B; ++i) {                   // second touch of the row: L1/L2 hits
+        const int c = c0 + 32 * i;
+        if (c < chunks) { av[i] = ldg_v4(r1 + c * 8); bv[i] = ldg_v4(r2 + c * 8); }
+      }
+#pragma unroll
+      for (int i = 0; i < BM_B; ++i) {
+        const int c = c0 + 32 * i;
+        if (c >= chunks) break;
+        const float4 wa0 = *reinterpret_cast<const float4*>(w1 + c * 8);
+        const float4 wa1 = *reinterpret_cast<const float4*>(w1 + c * 8 + 4);
+        const float4 wb0 = *reinterpret_cast<const float4*>(w2 + c * 8);
+        const float4 wb1 = *reinterpret_cast<const float4*>(w2 + c * 8 + 4);
+        const float wa[8] = {wa0.x, wa0.y, wa0.z, wa0.w, wa1.x, wa1.y, wa1.z, wa1.w};
+        const float wb[8] = {wb0.x, wb0.y, wb0.z, wb0.w, wb1.x, wb1.y, wb1.z, wb1.w};
+        const uint32_t* ap = &av[i].x;
+        const uint32_t* bp = &bv[i].x;
+        uint4 r;
+        uint32_t* rp = &r.x;
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const float y0 = __fadd_rn(__fmul_rn(round_bf16(__fmul_rn(bf16_lo(ap[e]), rs1)), wa[2 * e]),
+                                     __fmul_rn(round_bf16(__fmul_rn(bf16_lo(bp[e]), rs2)), wb[2 * e]));
+          const float y1 = __fadd_rn(__fmul_rn(round_bf16(__fmul_rn(bf16_hi(ap[e]), rs1)), wa[2 * e + 1]),
+                                     __fmul_rn(round_bf16(__fmul_rn(bf16_hi(bp[e]), rs2)), wb[2 * e + 1]));
+          rp[e] = pack_bf16(y0 * 0.5f, y1 * 0.5f);
+        }
+        stg_v4(o + c * 8, r);
+      }
+    }
+  }
+}
+
+// Register-resident form for rows of at most 32 * NC chunks (NC = 14: hidden/tp <= 3584, every
+// Hymeta geometry): the warp loads both rows ONCE into registers (2 * NC independent 16-byte loads
+// in flight per lane), reduces, scales and stores -- no second touch, no dependent load chain.
+template <int NC>
+__global__ void __launch_bounds__(128)
+branch_norm_merge_reg_kernel(const __nv_bfloat16* x1, const __nv_bfloat16* x2, const float* means,
+                             const float* __restrict__ w1, const float* __restrict__ w2,
+                             __nv_bfloat16* out, int T, int hidden, float inv_tp, float eps,
+                             int64_t x1_st, int64_t x2_st, int64_t o_st) {
+  const int lane = threadIdx.x & 31, wpb = blockDim.x >> 5;
+  const int chunks = hidden / 8;
+  const float inv = 1.f / (float)hidden;
+  for (int t = blockIdx.x * wpb + (threadIdx.x >> 5); t < T; t += gridDim.x * wpb) {
+    const uint4* r1 = reinterpret_cast<const uint4*>(x1 + t * x1_st);
+    const uint4* r2 = reinterpret_cast<const uint4*>(x2 + t * x2_st);
+    uint4 a[NC], b[NC];
+#pragma unroll
+    for (int i = 0; i < NC; ++i) {
+      const int c = lane + 32 * i;
+      a[i] = b[i] = make_uint4(0, 0, 0, 0);
+      if (c < chunks) { a[i] = r1[c]; b[i] = r2[c]; }
+    }
+    float m1, m2;
+    if (means) { m1 = means[t]; m2 = means[T + t]; }
+    else {
+      float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+      for (int i = 0; i < NC; ++i) { s1 = sumsq8(a[i], s1); s2 = sumsq8(b[i], s2); }
+#pragma unroll
+      for (int off = 16; off > 0; off >>= 1) {
+        s1 += __shfl_xor_sync(0xffffffffu, s1, off);
+        s2 += __shfl_xor_sync(0xffffffffu, s2, off);
+      }
+      m1 = s1 * inv; m2 = s2 * inv;
+    }
+    const float rs1 = rsqrtf(m1 * inv_tp + eps), rs2 = rsqrtf(m2 * inv_tp + eps);
+    uint4* o = reinterpret_cast<uint4*>(out + t * o_st);
+#pragma unroll
+    for (int i = 0; i < NC; ++i) {
+      const int c = lane + 32 * i;
+      if (c < chunks) {
+        const float4 wa0 = *reinterpret_cast<const float4*>(w1 + c * 8);
+        const float4 wa1 = *reinterpret_cast<const float4*>(w1 + c * 8 + 4);
+        const float4 wb0 = *reinterpret_cast<const float4*>(w2 + c * 8);
+        const float4 wb1 = *reinterpret_cast<const float4*>(w2 + c * 8 + 4);
+        const float wa[8] = {wa0.x, wa0.y, wa0.z, wa0.w, wa1.x, wa1.y, wa1.z, wa1.w};
+        const float wb[8] = {wb0.x, wb0.y, wb0.z, wb0.w, wb1.x, wb1.y, wb1.z, wb1.w};
+        const uint32_t* ap = &a[i].x;
+        const uint32_t* bp = &b[i].x;
+        uint4 r;
+        uint32_t* rp = &r.x;
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const float y0 = __fadd_rn(__fmul_rn(round_bf16(__fmul_rn(bf16_lo(ap[e]), rs1)), wa[2 * e]),
+                                     __fmul_rn(round_bf16(__fmul_rn(bf16_lo(bp[e]), rs2)), wb[2 * e]));
+          const float y1 = __fadd_rn(__fmul_rn(round_bf16(__fmul_rn(bf16_hi(ap[e]), rs1)), wa[2 * e + 1]),
+                                     __fmul_rn(round_bf16(__fmul_rn(bf16_hi(bp[e]), rs2)), wb[2 * e + 1]));
+          rp[e] = pack_bf16(y0 * 0.5f, y1 * 0.5f);
+        }
+        o[c] = r;
+      }
+    }
+  }
+}
+
+static int check_common(const void* x1, const void* x2, int T, int hidden, int64_t x1_st,
+                        int64_t x2_st) {
+  if (!x1 || !x2 || T < 0 || hidden <= 0) return HYMETA_ERR_INVALID_ARG;
+  if (hidden % 8 || x1_st % 8 || x2_st % 8) return HYMETA_ERR_INVALID_ARG;   // 16-byte vector access
+  if (((uintptr_t)x1 | (uintptr_t)x2) & 15) return HYMETA_ERR_INVALID_ARG;
+  return HYMETA_OK;
+}
+static int grid_for(int T) {
+  const int want = (T + 7) / 8;   // 8 warps (rows) per CTA
+  return want < 148 * 8 ? want : 148 * 8;
+}
+
+}  // namespace hymeta
+
+using namespace hymeta;
+
+extern "C" int hymeta_branch_sumsq(const void* x_attn, const void* x_linear, float* means_out, int T,
+                                   int hidden_local, int64_t xa_st, int64_t xl_st, void* stream) {
+  if (T == 0) return HYMETA_OK;
+  const int rc = check_common(x_attn, x_linear, T, hidden_local, xa_st, xl_st);
+  if (rc) return rc;
+  if (!means_out) return HYMETA_ERR_INVALID_ARG;
+  branch_sumsq_kernel<<<grid_for(T), 256, 0, (cudaStream_t)stream>>>(
+      (const __nv_bfloat16*)x_attn, (const __nv_bfloat16*)x_linear, means_out, T, hidden_local,
+      xa_st, xl_st);
+  count_launch();
+  return check_launch();
+}
+
+extern "C" int hymeta_branch_norm_merge(const void* x_attn, const void* x_linear, const float* means,
+                                        const float* w_attn, const float* w_linear, void* out, int T,
+                                        int hidden_local, int tp_world, float eps, int64_t xa_st,
+                                        int64_t xl_st, int64_t o_st, void* stream) {
+  if (T == 0) return HYMETA_OK;
+  const int rc = check_common(x_attn, x_linear, T, hidden_local, xa_st, xl_st);
+  if (rc) return rc;
+  if (!w_attn || !w_linear || !out || tp_world <= 0 || o_st % 8) return HYMETA_ERR_INVALID_ARG;
+  if (((uintptr_t)out | (uintptr_t)w_attn | (uintptr_t)w_linear) & 15) return HYMETA_ERR_INVALID_ARG;
+  if (tp_world > 1 && !means) return HYMETA_ERR_INVALID_ARG;   // the cross-shard sum is the caller's
+  const float inv_tp = 1.f / (float)tp_world;
+  if (hidden_local <= 32 * 8 * 14) {   // row fits the register-resident form
+    const int want = (T + 3) / 4;      // 4 warps (rows) per CTA
+    const int grid = want < 148 * 4 ? want : 148 * 4;
+    if (hidden_local <= 32 * 8 * 4)
+      branch_norm_merge_reg_kernel<4><<<grid, 128, 0, (cudaStream_t)stream>>>(
+          (const __nv_bfloat16*)x_attn, (const __nv_bfloat16*)x_linear, means, w_attn, w_linear,
+          (__nv_bfloat16*)out, T, hidden_local, inv_tp, eps, xa_st, xl_st, o_st);
+    else
+      branch_norm_merge_reg_kernel<14><<<grid, 128, 0, (cudaStream_t)stream>>>(
+          (const __nv_bfloat16*)x_attn, (const __nv_bfloat16*)x_linear, means, w_attn, w_linear,
+          (__nv_bfloat16*)out, T, hidden_local, inv_tp, eps, xa_st, xl_st, o_st);
+  } else {
+    branch_norm_merge_kernel<<<grid_for(T), 256, 0, (cudaStream_t)stream>>>(
+        (const __nv_bfloat16*)x_attn, (const __nv_bfloat16*)x_linear, means, w_attn, w_linear,
+        (__nv_bfloat16*)out, T, hidden_local, inv_tp, eps, xa_st, xl_st, o_st);
+  }
+  count_launch();
+  return check_launch();
+}

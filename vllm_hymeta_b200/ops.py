@@ -286,6 +286,58 @@ def rope_kv_write_paged(q, k, v, cos_sin_cache, positions, pos_offset=0, k_cache
     return q_out, k_out
 
 
+# ----------------------------------------------------------------------------------- f1
+def branch_sumsq(x_attn: torch.Tensor, x_linear: torch.Tensor,
+                 out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Per-token mean of x^2 over the rank's hidden slice, both branches: [2, T] fp32."""
+    T, Hd = x_attn.shape
+    _req(x_attn, "x_attn", torch.bfloat16)
+    _req(x_linear, "x_linear", torch.bfloat16)
+    if x_linear.shape != x_attn.shape:
+        raise ValueError("the two branches must have the same shape")
+    if out is None:
+        out = torch.empty(2, T, dtype=torch.float32, device=x_attn.device)
+    check(lib().hymeta_branch_sumsq(_ptr(x_attn), _ptr(x_linear), _ptr(out), T, Hd,
+                                    x_attn.stride(0), x_linear.stride(0), _stream()),
+          "hymeta_branch_sumsq")
+    return out
+
+
+def branch_norm_merge(x_attn: torch.Tensor, x_linear: torch.Tensor, w_attn: torch.Tensor,
+                      w_linear: torch.Tensor, eps: float, tp_world: int = 1,
+                      means: Optional[torch.Tensor] = None, group=None,
+                      out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """``((norm1(out_attn) + norm2(out_linear)) / 2).to(bfloat16)`` of the 70B layer
+    (modeling_hymeta.py:909-919, HymetaRMSNormTP :151-173).  x_* [T, hidden/tp] bf16, w_* the
+    rank's fp32 weight slice.  tp_world > 1: the per-token means are computed by
+    ``branch_sumsq`` and summed over ``group`` with ONE all-reduce of 8*T bytes (pass ``means``
+    to supply an already reduced buffer)."""
+    T, Hd = x_attn.shape
+    for n, t in (("x_attn", x_attn), ("x_linear", x_linear)):
+        _req(t, n, torch.bfloat16)
+    for n, t in (("w_attn", w_attn), ("w_linear", w_linear)):
+        _req(t, n, torch.float32)
+        if t.numel() != Hd:
+            raise ValueError(f"{n} must hold hidden/tp = {Hd} elements")
+    if x_linear.shape != x_attn.shape:
+        raise ValueError("the two branches must have the same shape")
+    if tp_world > 1 and means is None:
+        import torch.distributed as dist
+        means = branch_sumsq(x_attn, x_linear)
+        dist.all_reduce(means, group=group)
+    if means is not None:
+        _req(means, "means", torch.float32)
+        if means.numel() != 2 * T or not means.is_contiguous():
+            raise ValueError("means must be a contiguous [2, T] fp32 buffer")
+    if out is None:
+        out = torch.empty(T, Hd, dtype=torch.bfloat16, device=x_attn.device)
+    check(lib().hymeta_branch_norm_merge(
+        _ptr(x_attn), _ptr(x_linear), _ptr(means), _ptr(w_attn), _ptr(w_linear), _ptr(out), T, Hd,
+        int(tp_world), float(eps), x_attn.stride(0), x_linear.stride(0), out.stride(0), _stream()),
+        "hymeta_branch_norm_merge")
+    return out
+
+
 # ----------------------------------------------------------------------------------- a8
 def _workspace(nbytes: int, device) -> torch.Tensor:
     key = device.index        # one workspace per device: calls on one device are stream-ordered by the caller
