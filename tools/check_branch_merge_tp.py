@@ -1,0 +1,68 @@
+#!/usr/bin/env python3
+"""N-GPU check of the one exchange adjacent to the path: the 70B branch merge with
+the hidden size sharded over the tensor-parallel ranks, per-token means summed by ONE NCCL
+all-reduce of 8*T bytes.  Every rank checks its slice against the oracle restatement of
+HymetaRMSNormTP evaluated on the full (replicated, same seed) activations.
+  torchrun --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 tools/check_branch_merge_tp.py"""
+import os
+import sys
+import time
+
+import torch
+import torch.distributed as dist
+
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), ".."))
+from oracle import gla as ogla                      # checker only
+from vllm_hymeta_b200 import ops
+
+
+def main():
+    rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+    torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", 0)))
+    if world > 1:
+        dist.init_process_group("nccl")
+    T, hidden, eps = 4096, 3584, 1e-6
+    gen = torch.Generator().manual_seed(0)           # same data on every rank
+    xa = (torch.randn(T, hidden, generator=gen) * 3).bfloat16()
+    xl = (torch.randn(T, hidden, generator=gen) * 0.2).bfloat16()
+    w1 = 1 + 0.1 * torch.randn(hidden, generator=gen)
+    w2 = 1 + 0.1 * torch.randn(hidden, generator=gen)
+    hl = hidden // world
+    s = slice(rank * hl, (rank + 1) * hl)
+    sl = [slice(r * hl, (r + 1) * hl) for r in range(world)]
+    tot = [sum(x[:, q].float().pow(2).mean(-1, keepdim=True, dtype=torch.float32) for q in sl) for x in (xa, xl)]
+    ref = ogla.branch_norm_merge(xa[:, s], xl[:, s], w1[s], w2[s], eps, world,
+                                 (lambda v: tot[0], lambda v: tot[1]))
+    dxa, dxl = xa[:, s].cuda().contiguous(), xl[:, s].cuda().contiguous()
+    dw1, dw2 = w1[s].cuda().contiguous(), w2[s].cuda().contiguous()
+    got = ops.branch_norm_merge(dxa, dxl, dw1, dw2, eps, tp_world=world)      # all-reduce inside
+    torch.cuda.synchronize()
+    diff = (got.float().cpu() - ref.float()).abs()
+    bad = int((diff > 2.0 ** -6 * ref.float().abs().clamp(min=1.0)).sum())
+    neq = float((diff > 0).float().mean())
+    # timing: sumsq + all-reduce + merge, device events, max over ranks
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    for _ in range(3):
+        ops.branch_norm_merge(dxa, dxl, dw1, dw2, eps, tp_world=world)
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    ev0.record()
+    for _ in range(20):
+        ops.branch_norm_merge(dxa, dxl, dw1, dw2, eps, tp_world=world)
+    ev1.record()
+    torch.cuda.synchronize()
+    us = torch.tensor([ev0.elapsed_time(ev1) / 20 * 1e3], device="cuda")
+    if world > 1:
+        dist.all_reduce(us, op=dist.ReduceOp.MAX)
+    print(f"rank {rank}/{world}: slice [{s.start}:{s.stop}] bad={bad} differing={neq:.3%} "
+          f"merge+exchange {us.item():.1f} us (max over ranks, T={T})", flush=True)
+    ok = torch.tensor([int(bad == 0 and neq <= 0.02)], device="cuda")
+    if world > 1:
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        dist.destroy_process_group()
+    sys.exit(0 if ok.item() else 1)
+
+
+if __name__ == "__main__":
+    main()
