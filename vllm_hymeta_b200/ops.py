@@ -140,18 +140,30 @@ def _gla_workspace(device, nbytes: int) -> torch.Tensor:
 
 def gla_prefill_seg_len(chains: int, max_seqlen: int, device=None, min_seg: int = 256) -> int:
     """Segment length for the sequence-parallel prefill, or 0 for the single-pass form.  One CTA per
-    SM walks one chain, so segmenting pays only when there are fewer chains than SMs; the summary
-    pass re-reads k/v/g (~18% extra traffic), so whole waves of full sequences are left alone."""
+    SM walks one chain, so the launch is quantised in waves of ``sms`` CTAs: candidates are the
+    segment counts that just fill 1, 2, 4 or 8 waves (chains * n_segs <= w * sms).  Measured on B200
+    (tools/sweep_gla_segs.py) the three-pass form costs ~1.5x its ideal w * T / n_segs (the summary
+    pass re-reads k/v/g), so it is taken only when that still beats ceil(chains / sms) full-length
+    waves -- never for whole waves of full sequences (config 2), always for few long chains."""
     dev = torch.cuda.current_device() if device is None or device.index is None else device.index
     sms = _SM_COUNT.get(dev)
     if sms is None:
         sms = _SM_COUNT[dev] = torch.cuda.get_device_properties(dev).multi_processor_count
-    if chains <= 0 or chains >= sms or max_seqlen < 2 * min_seg:
+    if chains <= 0 or max_seqlen < 2 * min_seg:
         return 0
-    n_segs = min(-(-2 * sms // chains), max_seqlen // min_seg)
-    if n_segs <= 1:
+    best_cost, best_ns = float(-(-chains // sms)), 1          # single pass: full-length waves
+    for w in (1, 2, 4, 8):
+        ns = min((w * sms) // chains, max_seqlen // min_seg)
+        if ns < 2:
+            continue
+        # + a small per-segment term (workspace state round trip, pipeline ramp): among fills that
+        # model the same, the sweep favours the fewer, longer segments
+        cost = -(-chains * ns // sms) * 1.5 / ns + 0.002 * ns
+        if cost < best_cost - 1e-9:
+            best_cost, best_ns = cost, ns
+    if best_ns <= 1:
         return 0
-    seg = -(-max_seqlen // n_segs)
+    seg = -(-max_seqlen // best_ns)
     return -(-seg // 16) * 16
 
 
