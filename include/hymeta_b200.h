@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define HYMETA_ABI_VERSION 2
+#define HYMETA_ABI_VERSION 3   /* 3: + rope_kv_write, *_gnorm, branch_*, slot_mgr_* */
 
 typedef enum {
   HYMETA_OK = 0,

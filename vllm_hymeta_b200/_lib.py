@@ -71,7 +71,7 @@ def lib() -> C.CDLL:
         for name, (res, args) in SIGNATURES.items():
             fn = getattr(h, name)      # AttributeError if the library lacks a declared symbol
             fn.restype, fn.argtypes = res, args
-        if h.hymeta_abi_version() != 2:
+        if h.hymeta_abi_version() != 3:
             raise ImportError("hymeta_b200 ABI version mismatch")
         _lib = h
     return _lib
