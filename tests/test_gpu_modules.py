@@ -427,3 +427,24 @@ def test_branch_norm_merge(ops, T, hidden, tp):
     assert torch.equal(x_in, got2)
     with pytest.raises(ValueError):
         ops.branch_norm_merge(keep, keep, w1[:5].to(DEV), w2[sl[0]].to(DEV).contiguous(), eps)
+
+
+def test_branch_norm_merge_edge_cases(ops):
+    e = torch.empty(0, 3584, dtype=torch.bfloat16, device=DEV)
+    w = torch.ones(3584, device=DEV)
+    assert ops.branch_norm_merge(e, e, w, w, 1e-6).shape == (0, 3584)          # empty batch: no-op
+    assert ops.branch_sumsq(e, e).shape == (2, 0)
+    x = torch.randn(4, 100, device=DEV).bfloat16()                              # hidden not a multiple of 8
+    with pytest.raises(ValueError):
+        ops.branch_norm_merge(x, x, torch.ones(100, device=DEV), torch.ones(100, device=DEV), 1e-6)
+    with pytest.raises(ValueError):
+        ops.branch_norm_merge(e.cpu(), e.cpu(), w, w, 1e-6)                     # no CPU path
+    # wide rows (> 3584) take the streaming kernel: same arithmetic
+    gen = torch.Generator().manual_seed(8)
+    xa = torch.randn(33, 8192, generator=gen).bfloat16()
+    xl = torch.randn(33, 8192, generator=gen).bfloat16()
+    w1, w2 = 1 + 0.1 * torch.randn(8192, generator=gen), 1 + 0.1 * torch.randn(8192, generator=gen)
+    ref = ogla.branch_norm_merge(xa, xl, w1, w2, 1e-5)
+    got = ops.branch_norm_merge(xa.to(DEV), xl.to(DEV), w1.to(DEV), w2.to(DEV), 1e-5)
+    torch.cuda.synchronize()
+    _assert_ulp_close(got, ref, "branch merge, wide rows", floor=1.0)
