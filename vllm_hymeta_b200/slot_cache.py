@@ -87,7 +87,10 @@ class NativeSlotAllocator:
     def __del__(self):
         h, self._h = getattr(self, "_h", None), None
         if h:
-            self._lib.hymeta_slot_mgr_destroy(h)
+            try:
+                self._lib.hymeta_slot_mgr_destroy(h)
+            except Exception:          # interpreter shutdown: ctypes may already be torn down
+                pass
 
     @staticmethod
     def _ids(ids) -> bytes:
