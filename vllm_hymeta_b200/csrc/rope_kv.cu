@@ -41,17 +41,20 @@ __device__ __forceinline__ void rope8(const uint4& x, const uint4& y, const uint
 
 // One work item = (token, head of [q | k | v], 16-byte chunk c of the first half) and the matching
 // chunk of the second half: 2 x 16 B in, 2 x 16 B out (x2 for k: k_out and the page).
+// IdxT = uint32_t whenever the item count fits (always in practice: T < 7.4 M tokens at 36 heads):
+// the per-item div/mod by the head count is then 32-bit instead of emulated 64-bit arithmetic.
+template <typename IdxT>
 __global__ void __launch_bounds__(256) rope_kv_write_kernel(const RopeKvParams p) {
   constexpr int HC = kD / 16;  // chunks per half row (8)
   pdl_wait();
   pdl_launch_dependents();
   const int heads = p.H + 2 * p.Hkv;
-  const int64_t total = (int64_t)p.T * heads * HC;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
-       i += (int64_t)gridDim.x * blockDim.x) {
+  const IdxT total = (IdxT)p.T * (IdxT)heads * HC;
+  const IdxT stride = (IdxT)gridDim.x * blockDim.x;
+  for (IdxT i = (IdxT)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
     const int c = (int)(i % HC);
-    const int hh = (int)((i / HC) % heads);
-    const int t = (int)(i / ((int64_t)HC * heads));
+    const int hh = (int)((i / HC) % (IdxT)heads);
+    const int64_t t = (int64_t)(i / ((IdxT)HC * (IdxT)heads));
     const bool is_meta = t < p.n_meta;
     if (hh >= p.H + p.Hkv) {  // value head: plain copy into the page / meta cache
       const int h = hh - p.H - p.Hkv;
@@ -149,7 +152,11 @@ extern "C" int hymeta_rope_kv_write_paged(
   const int64_t total = (int64_t)T * (H + 2 * Hkv) * (kD / 16);
   const int64_t want = (total + 255) / 256;
   const int blocks = (int)(want < 148 * 8 ? want : 148 * 8);
-  launch_pdl(rope_kv_write_kernel, dim3(blocks), dim3(256), 0, (cudaStream_t)stream, p);
+  // the grid-stride loop adds `stride` past `total`: keep head-room below 2^32 for the 32-bit form
+  if (total < (int64_t)0xf0000000LL)
+    launch_pdl(rope_kv_write_kernel<uint32_t>, dim3(blocks), dim3(256), 0, (cudaStream_t)stream, p);
+  else
+    launch_pdl(rope_kv_write_kernel<unsigned long long>, dim3(blocks), dim3(256), 0, (cudaStream_t)stream, p);
   count_launch();
   return check_launch();
 }
