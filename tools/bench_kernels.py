@@ -264,6 +264,7 @@ if __name__ == "__main__":
         bench_branch_merge(65536, flush=flush)
     if a.which in ("all", "gnorm"):
         bench_gla_gnorm(64, 8192, 64)
+        bench_gla_gnorm(8, 1024, 1000)
     if a.which in ("all", "rope_kv"):
         bench_rope_kv(64, flush=flush)
         bench_rope_kv(524288, flush=flush)
