@@ -78,7 +78,9 @@ constexpr int GD_SMEM = GD_SLOT + 32;
 template <int GT, bool GF32, bool GN>
 __global__ void __launch_bounds__(GD_THREADS, 2) gla_decode_kernel(const GlaDecodeParams p, const int n_items) {
   extern __shared__ __align__(128) uint8_t smem[];
-  __shared__ float s_norm[16];                      // g_norm epilogue: [parity][half-CTA][warp] sums of squares
+  __shared__ float s_norm[32];                      // g_norm epilogue: [head][warp of the half-CTA] sums of squares
+  __shared__ float s_gw[GN ? kD : 1];               // g_norm weight, staged once per CTA (a per-item global load
+                                                    // sits exposed on the epilogue's critical path)
   float (*s_q)[8] = reinterpret_cast<float (*)[8]>(smem + GD_SQ);
   uint2* s_kg = reinterpret_cast<uint2*>(smem + GD_SKG);
   const uint32_t ring = smem_u32(smem);
@@ -88,6 +90,7 @@ __global__ void __launch_bounds__(GD_THREADS, 2) gla_decode_kernel(const GlaDeco
   const int gs = gridDim.x;
   pdl_wait();
   pdl_launch_dependents();
+  if (GN && tid < kD) s_gw[tid] = __bfloat162float(p.gnorm_w[tid]);   // visible after the first __syncthreads
   const int gs_b = gs / p.Hs, gs_h = gs % p.Hs;     // item stride decomposed: no per-item division
 
   // Item bookkeeping without registers held across the loop: (b, hs) of items k, k+2, k+4 advance
@@ -259,31 +262,49 @@ __global__ void __launch_bounds__(GD_THREADS, 2) gla_decode_kernel(const GlaDeco
       }
     }
     __syncthreads();
-    {
+    if (GN) {
+      // 7B g_norm (model_for_7B/gla_attention.py:177,233): vLLM RMSNorm over the head's 128 outputs
+      // of the bf16-rounded o: y = bf16(bf16(o * rstd) * w).  The 128 threads of a half-CTA hold one
+      // head at a time (up to 4 heads each): all sums of squares are reduced first (warp shuffle,
+      // 4 warp partials per head in smem), ONE 128-thread named barrier, then scale and store.
       const float* rp = s_red + (tid >> 7) * kD + (tid & 127);
-      const float gw = GN ? __bfloat162float(p.gnorm_w[tid & 127]) : 0.f;
-      int it = 0;
-#pragma unroll 1
-      for (int hh = tid >> 7; hh < G; hh += 2, op += 2 * p.o_sh, rp += 2 * kD, ++it) {
-        float x = 0.f;
+      float xs[4];
 #pragma unroll
-        for (int w = 0; w < 8; ++w) x += rp[w * GT * kD];
-        if (GN) {
-          // 7B g_norm (model_for_7B/gla_attention.py:177,233): vLLM RMSNorm over the head's 128
-          // outputs of the bf16-rounded o: y = bf16(bf16(o * rstd) * w).  The 128 threads of this
-          // half-CTA hold one head; 4 warp sums meet in smem behind a 128-thread named barrier
-          // (buffers alternate per iteration, so one barrier per head is enough).
+      for (int n = 0; n < 4; ++n) {
+        const int hh = (tid >> 7) + 2 * n;
+        xs[n] = 0.f;
+        if (hh < G) {
+          float x = 0.f;
+#pragma unroll
+          for (int w = 0; w < 8; ++w) x += rp[(2 * n * kD) + w * GT * kD];
           const float xb = round_bf16(x);
+          xs[n] = xb;
           float ss = xb * xb;
 #pragma unroll
           for (int off = 16; off > 0; off >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, off);
-          float* sn = s_norm + (it & 1) * 8 + (tid >> 7) * 4;
-          if (lane == 0) sn[(tid >> 5) & 3] = ss;
-          if (tid >> 7) asm volatile("bar.sync 2, 128;" ::: "memory");
-          else asm volatile("bar.sync 1, 128;" ::: "memory");
-          const float tot = (sn[0] + sn[1]) + (sn[2] + sn[3]);
-          x = round_bf16(xb * rsqrtf(tot * (1.f / kD) + p.gnorm_eps)) * gw;
+          if (lane == 0) s_norm[hh * 4 + ((tid >> 5) & 3)] = ss;
         }
+      }
+      if (tid >> 7) asm volatile("bar.sync 2, 128;" ::: "memory");
+      else asm volatile("bar.sync 1, 128;" ::: "memory");
+      const float gw = s_gw[tid & 127];
+#pragma unroll
+      for (int n = 0; n < 4; ++n) {
+        const int hh = (tid >> 7) + 2 * n;
+        if (hh < G) {
+          const float* sn = s_norm + hh * 4;
+          const float tot = (sn[0] + sn[1]) + (sn[2] + sn[3]);
+          op[(int64_t)2 * n * p.o_sh] =
+              __float2bfloat16_rn(round_bf16(xs[n] * rsqrtf(tot * (1.f / kD) + p.gnorm_eps)) * gw);
+        }
+      }
+    } else {
+      const float* rp = s_red + (tid >> 7) * kD + (tid & 127);
+#pragma unroll 1
+      for (int hh = tid >> 7; hh < G; hh += 2, op += 2 * p.o_sh, rp += 2 * kD) {
+        float x = 0.f;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) x += rp[w * GT * kD];
         *op = __float2bfloat16_rn(x);
       }
     }
