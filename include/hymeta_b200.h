@@ -12,8 +12,14 @@
  *   - activations / KV / state are bf16 (uint16 storage); gates are fp32 or bf16
  *   - strides are in ELEMENTS; the innermost (head_dim) stride is always 1
  *   - `stream` is a cudaStream_t passed as void*
- *   - no allocation, no synchronisation, no global state: every call only
- *     enqueues kernels on `stream` and is CUDA-graph-capture safe
+ *   - no allocation and no synchronisation: every call only enqueues kernels on
+ *     `stream` and is CUDA-graph-capture safe.  Process-wide state is limited to
+ *     (a) the per-device "max dynamic shared memory" function attribute, set on
+ *     the first launch on each device (thread safe), (b) the launch counter and
+ *     the thread-local last-error code below, and (c) two tuning knobs read ONCE
+ *     from the environment: HYMETA_PDL=0 disables programmatic dependent launch
+ *     between the decode-step kernels, HYMETA_SWA_DEC_TPS=<n> overrides the
+ *     split-K plan of the SWA decode (tiles per split; 0/unset = built-in rule)
  *   - return 0 on success, a negative hymeta_status otherwise
  *   - head_dim (D) must be 128 (the only geometry the reference models use,
  *     SURVEY F2)
@@ -28,7 +34,8 @@
 extern "C" {
 #endif
 
-#define HYMETA_ABI_VERSION 3   /* 3: + rope_kv_write, *_gnorm, branch_*, slot_mgr_* */
+#define HYMETA_ABI_VERSION 4   /* 3: + rope_kv_write, *_gnorm, branch_*, slot_mgr_*; 4: paged-key prefill,
+                                  new_slot_mapping in the fused decode */
 
 typedef enum {
   HYMETA_OK = 0,
@@ -238,8 +245,12 @@ int hymeta_swa_meta_decode_paged(const void* q, const void* k_cache, const void*
 /* a8 + a9 fused: the same decode with (1) the step's paged-KV write folded in --
  * replaces reshape_and_cache_flash (meta_attention.py:790-799) followed by the decode call
  * (:954-981): new_k/new_v [B, Hkv, D] are the K/V of the token at position cache_seqlens[b]-1; the
- * kernel stores them to cache[block_tables[b, p / block_size], p % block_size] and attends to them
- * from registers, so the pages need not hold that row yet (null: the pages already hold it) -- and
+ * kernel stores them to their page and attends to them from registers, so the pages need not hold
+ * that row yet (null: the pages already hold it).  The destination is new_slot_mapping[b] in
+ * reshape_and_cache_flash's convention (slot = block * block_size + offset; slot < 0 = padded row,
+ * nothing is stored -- CUDA-graph padding, meta_attention.py:557-562), or, when new_slot_mapping
+ * is null, cache[block_tables[b, p / block_size], p % block_size] with p = cache_seqlens[b]-1 (then
+ * padded rows MUST carry cache_seqlens[b] = 0 so that no store happens) -- and
  * (2) the split-K combine folded into the split kernel: `tickets` is
  * hymeta_swa_decode_ticket_bytes(B, H, Hkv) bytes of int32, ZERO before the first call; the kernel
  * leaves it zero (null: separate combine launch).  One launch per layer-step instead of three. */
@@ -257,7 +268,8 @@ int hymeta_swa_meta_decode_paged_fused(const void* q, void* k_cache, void* v_cac
                                        int64_t mk_st, int64_t mk_sh, int64_t mv_st, int64_t mv_sh,
                                        const void* new_k, const void* new_v,
                                        int64_t nk_sb, int64_t nk_sh, int64_t nv_sb, int64_t nv_sh,
-                                       int32_t* tickets, void* stream);
+                                       const int64_t* new_slot_mapping, int32_t* tickets,
+                                       void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * a7  SWA + meta-prefix varlen prefill -- replaces metatoken_flash_attn_varlen_func
@@ -271,9 +283,17 @@ int hymeta_swa_meta_decode_paged_fused(const void* q, void* k_cache, void* v_cac
  * q2: [M, H, D] meta queries or null; when given they attend to the meta keys only,
  * bidirectionally (:261-275), and their rows come FIRST in `out` (:283):
  * out: [(M if q2) + Tq, H, D].
- * If block_tables != null the keys are read from the paged cache instead (prefix/chunked
- * prefill, meta_attention.py:886-919): k1,v1 are then [num_blocks, block_size, Hkv, D] caches
- * addressed like the decode entry point and cu_k holds cumulative seq_lens.
+ * If block_tables != null the keys are read from the PAGED cache instead -- prefix-cache hit /
+ * chunked prefill (meta_attention.py:886-919) and multi-token decode (:924-953): k1,v1 are then the
+ * [num_blocks, block_size, Hkv, D] caches (k_st/v_st = row stride inside a block, kc_sblk/vc_sblk =
+ * block stride, Tk = num_blocks * block_size, block_size % 16 == 0), block_tables is
+ * [N, max_blocks] with row stride bt_stride, and cu_k holds cumulative seq_lens: request n owns
+ * logical key positions 0 .. cu_k[n+1]-cu_k[n]-1, position p at
+ * cache[block_tables[n, p / block_size], p % block_size]; its queries are the LAST
+ * cu_q[n+1]-cu_q[n] positions.  Cache rows outside the visible range are never used as data (they
+ * may hold recycled-page garbage / NaN).  The reference passes the fresh key tensor together with
+ * block_tables here, which flash-attn's paged API cannot accept; this implements the
+ * evident intent (keys through the block table), like vLLM's stock backend.
  * ---------------------------------------------------------------------------------------------- */
 int hymeta_swa_meta_prefill_varlen(const void* q1, const void* k1, const void* v1, const void* q2,
                                    const void* meta_k, const void* meta_v, void* out,

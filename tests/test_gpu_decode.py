@@ -302,3 +302,49 @@ def test_swa_decode_fused_graph_capture(ops):
     torch.cuda.synchronize()
     assert torch.equal(out.view(torch.int16), eager.view(torch.int16))
     assert out[1].abs().max().item() == 0          # zero-length (padded) request
+
+
+def test_swa_decode_fused_write_padded_rows_by_slot_mapping(ops):
+    """CUDA-graph padded batch as vLLM builds it (meta_attention.py:557-562): padded rows carry
+    seq_len 1, an all-zero block-table row and slot -1.  With ``new_slot_mapping`` the fused write
+    follows reshape_and_cache_flash: slot < 0 stores nothing, so physical block 0 (owned by a LIVE
+    sequence here) stays bit-identical; live rows land exactly where kv_write_paged puts them."""
+    bs, wl, H, Hkv, D = 16, 63, 14, 2, 128
+    lens = [40, 1, 200, 1]                      # rows 1 and 3 are padding
+    live = [True, False, True, False]
+    kc, vc, tables, _, _ = make_paged([40, 200], Hkv, D, bs, seed=21, max_blocks=16)
+    # make block 0 belong to live request 0 so a stray store would corrupt it
+    blk = int(tables[0, 0])
+    if blk != 0:                                # swap the labels (and contents) of blocks 0 and blk
+        kc[[0, blk]] = kc[[blk, 0]]
+        vc[[0, blk]] = vc[[blk, 0]]
+        t = tables.clone()
+        t[tables == blk] = 0
+        t[tables == 0] = blk                    # (unused zero-padded columns too: never read)
+        tables = t
+    full = torch.zeros(4, tables.shape[1], dtype=torch.int32)
+    full[0], full[2] = tables[0], tables[1]
+    gen = torch.Generator().manual_seed(5)
+    q = torch.randn(4, H, D, generator=gen).bfloat16().to(DEV)
+    nk = torch.randn(4, Hkv, D, generator=gen).bfloat16()
+    nv = torch.randn(4, Hkv, D, generator=gen).bfloat16()
+    slot = torch.full((4,), -1, dtype=torch.int64)
+    for i, L in enumerate(lens):
+        if live[i]:
+            slot[i] = int(full[i, (L - 1) // bs]) * bs + (L - 1) % bs
+    d_lens = torch.tensor(lens, dtype=torch.int32, device=DEV)
+    kc_a, vc_a = kc.to(DEV), vc.to(DEV)
+    ops.kv_write_paged(nk.to(DEV), nv.to(DEV), kc_a, vc_a, slot.to(DEV))
+    out_a = ops.swa_meta_decode_paged(q, kc_a, vc_a, full.to(DEV), d_lens, None, None, wl)
+    kc_b, vc_b = kc.to(DEV), vc.to(DEV)
+    out_b = ops.swa_meta_decode_paged(q, kc_b, vc_b, full.to(DEV), d_lens, None, None, wl,
+                                      new_k=nk.to(DEV), new_v=nv.to(DEV),
+                                      new_slot_mapping=slot.to(DEV))
+    torch.cuda.synchronize()
+    assert torch.equal(kc_a.view(torch.int16), kc_b.view(torch.int16)), "padded row wrote a page"
+    assert torch.equal(vc_a.view(torch.int16), vc_b.view(torch.int16))
+    rows = torch.tensor(live)
+    assert torch.equal(out_a[rows].view(torch.int16), out_b[rows].view(torch.int16))
+    with pytest.raises(ValueError):
+        ops.swa_meta_decode_paged(q, kc_b, vc_b, full.to(DEV), d_lens, None, None, wl,
+                                  new_slot_mapping=slot.to(DEV))

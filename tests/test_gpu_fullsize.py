@@ -154,3 +154,45 @@ def test_gla_prefill_long_context_prefix_and_continuation(ops, T):
     # the continuation restarts from the bf16-rounded slot state: within bf16 state rounding
     assert_close(b, o_chain[cut:].float(), f"GLA T={T}: continuation through the slot state", rel_rms=4e-3)
     assert_close(s_split, s_chain.float(), f"GLA T={T}: final state after the split run", rel_rms=4e-3)
+
+
+# ------------------------------------------------------------------ config 2: the full bench batch
+def test_config2_full_batch_prefill_64x8192_sampled_rows(ops):
+    """The bench.py launch shapes themselves: 64 packed sequences x 8192 tokens (524 288 rows) in ONE
+    launch of each prefill kernel at the 7B geometry (28/4 heads, window 4096 keys before self,
+    no meta) -- the ``blockIdx.z = n`` x ``n_qpairs`` grid and the 256-chain GLA grid at benchmark
+    size.  Sampled rows of sampled sequences against the fp32 oracle evaluated for those rows, the
+    GLA final states of two sequences against the oracle recurrence, and every sequence's rows
+    checked finite."""
+    N, L, H, Hkv, W = 64, 8192, 28, 4, 4096
+    T = N * L
+    gen = torch.Generator(device=DEV).manual_seed(64)
+    cu = _i32([i * L for i in range(N + 1)])
+    # ---- SWA prefill
+    q, k, v = (torch.randn(T, h, D, generator=gen, device=DEV).bfloat16() for h in (H, Hkv, Hkv))
+    out = ops.swa_meta_prefill_varlen(q, k, v, None, None, None, cu, cu, L, W)
+    torch.cuda.synchronize()
+    assert torch.isfinite(out.float()).all()
+    for n in (0, 1, 31, 63):
+        for i in (0, 127, 128, 255, 256, 4095, 4096, 4097, 6000, 8191):
+            lo = max(0, i - W)
+            r = n * L
+            ref, _ = oswa.swa_meta_dense(q[r + i:r + i + 1].cpu(), k[r + lo:r + i + 1].cpu(),
+                                         v[r + lo:r + i + 1].cpu(), None, None, None, -1)
+            assert_close(out[r + i:r + i + 1], ref, f"config-2 SWA prefill seq {n} row {i}")
+    del out
+    # ---- GLA prefill (7B gate: relu q/k, g = logsigmoid/16), slot states written in-kernel
+    qg = torch.relu(q)
+    kg = torch.relu(k)
+    g = (torch.nn.functional.logsigmoid(torch.randn(T, Hkv, D, generator=gen, device=DEV)) / 16).bfloat16()
+    state = torch.zeros(N, Hkv, D, D, dtype=torch.bfloat16, device=DEV)
+    slots = torch.randperm(N, generator=gen, device=DEV).to(torch.int32)
+    o = ops.gla_prefill_varlen(qg, kg, v, g, state, cu, slots, _i32([0] * N), max_seqlen=L)
+    torch.cuda.synchronize()
+    assert torch.isfinite(o.float()).all()
+    for n in (0, 63):
+        r = slice(n * L, (n + 1) * L)
+        ro, rS = ogla.gla_chunked(qg[r].cpu(), kg[r].cpu(), v[r].cpu(), g[r].cpu())
+        rows = [0, 1, 15, 16, 63, 64, 1000, 4096, 8191]
+        assert_close(o[r][rows], ro[rows], f"config-2 GLA prefill seq {n} sampled rows")
+        assert_close(state[int(slots[n])], rS[:: H // Hkv], f"config-2 GLA final state seq {n}")

@@ -188,8 +188,11 @@ def test_gated_linear_attention_7b_mixed_batch(ops):
     rq, rk, rg = ogla.gate_7b(q, k, gk.view(T, Hkv, D))
     ref_state = state.clone()
     n_pf = sum(lens)
+    # request 0 is NEW (context 0) on a recycled, non-zero slot: it must start from zero
+    # (modeling_gla_swa.py:391-414); request 1 continues a chunked prefill from its slot state
+    ctx = [0, 64, 200, 300]
     o_pf = ogla.gla_prefill_varlen(rq[:n_pf], rk[:n_pf], v[:n_pf], rg[:n_pf], ref_state,
-                                   [0, lens[0], n_pf], slots[:2], [ogla.INIT_SLOT] * 2)
+                                   [0, lens[0], n_pf], slots[:2], [ogla.INIT_ZERO, ogla.INIT_SLOT])
     o_dec = ogla.gla_decode_step(rq[n_pf:], rk[n_pf:], v[n_pf:], rg[n_pf:], ref_state,
                                  torch.tensor(slots[2:]))
     ref = ogla.rms_norm_head(torch.cat([o_pf, o_dec]), w, 1e-6).reshape(T, H * D)
@@ -197,7 +200,7 @@ def test_gated_linear_attention_7b_mixed_batch(ops):
     core = GatedLinearAttention(H * D, H, Hkv, norm_eps=1e-6, g_norm_weight=w.to(DEV))
     d_state = state.to(DEV)
     params = GLACacheParams(d_state, torch.tensor(slots, dtype=torch.int32, device=DEV))
-    out = core.forward(qkv.to(DEV), gk.to(DEV), params, _md(2, lens, n_dec, [0] * 4))
+    out = core.forward(qkv.to(DEV), gk.to(DEV), params, _md(2, lens, n_dec, ctx))
     torch.cuda.synchronize()
     # the norm divides by the row rms, so compare with a slightly wider max-abs band
     assert_close(out, ref, "GatedLinearAttention mixed batch", maxabs_frac=2 ** -6, rel_rms=8e-3)
@@ -261,6 +264,73 @@ def test_flash_attention_backend_warmup_then_decode(ops):
                                       [L + 1 for L in lens], k3[:M], v3[:M], W - 1,
                                       out_dtype=torch.float32)
     assert_close(out2.view(2, H, D), ref2, "FlashAttention decode pass")
+
+
+def test_flash_attention_backend_prefix_hit_chunked_and_multitoken_decode(ops):
+    """``MetaAttentionImpl.forward`` branches that read keys from the paged cache: prefix-cache hit /
+    chunked prefill mixed with a decode row (reference meta_attention.py:886-919), then multi-token
+    decode (``max_decode_query_len > 1``, :924-953).  Pages are written by the same forward."""
+    from vllm_hymeta_b200.attention.meta_attention import MetaAttentionMetadataBuilder, SeqData
+    from vllm_hymeta_b200.models.attention import FlashAttention
+    from vllm_hymeta_b200.models.hymeta_cache import HymetaCacheParams
+    H, Hkv, M, bs, W = 14, 2, 128, 16, 64
+    ctx = [150, 40]                       # already cached (filled by a first no-cache prefill)
+    nb = 48
+    gen = torch.Generator().manual_seed(41)
+    perm = torch.randperm(nb, generator=gen).tolist()
+    tables = [perm[:16], perm[16:21], perm[21:25]]
+    kv_cache = torch.full((2, nb, bs, Hkv, D), float("nan"), dtype=torch.bfloat16)   # unowned rows: NaN
+    layer = FlashAttention(H, Hkv, D, num_meta_tokens=M, sliding_window=W)
+    d_cache = kv_cache.to(DEV)
+    layer.attn.bind_kv_cache(d_cache)
+    k2 = torch.randn(M, Hkv, D, generator=gen).bfloat16()
+    v2 = torch.randn(M, Hkv, D, generator=gen).bfloat16()
+    meta_fa = torch.stack([k2, v2]).to(DEV)
+    params = HymetaCacheParams(torch.empty(0), torch.empty(0), meta_fa, torch.empty(0))
+    rnd = lambda T, h: torch.randn(T, h * D, generator=gen).bfloat16()
+    ref_cache = kv_cache.clone()
+
+    def step(seqs):
+        """seqs: (is_prompt, context, new tokens, table); returns (out, ref rows builder inputs)."""
+        b = MetaAttentionMetadataBuilder(block_size=bs, sliding_window=None, device=DEV,
+                                         chunked_prefill_enabled=True)
+        for is_prompt, c, n, bt in seqs:
+            b.add(SeqData(is_prompt, c + n, n, c, bt), prefix_cache_hit=is_prompt and c > 0)
+        md = b.build()
+        T = sum(n for _, _, n, _ in seqs)
+        q, k, v = rnd(T, H), rnd(T, Hkv), rnd(T, Hkv)
+        out = layer.forward(q.to(DEV), k.to(DEV), v.to(DEV), params, md, has_meta_cache=True)
+        torch.cuda.synchronize()
+        oswa.kv_write_paged(k.view(T, Hkv, D), v.view(T, Hkv, D), ref_cache[0], ref_cache[1],
+                            md.slot_mapping.cpu().tolist())
+        assert torch.equal(torch.nan_to_num(d_cache.cpu().float(), nan=7.0),
+                           torch.nan_to_num(ref_cache.float(), nan=7.0)), "paged KV write must be bit-exact"
+        return out.view(T, H, D), q.view(T, H, D), md
+
+    # ---- pass 1: plain prompts (no cache hit) fill the pages
+    step([(True, 0, ctx[0], tables[0]), (True, 0, ctx[1], tables[1])])
+
+    # ---- pass 2: [chunk of request 0 on top of its 150 cached tokens | a new prompt | decode of request 1]
+    new0, new2 = 70, 33
+    out, q, md = step([(True, ctx[0], new0, tables[0]), (True, 0, new2, tables[2]),
+                       (False, ctx[1], 1, tables[1])])
+    assert md.num_prefills == 2 and md.num_decode_tokens == 1
+    bt_rows = md.block_tables.cpu().tolist()
+    ref_p = oswa.swa_meta_prefill_paged(q[:new0 + new2], ref_cache[0], ref_cache[1], bt_rows[:2],
+                                        [0, new0, new0 + new2], [ctx[0] + new0, new2], k2, v2, W - 1,
+                                        out_dtype=torch.float32)
+    ref_d = oswa.swa_meta_decode_paged(q[new0 + new2:], ref_cache[0], ref_cache[1], bt_rows[2:],
+                                       [ctx[1] + 1], k2, v2, W - 1, out_dtype=torch.float32)
+    assert_close(out, torch.cat([ref_p, ref_d]), "prefix-hit + chunked prefill + decode")
+
+    # ---- pass 3: multi-token decode (3 and 2 new tokens on requests 0 and 1)
+    L0, L1 = ctx[0] + new0, ctx[1] + 1
+    out, q, md = step([(False, L0, 3, tables[0]), (False, L1, 2, tables[1])])
+    assert md.max_decode_query_len == 3 and md.num_prefills == 0
+    bt_rows = md.block_tables.cpu().tolist()
+    ref = oswa.swa_meta_prefill_paged(q, ref_cache[0], ref_cache[1], bt_rows, [0, 3, 5],
+                                      [L0 + 3, L1 + 2], k2, v2, W - 1, out_dtype=torch.float32)
+    assert_close(out, ref, "multi-token decode over the paged cache")
 
 
 # ------------------------------------------------------------------------------------- f3 (fused prologue)

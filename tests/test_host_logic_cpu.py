@@ -33,7 +33,25 @@ def test_slot_allocator_lifecycle():
     assert a.cache_indices_mapping["r1"] == {1: s0[1]}
 
 
-def test_cache_managers_cpu_tensors():
+@pytest.fixture
+def fake_state_ops(monkeypatch):
+    """The cache managers have no CPU branch (the product has no CPU fallback): for the host-logic
+    tests the two device kernels they launch are replaced by torch stand-ins with the same
+    contract (state [L, slots, ...]; slots < 0 skipped)."""
+    from vllm_hymeta_b200 import ops
+
+    def copy(state, src, dst):
+        state[:, dst].copy_(state[:, src])
+
+    def zero(state, slots):
+        keep = slots[slots >= 0].long()
+        state[:, keep] = 0
+
+    monkeypatch.setattr(ops, "state_copy_slot", copy)
+    monkeypatch.setattr(ops, "state_zero_slots", zero)
+
+
+def test_cache_managers_cpu_tensors(fake_state_ops):
     L, S, Hs, D, M, Hkv = 2, 3, 2, 8, 4, 1
     m = HymetaCacheManager(torch.bfloat16, (L, S, Hs, D, D), (L, Hs, D, D), (L, 2, M, Hkv, D), device="cpu")
     state, meta_lin, meta_fa, idx = m.current_run_tensors(request_ids_to_seq_ids={"a": [0], "b": [1]},

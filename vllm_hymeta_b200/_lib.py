@@ -35,7 +35,7 @@ SIGNATURES = {
     "hymeta_swa_meta_decode_paged": (_i, [_p] * 9 + [_sz] + [_i] * 8 + [_i64, _i, _f] + [_i64] * 14 + [_p]),
     "hymeta_swa_decode_ticket_bytes": (_sz, [_i] * 3),
     "hymeta_swa_meta_decode_paged_fused": (_i, [_p] * 9 + [_sz] + [_i] * 8 + [_i64, _i, _f] + [_i64] * 14 +
-                                           [_p, _p] + [_i64] * 4 + [_p, _p]),
+                                           [_p, _p] + [_i64] * 4 + [_p, _p, _p]),
     "hymeta_swa_meta_prefill_varlen": (_i, [_p] * 10 + [_i64, _i] + [_i] * 9 + [_f] + [_i64] * 16 + [_p]),
     "hymeta_state_zero_slots": (_i, [_p, _p, _i, _i, _i64, _i64, _i64, _p]),
     "hymeta_state_copy_slot": (_i, [_p, _i, _i, _i, _i64, _i64, _i64, _p]),
@@ -71,7 +71,7 @@ def lib() -> C.CDLL:
         for name, (res, args) in SIGNATURES.items():
             fn = getattr(h, name)      # AttributeError if the library lacks a declared symbol
             fn.restype, fn.argtypes = res, args
-        if h.hymeta_abi_version() != 3:
+        if h.hymeta_abi_version() != 4:
             raise ImportError("hymeta_b200 ABI version mismatch")
         _lib = h
     return _lib

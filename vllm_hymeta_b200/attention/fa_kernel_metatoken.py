@@ -61,9 +61,13 @@ def metatoken_flash_attn_with_kvcache(
     num_meta_tokens=128, dropout_p=0.0, softmax_scale=None, causal=False,
     window_size=(-1, -1), alibi_slopes=None, block_tables=None, softcap=0.0,
     deterministic=False, return_attn_probs=False, attn_mask=None, out: Optional[torch.Tensor] = None,
+    new_key: Optional[torch.Tensor] = None, new_value: Optional[torch.Tensor] = None,
+    new_slot_mapping: Optional[torch.Tensor] = None,
 ):
     """Single-token paged decode (reference fa_kernel_metatoken.py:287-326 -> :124-194).
-    q1 [B,H,D] -> ``[B, 1, H, D]``."""
+    q1 [B,H,D] -> ``[B, 1, H, D]``.  Extension over the reference signature: ``new_key`` /
+    ``new_value`` [B,Hkv,D] + ``new_slot_mapping`` [B] fold the step's ``reshape_and_cache_flash``
+    (meta_attention.py:790-799) into the kernel."""
     _check_unused(dropout_p, alibi_slopes, softcap, attn_mask, return_attn_probs)
     assert causal and window_size[1] in [0, -1]
     if k2 is not None:
@@ -72,5 +76,6 @@ def metatoken_flash_attn_with_kvcache(
     if softmax_scale is None:
         softmax_scale = q1.shape[-1] ** (-0.5)
     o = ops.swa_meta_decode_paged(q1, key_cache, value_cache, block_tables, cache_seqlens, k2, v2,
-                                  _window_left(window_size), scale=softmax_scale, out=out)
+                                  _window_left(window_size), scale=softmax_scale, out=out,
+                                  new_k=new_key, new_v=new_value, new_slot_mapping=new_slot_mapping)
     return o.unsqueeze(1)

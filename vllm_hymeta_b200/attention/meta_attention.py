@@ -408,13 +408,21 @@ class MetaAttentionImpl(AttentionImpl):
         if output_scale is not None:
             raise NotImplementedError("fused output quantization is not supported in MetaAttention.")
         window_size = self.sliding_window
-        if (kv_cache.numel() > 0 and key is not None and value is not None
-                and not getattr(layer, "kv_already_written", False)):
-            # store the new keys/values in the paged cache first (:790-799); skipped when the
-            # fused RoPE prologue (ops.rope_kv_write_paged) already stored them
-            ops.kv_write_paged(key, value, kv_cache[0], kv_cache[1], attn_metadata.slot_mapping.flatten())
         (num_prefill_query_tokens, num_prefill_kv_tokens,
          num_decode_query_tokens) = get_num_prefill_decode_query_kv_tokens(attn_metadata)
+        # store the new keys/values in the paged cache first (:790-799); skipped when the fused RoPE
+        # prologue (ops.rope_kv_write_paged) already stored them.  The rows of single-token decode
+        # requests are not written here: the decode kernel stores them itself (same slots, PAD
+        # slots skipped) and attends to them from registers -- one launch less per layer-step.
+        kv_pending = (kv_cache.numel() > 0 and key is not None and value is not None
+                      and not getattr(layer, "kv_already_written", False))
+        fuse_decode_write = (kv_pending and num_decode_query_tokens > 0
+                             and (attn_metadata.max_decode_query_len or 1) == 1)
+        slot_mapping = attn_metadata.slot_mapping.flatten() if kv_pending else None
+        if kv_pending:
+            n_w = num_prefill_kv_tokens if fuse_decode_write else key.shape[0]
+            if n_w > 0:
+                ops.kv_write_paged(key[:n_w], value[:n_w], kv_cache[0], kv_cache[1], slot_mapping[:n_w])
         num_meta_prefill_tokens = num_prefill_query_tokens
         if query2 is not None:  # meta tokens are not cached yet: they are forwarded together
             num_meta_prefill_tokens += self.num_meta_tokens
@@ -477,5 +485,8 @@ class MetaAttentionImpl(AttentionImpl):
                     value_cache=kv_cache[1], cache_seqlens=decode_meta.seq_lens_tensor,
                     num_meta_tokens=self.num_meta_tokens, softmax_scale=self.scale, causal=True,
                     window_size=window_size, block_tables=decode_meta.block_tables,
-                    out=output[num_meta_prefill_tokens:num_meta_prefill_tokens + num_decode_query_tokens])
+                    out=output[num_meta_prefill_tokens:num_meta_prefill_tokens + num_decode_query_tokens],
+                    new_key=key[num_prefill_kv_tokens:] if fuse_decode_write else None,
+                    new_value=value[num_prefill_kv_tokens:] if fuse_decode_write else None,
+                    new_slot_mapping=slot_mapping[num_prefill_kv_tokens:] if fuse_decode_write else None)
         return output

@@ -4,6 +4,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <atomic>
+
 #include "../../include/hymeta_b200.h"
 
 namespace hymeta {
@@ -21,6 +23,32 @@ inline int check_launch() {
   }
   return HYMETA_OK;
 }
+
+// cudaFuncAttributeMaxDynamicSharedMemorySize is a PER-DEVICE attribute: one flag bit per device
+// ordinal, so a process that drives several GPUs sets it on each of them (thread safe: a redundant
+// set is harmless).
+struct DynSmemAttr {
+  std::atomic<uint64_t> done[4] = {};
+  static uint64_t bit_of(int dev) { return 1ull << (dev & 63); }
+  bool need() {                       // true until mark() ran on the current device
+    int dev = 0;
+    cudaGetDevice(&dev);
+    return !(done[(dev >> 6) & 3].load(std::memory_order_acquire) & bit_of(dev));
+  }
+  void mark() {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    done[(dev >> 6) & 3].fetch_or(bit_of(dev), std::memory_order_release);
+  }
+  template <typename K>
+  static void set(K* kernel, int bytes) {
+    cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  }
+  template <typename K>
+  void ensure(K* kernel, int bytes) {
+    if (need()) { set(kernel, bytes); mark(); }
+  }
+};
 
 // ---- programmatic dependent launch (PDL) ------------------------------------------------------
 // The decode step is a chain of short kernels (kv write -> split-K -> combine -> next layer ...);

@@ -318,13 +318,13 @@ template <int GT>
 static void launch_gla_decode(const GlaDecodeParams& p, bool g_fp32, cudaStream_t st) {
   const long n_items = (long)p.B * p.Hs;
   const int grid = (int)(n_items < 2 * 148 ? n_items : 2 * 148);
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaFuncSetAttribute(gla_decode_kernel<GT, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, GD_SMEM);
-    cudaFuncSetAttribute(gla_decode_kernel<GT, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, GD_SMEM);
-    cudaFuncSetAttribute(gla_decode_kernel<GT, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, GD_SMEM);
-    cudaFuncSetAttribute(gla_decode_kernel<GT, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, GD_SMEM);
-    attr_set = true;
+  static DynSmemAttr attr;   // one per template instantiation of this launcher
+  if (attr.need()) {
+    DynSmemAttr::set(gla_decode_kernel<GT, true, false>, GD_SMEM);
+    DynSmemAttr::set(gla_decode_kernel<GT, false, false>, GD_SMEM);
+    DynSmemAttr::set(gla_decode_kernel<GT, true, true>, GD_SMEM);
+    DynSmemAttr::set(gla_decode_kernel<GT, false, true>, GD_SMEM);
+    attr.mark();
   }
   const dim3 gr(grid), bl(GD_THREADS);
   const int n = (int)n_items;

@@ -658,13 +658,13 @@ extern "C" int hymeta_gla_prefill_varlen_seg_gnorm(
     if ((rc = make_tmap(&tmK, k, 2, 3, dk, sk, braw, false))) return rc;
     if ((rc = make_tmap(&tmV, v, 2, 3, dv, sv, bv, true))) return rc;
   }
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaFuncSetAttribute(gla_prefill_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, GP_SMEM);
-    cudaFuncSetAttribute(gla_prefill_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, GP_SMEM);
-    cudaFuncSetAttribute(gla_prefill_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, GP_SMEM);
-    cudaFuncSetAttribute(gla_prefill_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, GP_SMEM);
-    attr_set = true;
+  static DynSmemAttr attr;
+  if (attr.need()) {
+    DynSmemAttr::set(gla_prefill_kernel<true, false>, GP_SMEM);
+    DynSmemAttr::set(gla_prefill_kernel<false, false>, GP_SMEM);
+    DynSmemAttr::set(gla_prefill_kernel<true, true>, GP_SMEM);
+    DynSmemAttr::set(gla_prefill_kernel<false, true>, GP_SMEM);
+    attr.mark();
   }
   auto launch = [&](int pass, int segs) {
     p.pass = pass;

@@ -46,6 +46,9 @@ struct SwaDecodeParams {
   const __nv_bfloat16 *new_k, *new_v;
   __nv_bfloat16 *k_cache, *v_cache;
   int64_t nk_sb, nk_sh, nv_sb, nv_sh, kc_sblk, kc_stok, kc_sh, vc_sblk, vc_stok, vc_sh;
+  // slot of each request's new token (reshape_and_cache_flash convention: < 0 = padded row, no
+  // store); null = the page of position L-1 taken from the block table
+  const int64_t* new_slots;
   // fused combine: one ticket per (request, kv-head group); null = separate combine kernel
   int* tickets;
 };
@@ -264,10 +267,19 @@ swa_decode_split_kernel(const SwaDecodeParams p, const __grid_constant__ CUtenso
     const __nv_bfloat16* src = lane < 16 ? p.new_k + b * p.nk_sb + (int64_t)hkv * p.nk_sh
                                          : p.new_v + b * p.nv_sb + (int64_t)hkv * p.nv_sh;
     new_x = ldg_nc_v4(src + (lane & 15) * 8);
-    if (hg == 0) {
+    int64_t blk;
+    int off;
+    bool store = hg == 0;
+    if (p.new_slots) {
+      const int64_t slot = p.new_slots[b];
+      store = store && slot >= 0;
+      blk = slot / p.block_size; off = (int)(slot % p.block_size);
+    } else {
       const int pos = L - 1;
-      const int64_t blk = p.block_tables[(int64_t)b * p.bt_stride + pos / p.block_size];
-      const int off = pos % p.block_size;
+      blk = p.block_tables[(int64_t)b * p.bt_stride + pos / p.block_size];
+      off = pos % p.block_size;
+    }
+    if (store) {
       __nv_bfloat16* dst = lane < 16 ? p.k_cache + blk * p.kc_sblk + off * p.kc_stok + (int64_t)hkv * p.kc_sh
                                      : p.v_cache + blk * p.vc_sblk + off * p.vc_stok + (int64_t)hkv * p.vc_sh;
       stg_v4(dst + (lane & 15) * 8, new_x);
@@ -479,7 +491,7 @@ extern "C" int hymeta_swa_meta_decode_paged_fused(
     int64_t o_sb, int64_t o_sh, int64_t kc_sblk, int64_t kc_stok, int64_t kc_sh, int64_t vc_sblk,
     int64_t vc_stok, int64_t vc_sh, int64_t mk_st, int64_t mk_sh, int64_t mv_st, int64_t mv_sh,
     const void* new_k, const void* new_v, int64_t nk_sb, int64_t nk_sh, int64_t nv_sb, int64_t nv_sh,
-    int32_t* tickets, void* stream) {
+    const int64_t* new_slot_mapping, int32_t* tickets, void* stream) {
   if (B == 0) return HYMETA_OK;
   if (!q || !k_cache || !v_cache || !block_tables || !cache_seqlens || !out || !workspace || B < 0 ||
       H <= 0 || Hkv <= 0 || M < 0 || block_size <= 0 || max_blocks < 0 || num_blocks <= 0)
@@ -515,6 +527,7 @@ extern "C" int hymeta_swa_meta_decode_paged_fused(
   p.kc_sblk = kc_sblk; p.kc_stok = kc_stok; p.kc_sh = kc_sh;
   p.vc_sblk = vc_sblk; p.vc_stok = vc_stok; p.vc_sh = vc_sh;
   p.tickets = tickets;
+  p.new_slots = new_k ? new_slot_mapping : nullptr;
 
   // tensor maps: [D, Hkv, block_size, num_blocks] over the paged caches, [D, Hkv, M, 1] over meta
   CUtensorMap tmK, tmV, tmMK, tmMV;
@@ -536,13 +549,11 @@ extern "C" int hymeta_swa_meta_decode_paged_fused(
     tmMK = tmK; tmMV = tmV;
   }
 
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaFuncSetAttribute(swa_decode_split_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                         SWA_DEC_SMEM);
-    cudaFuncSetAttribute(swa_decode_combine_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                         16 * 1025 * (int)sizeof(float));
-    attr_set = true;
+  static DynSmemAttr attr;
+  if (attr.need()) {
+    DynSmemAttr::set(swa_decode_split_kernel, SWA_DEC_SMEM);
+    DynSmemAttr::set(swa_decode_combine_kernel, 16 * 1025 * (int)sizeof(float));
+    attr.mark();
   }
   cudaStream_t st = (cudaStream_t)stream;
   dim3 grid(pl.n_splits, Hkv * pl.n_hgroups, B);
@@ -571,5 +582,5 @@ extern "C" int hymeta_swa_meta_decode_paged(
       q, const_cast<void*>(k_cache), const_cast<void*>(v_cache), block_tables, cache_seqlens, meta_k,
       meta_v, out, workspace, workspace_bytes, B, H, Hkv, D, M, block_size, num_blocks, max_blocks,
       bt_stride, window_left, scale, q_sb, q_sh, o_sb, o_sh, kc_sblk, kc_stok, kc_sh, vc_sblk, vc_stok,
-      vc_sh, mk_st, mk_sh, mv_st, mv_sh, nullptr, nullptr, 0, 0, 0, 0, nullptr, stream);
+      vc_sh, mk_st, mk_sh, mv_st, mv_sh, nullptr, nullptr, 0, 0, 0, 0, nullptr, nullptr, stream);
 }

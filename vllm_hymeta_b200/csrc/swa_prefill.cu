@@ -44,6 +44,11 @@ struct SwaPrefillParams {
   int N, H, Hkv, M, window_left, has_q2, n_qpairs;
   float scale_log2;
   int64_t o_st, o_sh;
+  // paged keys (prefix-cache / chunked prefill / multi-token decode): logical key position p of
+  // request n lives in page block_tables[n][p / block_size], row p % block_size
+  const int32_t* block_tables;
+  int64_t bt_stride;
+  int paged, block_size, box_rows;
 };
 
 struct QTile { int on, rows, pmin, pmax, lo, hi; };   // real key-tile range [lo, hi] (empty if hi < lo)
@@ -94,6 +99,9 @@ swa_prefill_kernel(const SwaPrefillParams p, const __grid_constant__ CUtensorMap
     else { u_lo = min(u_lo, qt[1].lo); u_hi = max(u_hi, qt[1].hi); }
   }
   const int n_steps = nm + (u_hi >= u_lo ? u_hi - u_lo + 1 : 0);
+  // lowest key position any query of this CTA can see (rows below it / at or past Lk are masked for
+  // every query: in the paged form they may hold recycled-page bytes and are cleared before PV)
+  const int lo_all = p.window_left < 0 ? 0 : max(0, qt[0].pmin - p.window_left);
   int last_step[2];   // last key step each query tile takes part in (-1: none)
 #pragma unroll
   for (int i = 0; i < 2; ++i)
@@ -139,26 +147,40 @@ swa_prefill_kernel(const SwaPrefillParams p, const __grid_constant__ CUtensorMap
         tma_load_3d(sQ + i * PF_TILE, tq, bar_q, 0, h, row);
         tma_load_3d(sQ + i * PF_TILE + 16384, tq, bar_q, 64, h, row);
       }
+      const int32_t* bt = p.paged ? p.block_tables + (int64_t)n * p.bt_stride : nullptr;
+      // one K or V tile: a 3-D box of the packed tensor / meta rows, or -- paged -- box_rows-row
+      // boxes of the 4-D cache map, each resolved through the block table (a box never straddles a
+      // page: box_rows divides block_size and logical positions are box aligned)
+      auto load_tile = [&](uint32_t dst, uint32_t bar, const CUtensorMap* m3, const CUtensorMap* m4, int t) {
+        mbar_expect_tx(bar, PF_TILE);
+        if (t < nm || !p.paged) {
+          const int row = t < nm ? t * PF_BN : k_row0 + (u_lo + t - nm) * PF_BN;
+          tma_load_3d(dst, m3, bar, 0, hkv, row);
+          tma_load_3d(dst + 16384, m3, bar, 64, hkv, row);
+        } else {
+          const int pos0 = (u_lo + t - nm) * PF_BN, rb = p.box_rows;
+          for (int sub = 0; sub < PF_BN / rb; ++sub) {
+            // boxes wholly outside [lo_all, Lk) are redirected to the nearest box that holds a
+            // visible position (their rows are masked and their V rows cleared by the softmax warps)
+            const int pos = min(max(pos0 + sub * rb, lo_all / rb * rb), Lk - 1);
+            const int blk = bt[pos / p.block_size];
+            const int row = (pos % p.block_size) / rb * rb;
+            const uint32_t o = sub * rb * 128;
+            tma_load_4d(dst + o, m4, bar, 0, hkv, row, blk);
+            tma_load_4d(dst + 16384 + o, m4, bar, 64, hkv, row, blk);
+          }
+        }
+      };
       for (int t = 0; t < n_steps; ++t) {
-        const CUtensorMap *mk, *mv;
-        int row;
-        if (t < nm) { mk = &tmMK; mv = &tmMV; row = t * PF_BN; }
-        else { mk = &tmK; mv = &tmV; row = k_row0 + (u_lo + t - nm) * PF_BN; }
         {
           const int st = t % PF_NKS;
           if (t >= PF_NKS) mbar_wait(bar_ke + 8 * st, ((t / PF_NKS) - 1) & 1);
-          const uint32_t bar = bar_kf + 8 * st, dst = sK + st * PF_TILE;
-          mbar_expect_tx(bar, PF_TILE);
-          tma_load_3d(dst, mk, bar, 0, hkv, row);
-          tma_load_3d(dst + 16384, mk, bar, 64, hkv, row);
+          load_tile(sK + st * PF_TILE, bar_kf + 8 * st, t < nm ? &tmMK : &tmK, &tmK, t);
         }
         {
           const int st = t % PF_NVS;
           if (t >= PF_NVS) mbar_wait(bar_ve + 8 * st, ((t / PF_NVS) - 1) & 1);
-          const uint32_t bar = bar_vf + 8 * st, dst = sV + st * PF_TILE;
-          mbar_expect_tx(bar, PF_TILE);
-          tma_load_3d(dst, mv, bar, 0, hkv, row);
-          tma_load_3d(dst + 16384, mv, bar, 64, hkv, row);
+          load_tile(sV + st * PF_TILE, bar_vf + 8 * st, t < nm ? &tmMV : &tmV, &tmV, t);
         }
       }
     }
@@ -297,6 +319,23 @@ swa_prefill_kernel(const SwaPrefillParams p, const __grid_constant__ CUtensorMap
           tmem_st16(tS + 16 * c, w);
         }
         l_run += (rs0 + rs1) + (rs2 + rs3);
+        if (p.paged && t >= nm && (kp0 + PF_BN > Lk || kp0 < lo_all)) {
+          // paged boundary tile: key rows outside [lo_all, Lk) are masked for every query (P = 0)
+          // but may hold recycled-page bytes (NaN patterns), and 0 * NaN would poison O -- clear
+          // those V rows in the landed stage before PV is issued (generic -> async proxy fence)
+          const int st = t % PF_NVS;
+          mbar_wait(bar_vf + 8 * st, (t / PF_NVS) & 1);
+          const int kp = kp0 + r;
+          if (kp >= Lk || kp < lo_all) {
+            uint8_t* row = smem + PF_SV + st * PF_TILE + r * 128;
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+              *reinterpret_cast<uint4*>(row + c * 16) = make_uint4(0, 0, 0, 0);
+              *reinterpret_cast<uint4*>(row + 16384 + c * 16) = make_uint4(0, 0, 0, 0);
+            }
+          }
+          fence_proxy_async_smem();
+        }
         tmem_wait_st();
         tc_fence_before();
         mbar_arrive(bar_p + 8 * i);
@@ -346,10 +385,11 @@ extern "C" int hymeta_swa_meta_prefill_varlen(
     int64_t k_st, int64_t k_sh, int64_t v_st, int64_t v_sh, int64_t q2_st, int64_t q2_sh,
     int64_t mk_st, int64_t mk_sh, int64_t mv_st, int64_t mv_sh, int64_t o_st, int64_t o_sh,
     int64_t kc_sblk, int64_t vc_sblk, void* stream) {
-  (void)bt_stride; (void)block_size; (void)kc_sblk; (void)vc_sblk;
   if (N < 0 || Tq < 0 || Tk < 0 || H <= 0 || Hkv <= 0 || M < 0 || !out) return HYMETA_ERR_INVALID_ARG;
   if (D != kD || H % Hkv) return HYMETA_ERR_UNSUPPORTED;
-  if (block_tables) return HYMETA_ERR_UNSUPPORTED;   // paged-prefix prefill: see DESIGN.md (next)
+  const bool paged = block_tables != nullptr;
+  if (paged && (block_size < 16 || block_size % 16 || Tk <= 0 || Tk % block_size || bt_stride < 0))
+    return block_size > 0 && block_size % 16 ? HYMETA_ERR_UNSUPPORTED : HYMETA_ERR_INVALID_ARG;
   if (M > 0 && (!meta_k || !meta_v)) return HYMETA_ERR_INVALID_ARG;
   if (q2 && M == 0) return HYMETA_ERR_INVALID_ARG;
   const bool real = N > 0 && Tq > 0;
@@ -366,11 +406,25 @@ extern "C" int hymeta_swa_meta_prefill_varlen(
     const uint32_t box[3] = {64, 1, box_rows};
     return make_tmap_bf16(tm, base, 3, dims, strides, box, true);
   };
+  // paged: [D, Hkv, block_size, num_blocks] over the caches, boxes of box_rows key rows
+  const int box_rows = !paged ? PF_BN : block_size % 128 == 0 ? 128 : block_size % 64 == 0 ? 64
+                                        : block_size % 32 == 0 ? 32 : 16;
+  auto mk4 = [&](CUtensorMap* tm, const void* base, int64_t s_h, int64_t s_tok, int64_t s_blk) {
+    const uint64_t dims[4] = {(uint64_t)kD, (uint64_t)Hkv, (uint64_t)block_size, (uint64_t)(Tk / block_size)};
+    const int64_t str[4] = {1, s_h, s_tok, s_blk};
+    const uint32_t box[4] = {64, 1, (uint32_t)box_rows, 1};
+    return make_tmap_bf16(tm, base, 4, dims, str, box, true);
+  };
   int rc = HYMETA_OK;
   if (real) {
     if ((rc = mk3(&tmQ, q1, H, Tq, q_st, q_sh, PF_BM))) return rc;
-    if ((rc = mk3(&tmK, k1, Hkv, Tk, k_st, k_sh, PF_BN))) return rc;
-    if ((rc = mk3(&tmV, v1, Hkv, Tk, v_st, v_sh, PF_BN))) return rc;
+    if (paged) {
+      if ((rc = mk4(&tmK, k1, k_sh, k_st, kc_sblk))) return rc;
+      if ((rc = mk4(&tmV, v1, v_sh, v_st, vc_sblk))) return rc;
+    } else {
+      if ((rc = mk3(&tmK, k1, Hkv, Tk, k_st, k_sh, PF_BN))) return rc;
+      if ((rc = mk3(&tmV, v1, Hkv, Tk, v_st, v_sh, PF_BN))) return rc;
+    }
   }
   if (M > 0) {
     if ((rc = mk3(&tmMK, meta_k, Hkv, M, mk_st, mk_sh, PF_BN))) return rc;
@@ -379,7 +433,7 @@ extern "C" int hymeta_swa_meta_prefill_varlen(
   }
   if (!real) { tmQ = tmQ2; tmK = tmMK; tmV = tmMV; }   // never dereferenced, but must be valid maps
   if (!q2) tmQ2 = tmQ;
-  if (M == 0) { tmMK = tmK; tmMV = tmV; }
+  if (M == 0) { tmMK = tmQ; tmMV = tmQ; }               // never dereferenced (no meta tiles)
 
   SwaPrefillParams p;
   p.cu_q = cu_q; p.cu_k = cu_k; p.out = (__nv_bfloat16*)out;
@@ -391,12 +445,11 @@ extern "C" int hymeta_swa_meta_prefill_varlen(
   p.n_qpairs = (msq + 2 * PF_BM - 1) / (2 * PF_BM);
   p.scale_log2 = scale * 1.4426950408889634f;
   p.o_st = o_st; p.o_sh = o_sh;
+  p.block_tables = block_tables; p.bt_stride = bt_stride;
+  p.paged = paged && real ? 1 : 0; p.block_size = paged ? block_size : 1; p.box_rows = box_rows;
 
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaFuncSetAttribute(swa_prefill_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PF_SMEM);
-    attr_set = true;
-  }
+  static DynSmemAttr attr;
+  attr.ensure(swa_prefill_kernel, PF_SMEM);
   dim3 grid(H, p.n_qpairs, p.N + (q2 ? 1 : 0));
   swa_prefill_kernel<<<grid, PF_THREADS, PF_SMEM, (cudaStream_t)stream>>>(p, tmQ, tmK, tmV, tmQ2, tmMK, tmMV);
   count_launch();

@@ -63,7 +63,15 @@ class GatedLinearAttention:
             n_tok = attn_metadata.num_prefill_tokens
             cu = attn_metadata.query_start_loc[:num_prefills + 1].to(torch.int32)
             slots = state_indices_tensor[:num_prefills].to(torch.int32)
-            mode = torch.full((num_prefills,), ops.INIT_SLOT, dtype=torch.int32, device=q.device)
+            # context_len == 0: a new (or recompute-preempted) request starts from a ZERO state
+            # whatever its possibly recycled slot holds -- the reference zeroes those slots in
+            # GLAswaModel._clear_prefill_cache (modeling_gla_swa.py:391-414, called at :450); here
+            # the choice is made on device per request, no host sync and no separate zero-fill
+            ctx = getattr(attn_metadata, "context_lens_tensor", None)
+            if ctx is not None:
+                mode = torch.where(ctx[:num_prefills] == 0, ops.INIT_ZERO, ops.INIT_SLOT).to(torch.int32)
+            else:
+                mode = torch.full((num_prefills,), ops.INIT_SLOT, dtype=torch.int32, device=q.device)
             ops.gla_prefill_varlen(q[:n_tok], k[:n_tok], v[:n_tok], gk[:n_tok], kv_cache, cu, slots,
                                    mode, max_seqlen=getattr(attn_metadata, "max_query_len", None) or n_tok,
                                    out=out[:n_tok], gnorm_weight=self._gnorm_w(q.device),

@@ -35,21 +35,19 @@ class GLACacheManager(NativeSlotAllocator):
         return self._gla_cache
 
     def _copy_cache(self, from_index: int, to_index: int):
-        if self._gla_cache.is_cuda:
-            from .. import ops
-            ops.state_copy_slot(self._gla_cache, from_index, to_index)
-        else:
-            self._gla_cache[:, to_index].copy_(self._gla_cache[:, from_index])
+        from .. import ops
+        ops.state_copy_slot(self._gla_cache, from_index, to_index)
 
     def clear_slots(self, slots: List[int]) -> None:
+        """Zero slots explicitly (the prefill kernel already starts context-0 requests from a zero
+        state on device -- ``GatedLinearAttention._prefill_and_mix_infer`` -- so the model's forward
+        does not need this; kept for callers that want reference ``_clear_prefill_cache``
+        semantics on the tensor itself, modeling_gla_swa.py:391-414)."""
         if not slots:
             return
-        if self._gla_cache.is_cuda:
-            from .. import ops
-            ops.state_zero_slots(self._gla_cache, torch.tensor(slots, dtype=torch.int32,
-                                                               device=self._gla_cache.device))
-        else:
-            self._gla_cache[:, torch.tensor(slots, dtype=torch.long)] = 0
+        from .. import ops
+        ops.state_zero_slots(self._gla_cache, torch.tensor(slots, dtype=torch.int32,
+                                                           device=self._gla_cache.device))
 
     def current_run_tensors(self, **kwargs):
         if "seqlen_agnostic_capture_inputs" not in kwargs:

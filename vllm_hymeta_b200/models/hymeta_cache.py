@@ -55,24 +55,17 @@ class HymetaCacheManager(NativeSlotAllocator):
 
     def _copy_cache(self, from_index: int, to_index: int):
         """Fork a request's state into another slot (all layers, one launch)."""
-        state = self._hymeta_cache[0]
-        if state.is_cuda:
-            from .. import ops
-            ops.state_copy_slot(state, from_index, to_index)
-        else:                                      # host-logic tests
-            state[:, to_index].copy_(state[:, from_index])
+        from .. import ops
+        ops.state_copy_slot(self._hymeta_cache[0], from_index, to_index)
 
     def clear_slots(self, slots: List[int]) -> None:
         """Zero the states of newly admitted requests (reference ``_clear_prefill_cache``,
         modeling_hymeta.py:1202-1227) with one launch over all layers."""
         if not slots:
             return
+        from .. import ops
         state = self._hymeta_cache[0]
-        if state.is_cuda:
-            from .. import ops
-            ops.state_zero_slots(state, torch.tensor(slots, dtype=torch.int32, device=state.device))
-        else:
-            state[:, torch.tensor(slots, dtype=torch.long)] = 0
+        ops.state_zero_slots(state, torch.tensor(slots, dtype=torch.int32, device=state.device))
 
     def current_run_tensors(self, **kwargs):
         """-> (state, meta_linear, meta_fattn, state_indices[B] int32).  Outside CUDA graphs the

@@ -382,11 +382,15 @@ def swa_meta_decode_paged(q, k_cache, v_cache, block_tables, cache_seqlens, meta
                           window_left: int, scale: Optional[float] = None,
                           out: Optional[torch.Tensor] = None,
                           new_k: Optional[torch.Tensor] = None, new_v: Optional[torch.Tensor] = None,
-                          fused_combine: bool = False) -> torch.Tensor:
+                          fused_combine: bool = False,
+                          new_slot_mapping: Optional[torch.Tensor] = None) -> torch.Tensor:
     """q [B,H,D]; caches [nb,bs,Hkv,D]; block_tables [B,max_blocks] int32; cache_seqlens [B]
     int32; meta_k/meta_v [M,Hkv,D] or None.  Returns out [B,H,D].
     new_k/new_v [B,Hkv,D]: K/V of the token at position cache_seqlens[b]-1; the kernel writes them to
     their page (reshape_and_cache_flash folded in) and attends to them -- no separate kv_write_paged.
+    new_slot_mapping [B] int64: destination slots of the new tokens (< 0 = padded row, not stored);
+    without it the page of position cache_seqlens[b]-1 is taken from the block table and padded
+    rows MUST carry cache_seqlens = 0.
     fused_combine: the split-K partials are merged by the last split CTA to finish instead of a
     second launch (bit-identical; measured no faster on B200, so off by default).  With a single
     split per (request, kv-head) -- the plan whenever the batch fills the GPU -- the split kernel
@@ -408,6 +412,12 @@ def swa_meta_decode_paged(q, k_cache, v_cache, block_tables, cache_seqlens, meta
         _req(new_v, "new_v", torch.bfloat16)
         if new_k.shape != (B, Hkv, D) or new_v.shape != (B, Hkv, D):
             raise ValueError("new_k/new_v must be [B, Hkv, D]")
+        if new_slot_mapping is not None:
+            _req(new_slot_mapping, "new_slot_mapping", torch.int64)
+            if new_slot_mapping.numel() < B:
+                raise ValueError("new_slot_mapping shorter than the batch")
+    elif new_slot_mapping is not None:
+        raise ValueError("new_slot_mapping needs new_k/new_v")
     if out is None:
         out = torch.empty(B, H, D, dtype=q.dtype, device=q.device)
     if scale is None:
@@ -430,7 +440,7 @@ def swa_meta_decode_paged(q, k_cache, v_cache, block_tables, cache_seqlens, meta
         _ptr(new_k), _ptr(new_v),
         new_k.stride(0) if new_k is not None else 0, new_k.stride(1) if new_k is not None else 0,
         new_v.stride(0) if new_v is not None else 0, new_v.stride(1) if new_v is not None else 0,
-        _ptr(tickets), _stream()),
+        _ptr(new_slot_mapping), _ptr(tickets), _stream()),
         "hymeta_swa_meta_decode_paged_fused")
     return out
 
@@ -466,7 +476,11 @@ def swa_meta_prefill_varlen(q1, k1, v1, q2, meta_k, meta_v, cu_seqlens_q, cu_seq
         scale = D ** -0.5
     if paged:
         _req(block_tables, "block_tables", torch.int32)
-        Tk, bs = 0, k1.shape[1]
+        if k1.dim() != 4 or v1.shape != k1.shape:
+            raise ValueError("paged prefill: k1/v1 must be the [num_blocks, block_size, Hkv, D] caches")
+        if block_tables.dim() != 2 or block_tables.shape[0] < cu_seqlens_q.numel() - 1:
+            raise ValueError("block_tables must be [num_seqs, max_blocks]")
+        Tk, bs = k1.shape[0] * k1.shape[1], k1.shape[1]     # rows of the cache = num_blocks * block_size
         k_st, k_sh, v_st, v_sh = k1.stride(1), k1.stride(2), v1.stride(1), v1.stride(2)
         kc_sblk, vc_sblk, bt_stride = k1.stride(0), v1.stride(0), block_tables.stride(0)
     else:
