@@ -518,3 +518,114 @@ def test_branch_norm_merge_edge_cases(ops):
     got = ops.branch_norm_merge(xa.to(DEV), xl.to(DEV), w1.to(DEV), w2.to(DEV), 1e-5)
     torch.cuda.synchronize()
     _assert_ulp_close(got, ref, "branch merge, wide rows", floor=1.0)
+
+
+# ------------------------------------------------------------------------------------- b (boundary)
+def test_platform_binds_to_vllm_nvml_platform():
+    """On a GPU host the platform class derives from the installed vLLM's NVML CUDA platform
+    (reference platform.py:7-10) and answers the V1 selection protocol."""
+    pytest.importorskip("vllm")
+    from types import SimpleNamespace
+    from vllm_hymeta_b200.platform import HymetaCudaPlatform as P
+    assert P.__mro__[1].__name__ == "NvmlCudaPlatform"
+    cfg = SimpleNamespace(use_mla=False, head_size=128)
+    assert P.get_attn_backend_cls(None, cfg, 28).endswith("meta_attention_v1.MetaAttentionV1Backend")
+
+
+def test_custom_op_path_equals_direct_call(ops):
+    """``torch.ops.vllm.unified_meta_attention_with_output`` (reference models/attention.py:361-387)
+    through the forward context == the direct ``impl.forward`` call, bit for bit."""
+    from vllm_hymeta_b200.attention.meta_attention import MetaAttentionMetadataBuilder, SeqData
+    from vllm_hymeta_b200.models import attention as A
+    H, Hkv, M, bs, W = 14, 2, 128, 16, 64
+    lens = [90, 33]
+    gen = torch.Generator().manual_seed(51)
+    nb = 20
+    perm = torch.randperm(nb, generator=gen).tolist()
+    tables = [perm[:7], perm[7:11]]
+    T = sum(lens)
+    q = torch.randn(T, H * D, generator=gen).bfloat16().to(DEV)
+    k = torch.randn(T, Hkv * D, generator=gen).bfloat16().to(DEV)
+    v = torch.randn(T, Hkv * D, generator=gen).bfloat16().to(DEV)
+    k2 = torch.randn(M, Hkv, D, generator=gen).bfloat16().to(DEV)
+    v2 = torch.randn(M, Hkv, D, generator=gen).bfloat16().to(DEV)
+    outs = []
+    for direct in (True, False):
+        name = f"parity.layers.{int(direct)}.attn"
+        layer = A.MetaAttention(H, D, D ** -0.5, Hkv, per_layer_sliding_window=W, num_meta_tokens=M,
+                                prefix=name, use_direct_call=direct)
+        layer.bind_kv_cache(torch.zeros(2, nb, bs, Hkv, D, dtype=torch.bfloat16, device=DEV))
+        b = MetaAttentionMetadataBuilder(block_size=bs, sliding_window=None, device=DEV)
+        for L, bt in zip(lens, tables):
+            b.add(SeqData(True, L, L, 0, bt))
+        md = b.build()
+        with A.set_forward_context(md):
+            outs.append(layer.forward(q, k, v, key2=k2, value2=v2).clone())
+        del A._LAYERS[name]
+    torch.cuda.synchronize()
+    assert torch.isfinite(outs[0].float()).all() and torch.equal(outs[0], outs[1])
+
+
+# ------------------------------------------------------------------------------------- f4 (V1 adapter)
+def test_v1_adapter_mixed_batch_vs_oracle(ops):
+    """``MetaAttentionV1Impl`` driven the way the installed vLLM's V1 runner drives a backend:
+    ``do_kv_cache_update`` then ``forward`` on a reordered [decodes | prefills / extends] batch with
+    a padded query tensor, against the oracle over the paged cache; with and without meta K/V."""
+    from vllm_hymeta_b200.attention.meta_attention_v1 import (MetaAttentionV1Backend,
+                                                              MetaAttentionV1Impl,
+                                                              MetaAttentionV1MetadataBuilder)
+    H, Hkv, bs, W, M = 14, 2, 16, 64, 128
+    # request: (context, new tokens); two decodes first, then an extend (prefix hit) and a new prompt
+    reqs = [(40, 1), (300, 1), (150, 70), (0, 33)]
+    gen = torch.Generator().manual_seed(61)
+    nblk = [(c + n + bs - 1) // bs for c, n in reqs]
+    nb = sum(nblk) + 3
+    perm = torch.randperm(nb, generator=gen).tolist()
+    kv = torch.full(MetaAttentionV1Backend.get_kv_cache_shape(nb, bs, Hkv, D), float("nan"),
+                    dtype=torch.bfloat16)
+    bt = torch.zeros(len(reqs), max(nblk), dtype=torch.int32)
+    at = 0
+    for i, (c, n) in enumerate(reqs):
+        row = perm[at:at + nblk[i]]
+        at += nblk[i]
+        bt[i, :nblk[i]] = torch.tensor(row, dtype=torch.int32)
+        for p in range(c):                      # the cached context
+            kv[0, row[p // bs], p % bs] = torch.randn(Hkv, D, generator=gen).bfloat16()
+            kv[1, row[p // bs], p % bs] = torch.randn(Hkv, D, generator=gen).bfloat16()
+    T = sum(n for _, n in reqs)
+    qsl = torch.tensor([0] + torch.tensor([n for _, n in reqs]).cumsum(0).tolist(), dtype=torch.int32)
+    seq = torch.tensor([c + n for c, n in reqs], dtype=torch.int32)
+    slots = torch.tensor([int(bt[i, p // bs]) * bs + p % bs for i, (c, n) in enumerate(reqs)
+                          for p in range(c, c + n)], dtype=torch.int64)
+    pad = 3                                     # CUDA-graph style padding of the token tensors
+    q = torch.randn(T + pad, H * D, generator=gen).bfloat16()
+    k = torch.randn(T + pad, Hkv * D, generator=gen).bfloat16()
+    v = torch.randn(T + pad, Hkv * D, generator=gen).bfloat16()
+    k2 = torch.randn(M, Hkv, D, generator=gen).bfloat16()
+    v2 = torch.randn(M, Hkv, D, generator=gen).bfloat16()
+    cm = SimpleNamespace(query_start_loc=qsl.to(DEV), query_start_loc_cpu=qsl, seq_lens=seq.to(DEV),
+                         num_reqs=len(reqs), num_actual_tokens=T, max_query_len=70, max_seq_len=301,
+                         block_table_tensor=bt.to(DEV), slot_mapping=slots.to(DEV), causal=True)
+    md = MetaAttentionV1MetadataBuilder(SimpleNamespace(block_size=bs), ["l"], None, DEV).build(0, cm)
+    ref_kv = kv.clone()
+    oswa.kv_write_paged(k[:T].view(T, Hkv, D), v[:T].view(T, Hkv, D), ref_kv[0], ref_kv[1], slots.tolist())
+    impl = MetaAttentionV1Impl(H, D, D ** -0.5, Hkv, None, W, "auto")
+    for with_meta in (True, False):
+        layer = SimpleNamespace(meta_key=k2.to(DEV) if with_meta else None,
+                                meta_value=v2.to(DEV) if with_meta else None)
+        d_kv = kv.to(DEV)
+        out = torch.full((T + pad, H * D), 9.0, dtype=torch.bfloat16, device=DEV)
+        impl.do_kv_cache_update(layer, k.to(DEV), v.to(DEV), d_kv, md.slot_mapping)
+        impl.forward(layer, q.to(DEV).view(-1, H, D), k.to(DEV), v.to(DEV), d_kv, md, output=out.view(-1, H, D))
+        torch.cuda.synchronize()
+        assert torch.equal(torch.nan_to_num(d_kv.cpu().float(), nan=7.0),
+                           torch.nan_to_num(ref_kv.float(), nan=7.0))
+        mk, mv = (k2, v2) if with_meta else (None, None)
+        q3 = q.view(-1, H, D)
+        ref_d = oswa.swa_meta_decode_paged(q3[:2], ref_kv[0], ref_kv[1], bt[:2].tolist(), seq[:2].tolist(),
+                                           mk, mv, W - 1, out_dtype=torch.float32)
+        ref_p = oswa.swa_meta_prefill_paged(q3[2:T], ref_kv[0], ref_kv[1], bt[2:].tolist(), [0, 70, 103],
+                                            seq[2:].tolist(), mk, mv, W - 1, out_dtype=torch.float32)
+        assert_close(out[:T].view(T, H, D), torch.cat([ref_d, ref_p]), f"V1 adapter (meta={with_meta})")
+        assert (out[T:] == 9.0).all(), "padded rows must not be written"
+    assert impl.forward(layer, q.to(DEV), None, None, d_kv, None, output=out).abs().max().item() == 0

@@ -241,3 +241,123 @@ def test_native_slot_manager_batch_outputs_and_errors():
     assert sorted(a.free_cache_indices) == [0, 1, 2] and a.live() == []
     assert a.prepare_batch({}, []) == ([], [], [])
     assert a.prepare_batch({"x": [1]}, ["x"])[0] == [PAD_SLOT_ID]
+
+
+# ------------------------------------------------------------------------------------- b (packaging)
+def test_vllm_plugin_loader_discovers_the_package(tmp_path):
+    """pyproject.toml declares the reference's two entry-point groups (setup.py:69-76).  The package
+    is pip-installed from the source tree into a scratch directory and the INSTALLED vLLM's own
+    plugin loader (vllm/plugins/__init__.py) must find and load both entry points."""
+    import os
+    import subprocess
+    import sys
+    pytest.importorskip("vllm")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    target = tmp_path / "site"
+    r = subprocess.run([sys.executable, "-m", "pip", "install", "--no-index", "--no-build-isolation",
+                        "--no-deps", "--quiet", "--target", str(target), root],
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout[-1500:] + r.stderr[-1500:]
+    code = (
+        "from vllm.plugins import load_plugins_by_group\n"
+        "p = load_plugins_by_group('vllm.platform_plugins')\n"
+        "g = load_plugins_by_group('vllm.general_plugins')\n"
+        "assert p['hymeta_b200']() == 'vllm_hymeta_b200.platform.HymetaCudaPlatform', p\n"
+        "g['hymeta_b200_model']()\n"
+        "from vllm.v1.attention.backends.registry import AttentionBackendEnum as E\n"
+        "print('BACKEND', E.CUSTOM.get_path())\n"
+        "import vllm_hymeta_b200.platform as pl\n"
+        "print('PLATFORM', pl.HymetaCudaPlatform.__mro__[1].__name__)\n")
+    env = dict(os.environ, PYTHONPATH=str(target), VLLM_LOGGING_LEVEL="ERROR")
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, env=env,
+                       cwd=str(tmp_path))
+    assert r.returncode == 0, r.stdout[-1500:] + r.stderr[-3000:]
+    assert "BACKEND vllm_hymeta_b200.attention.meta_attention_v1.MetaAttentionV1Backend" in r.stdout
+    # binds to vLLM's NVML platform (reference platform.py:7) where vllm.platforms.cuda imports -- it
+    # needs libcuda, so on a GPU-less host the class is a plain object (checked on the GPU box by
+    # tests/test_gpu_modules.py::test_platform_binds_to_vllm_nvml_platform)
+    assert "PLATFORM NvmlCudaPlatform" in r.stdout or "PLATFORM object" in r.stdout
+
+
+def test_platform_selection_rules():
+    from types import SimpleNamespace
+    from vllm_hymeta_b200.platform import HymetaCudaPlatform as P
+    # V0 protocol (reference platform.py:20-30)
+    assert P.get_attn_backend_cls(None, 128, torch.bfloat16, "auto", 256, False, False).endswith(
+        "meta_attention.MetaAttentionBackend")
+    assert P.get_attn_backend_cls("XFORMERS", 128, torch.bfloat16, "auto", 256, False, False).endswith(
+        "flash_attn.FlashAttentionBackend")
+    # V1 protocol of the installed vLLM: (selected_backend, attn_selector_config, num_heads)
+    cfg = SimpleNamespace(use_mla=False, head_size=128)
+    assert P.get_attn_backend_cls(None, cfg, 28).endswith("meta_attention_v1.MetaAttentionV1Backend")
+
+
+def test_unified_meta_attention_custom_ops_route_through_forward_context():
+    """``torch.ops.vllm.unified_meta_attention_with_output`` (reference models/attention.py:361-409):
+    looks the layer up by name in the forward context and calls ``impl.forward`` with the context's
+    metadata, the layer's kv cache and the query2/key2/value2 tensors; the fakes accept the same
+    arguments."""
+    from vllm_hymeta_b200.models import attention as A
+    layer = A.MetaAttention(4, 128, 128 ** -0.5, 2, per_layer_sliding_window=64, num_meta_tokens=8,
+                            prefix="test.layers.0.attn", use_direct_call=False)
+    with pytest.raises(ValueError, match="Duplicate layer name"):
+        A.MetaAttention(4, 128, 128 ** -0.5, 2, prefix="test.layers.0.attn")
+    seen = {}
+
+    def fake_forward(lyr, q, k, v, q2, k2, v2, kv_cache, md, output=None):
+        seen.update(layer=lyr, md=md, kv=kv_cache, shapes=(q.shape, k.shape, q2.shape, k2.shape))
+        output.fill_(3.0)
+
+    layer.impl.forward = fake_forward
+    layer.bind_kv_cache([torch.zeros(1), torch.ones(1)])         # one cache per virtual engine (:170-176)
+    T, M = 5, 8
+    q, k, v = torch.zeros(T, 4 * 128), torch.zeros(T, 2 * 128), torch.zeros(T, 2 * 128)
+    q2, k2, v2 = torch.zeros(M, 4 * 128), torch.zeros(M, 2, 128), torch.zeros(M, 2, 128)
+    with A.set_forward_context("MD", virtual_engine=1):
+        out = layer.forward(q, k, v, query2=q2, key2=k2, value2=v2)
+    assert out.shape == (T + M, 4 * 128) and out.min() == 3.0
+    assert seen["layer"] is layer and seen["md"] == "MD" and seen["kv"].item() == 1.0
+    assert seen["shapes"] == ((T, 4, 128), (T, 2, 128), (M, 4, 128), (M, 2, 128))
+    # fake (meta-device) evaluation with the meta-token arguments present
+    mq, mk = torch.empty(T, 4, 128, device="meta"), torch.empty(T, 2, 128, device="meta")
+    mq2, mk2 = torch.empty(M, 4, 128, device="meta"), torch.empty(M, 2, 128, device="meta")
+    o = torch.ops.vllm.unified_meta_attention(mq, mk, mk, "test.layers.0.attn", mq2, mk2, mk2)
+    assert o.shape == (T + M, 4, 128)
+    torch.ops.vllm.unified_meta_attention_with_output(mq, mk, mk, torch.empty(T + M, 4, 128, device="meta"),
+                                                     "test.layers.0.attn", mq2, mk2, mk2)
+    del A._LAYERS["test.layers.0.attn"]
+
+
+# ------------------------------------------------------------------------------------- f4 (V1 adapter)
+def test_v1_metadata_builder_bit_exact():
+    """``CommonAttentionMetadata`` -> ``MetaAttentionV1Metadata``: the decode / prefill split and the
+    rebased offsets are exact integer work."""
+    from types import SimpleNamespace
+    from vllm_hymeta_b200.attention.meta_attention_v1 import (MetaAttentionV1Backend,
+                                                              MetaAttentionV1Impl,
+                                                              MetaAttentionV1MetadataBuilder)
+    qsl = torch.tensor([0, 1, 2, 3, 13, 41, 42], dtype=torch.int32)      # 3 decodes, 10, 28, then a 1-token chunk
+    seq = torch.tensor([5, 9, 300, 10, 60, 7], dtype=torch.int32)
+    cm = SimpleNamespace(query_start_loc=qsl, query_start_loc_cpu=qsl, seq_lens=seq, num_reqs=6,
+                         num_actual_tokens=42, max_query_len=28, max_seq_len=300,
+                         block_table_tensor=torch.arange(6 * 20, dtype=torch.int32).view(6, 20),
+                         slot_mapping=torch.arange(50), causal=True)            # slot_mapping padded
+    b = MetaAttentionV1MetadataBuilder(SimpleNamespace(block_size=16), ["l"], None, "cpu")
+    md = b.build(0, cm)
+    assert (md.num_decodes, md.num_prefills, md.num_prefill_tokens, md.num_actual_tokens) == (3, 3, 39, 42)
+    assert md.prefill_query_start_loc.tolist() == [0, 10, 38, 39]
+    assert md.prefill_seq_start_loc.tolist() == [0, 10, 70, 77]
+    assert md.max_prefill_query_len == 28 and md.slot_mapping.numel() == 42
+    assert md.block_table.shape == (6, 20) and md.seq_lens.dtype == torch.int32
+    cm.query_start_loc = cm.query_start_loc_cpu = torch.tensor([0, 1, 2], dtype=torch.int32)
+    cm.seq_lens, cm.num_reqs, cm.num_actual_tokens, cm.max_query_len = seq[:2], 2, 2, 1
+    md = b.build(0, cm)
+    assert md.num_decodes == 2 and md.num_prefills == 0 and md.prefill_query_start_loc is None
+    assert MetaAttentionV1Backend.get_kv_cache_shape(7, 256, 4, 128) == (2, 7, 256, 4, 128)
+    with pytest.raises(ValueError):
+        MetaAttentionV1Backend.get_kv_cache_shape(7, 24, 4, 128)
+    with pytest.raises(NotImplementedError):
+        MetaAttentionV1Impl(28, 128, 0.1, 4, alibi_slopes=[1.0])
+    with pytest.raises(ValueError):
+        MetaAttentionV1Impl(28, 64, 0.1, 4)
+    assert MetaAttentionV1Impl(28, 128, 0.1, 4, sliding_window=4096).window_left == 4095

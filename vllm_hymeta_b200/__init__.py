@@ -13,7 +13,11 @@ def register():
 
 
 def register_model():
-    """vllm.general_plugins entry point (reference vllm_hymeta/__init__.py:6-11)."""
+    """vllm.general_plugins entry point (reference vllm_hymeta/__init__.py:6-11).  Besides the two
+    model registrations it puts the V1 adapter of the backend into the installed vLLM's
+    ``AttentionBackendEnum.CUSTOM`` slot when that registry exists (vLLM >= 0.11)."""
+    from .attention.meta_attention_v1 import register_v1_backend
+    register_v1_backend()
     from .model_for_7B import register_7B_model
     register_7B_model()
     from .models import register_model as _register

@@ -10,6 +10,7 @@ vLLM-side -- ``forward`` takes post-RoPE q/k/v.
 """
 from __future__ import annotations
 
+from contextlib import contextmanager
 from typing import Optional
 
 import torch
@@ -49,13 +50,106 @@ class HymetaRotaryEmbedding:
     __call__ = forward
 
 
+# ---------------------------------------------------------------------------------------------
+# forward context + the custom ops of the reference (models/attention.py:286-409)
+# ---------------------------------------------------------------------------------------------
+class ForwardContext:
+    """The three fields of vLLM's ForwardContext the ops read (reference :361-366)."""
+
+    def __init__(self, attn_metadata, no_compile_layers, virtual_engine: int = 0):
+        self.attn_metadata = attn_metadata
+        self.no_compile_layers = no_compile_layers
+        self.virtual_engine = virtual_engine
+
+
+_LAYERS: dict = {}          # layer_name -> MetaAttention (vLLM: compilation_config.static_forward_context)
+_forward_context: Optional[ForwardContext] = None
+
+
+@contextmanager
+def set_forward_context(attn_metadata, virtual_engine: int = 0, layers: Optional[dict] = None):
+    """Stand-alone equivalent of ``vllm.forward_context.set_forward_context`` for callers that run
+    the layers without a vLLM engine (tests, bench.py)."""
+    global _forward_context
+    prev = _forward_context
+    _forward_context = ForwardContext(attn_metadata, _LAYERS if layers is None else layers, virtual_engine)
+    try:
+        yield _forward_context
+    finally:
+        _forward_context = prev
+
+
+def get_forward_context() -> ForwardContext:
+    """This package's context when one is set, else vLLM's (the engine sets it around the model's
+    forward; reference :361)."""
+    if _forward_context is not None:
+        return _forward_context
+    from vllm.forward_context import get_forward_context as _vllm_ctx  # type: ignore
+    return _vllm_ctx()
+
+
+def _layer_kv_cache(layer, ctx: ForwardContext) -> torch.Tensor:
+    kv = layer.kv_cache
+    return kv[ctx.virtual_engine] if isinstance(kv, (list, tuple)) else kv
+
+
+def _unified_meta_attention_with_output(query: torch.Tensor, key: torch.Tensor, value: torch.Tensor,
+                                        output: torch.Tensor, layer_name: str,
+                                        query2: Optional[torch.Tensor] = None,
+                                        key2: Optional[torch.Tensor] = None,
+                                        value2: Optional[torch.Tensor] = None) -> None:
+    ctx = get_forward_context()
+    layer = ctx.no_compile_layers[layer_name]
+    layer.impl.forward(layer, query, key, value, query2, key2, value2, _layer_kv_cache(layer, ctx),
+                       ctx.attn_metadata, output=output)
+
+
+def _unified_meta_attention(query: torch.Tensor, key: torch.Tensor, value: torch.Tensor,
+                            layer_name: str, query2: Optional[torch.Tensor] = None,
+                            key2: Optional[torch.Tensor] = None,
+                            value2: Optional[torch.Tensor] = None) -> torch.Tensor:
+    rows = query.shape[0] + (query2.shape[0] if query2 is not None else 0)
+    output = torch.empty((rows,) + tuple(query.shape[1:]), dtype=query.dtype, device=query.device)
+    _unified_meta_attention_with_output(query, key, value, output, layer_name, query2, key2, value2)
+    return output
+
+
+def _register_custom_ops() -> None:
+    """``torch.ops.vllm.unified_meta_attention[_with_output]`` -- same op names and arguments as the
+    reference (:317-409).  The fakes carry the query2/key2/value2 parameters the reference's
+    ``unified_meta_attention_fake`` forgets (:343-349), and the functional op's fake
+    accounts for the meta rows in its output shape.  Registering twice (re-import, or the reference
+    plugin loaded next to this one) is tolerated."""
+    try:
+        torch.library.custom_op("vllm::unified_meta_attention_with_output",
+                                _unified_meta_attention_with_output, mutates_args=["output"])
+
+        @torch.library.register_fake("vllm::unified_meta_attention_with_output")
+        def _(query, key, value, output, layer_name, query2=None, key2=None, value2=None):
+            return None
+
+        torch.library.custom_op("vllm::unified_meta_attention", _unified_meta_attention, mutates_args=[])
+
+        @torch.library.register_fake("vllm::unified_meta_attention")
+        def _(query, key, value, layer_name, query2=None, key2=None, value2=None):
+            rows = query.shape[0] + (query2.shape[0] if query2 is not None else 0)
+            return query.new_empty((rows,) + tuple(query.shape[1:]))
+    except RuntimeError:      # already defined in this process
+        pass
+
+
+_register_custom_ops()
+
+
 class MetaAttention:
     """Reference models/attention.py:25-283 without the vLLM config plumbing: same ``forward``
-    arguments; ``attn_metadata`` is passed explicitly instead of through vLLM's forward context."""
+    arguments.  ``attn_metadata`` may be passed explicitly; when omitted it comes from the forward
+    context, and with ``use_direct_call=False`` the call goes through
+    ``torch.ops.vllm.unified_meta_attention_with_output`` exactly as in the reference (:242-245)."""
 
     def __init__(self, num_heads: int, head_size: int, scale: float, num_kv_heads: Optional[int] = None,
                  per_layer_sliding_window: Optional[int] = None, num_meta_tokens: int = 128,
-                 kv_cache_dtype: str = "auto", prefix: str = ""):
+                 kv_cache_dtype: str = "auto", prefix: str = "", use_direct_call: bool = True):
         self.num_heads = num_heads
         self.head_size = head_size
         self.num_kv_heads = num_kv_heads if num_kv_heads is not None else num_heads
@@ -66,6 +160,11 @@ class MetaAttention:
                                       num_meta_tokens=num_meta_tokens)
         self.use_output = self.attn_backend.accept_output_buffer
         self.layer_name = prefix
+        self.use_direct_call = use_direct_call
+        if prefix:
+            if prefix in _LAYERS:
+                raise ValueError(f"Duplicate layer name: {prefix}")      # reference :164-165
+            _LAYERS[prefix] = self
         self.kv_cache = torch.tensor([])          # replaced by bind_kv_cache (reference :170-176)
         self.kv_already_written = False           # set per call by FlashAttention.forward_fused
 
@@ -82,8 +181,16 @@ class MetaAttention:
         k = key.view(-1, self.num_kv_heads, self.head_size) if key is not None else None
         v = value.view(-1, self.num_kv_heads, self.head_size) if value is not None else None
         q2 = query2.view(-1, self.num_heads, self.head_size) if query2 is not None else None
-        self.impl.forward(self, q, k, v, q2, key2, value2, self.kv_cache, attn_metadata,
-                          output=output.view(-1, self.num_heads, self.head_size))
+        o3 = output.view(-1, self.num_heads, self.head_size)
+        if self.use_direct_call:
+            if attn_metadata is None:
+                ctx = get_forward_context()
+                attn_metadata, kv_cache = ctx.attn_metadata, _layer_kv_cache(self, ctx)
+            else:
+                kv_cache = self.kv_cache
+            self.impl.forward(self, q, k, v, q2, key2, value2, kv_cache, attn_metadata, output=o3)
+        else:
+            torch.ops.vllm.unified_meta_attention_with_output(q, k, v, o3, self.layer_name, q2, key2, value2)
         return output.view(-1, hidden)
 
 
