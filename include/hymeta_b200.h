@@ -272,6 +272,21 @@ int hymeta_swa_meta_decode_paged_fused(const void* q, void* k_cache, void* v_cac
                                        void* stream);
 
 /* ------------------------------------------------------------------------------------------------
+ * a10 multi-step decode metadata advance -- replaces vllm._custom_ops.advance_step_flashattn as
+ *     called by MetaAttentionMetadata.advance_step (vllm_hymeta/attention/meta_attention.py:338-409).
+ *
+ * For i < num_queries: seq_lens[i] += 1; p = seq_lens[i] - 1; input_positions[i] = p;
+ * input_tokens[i] = sampled_token_ids[i]; slot_mapping[i] = block_tables[i, p / block_size] *
+ * block_size + p % block_size.  For num_queries <= i < num_seqs (CUDA-graph padding):
+ * slot_mapping[i] = -1.  input_tokens / sampled_token_ids / input_positions may be null (the
+ * attention path needs only seq_lens and slot_mapping).  Exact integer work.
+ * ---------------------------------------------------------------------------------------------- */
+int hymeta_advance_step(int num_seqs, int num_queries, int block_size, int64_t* input_tokens,
+                        const int64_t* sampled_token_ids, int64_t* input_positions,
+                        int32_t* seq_lens, int64_t* slot_mapping, const int32_t* block_tables,
+                        int64_t bt_stride, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
  * a7  SWA + meta-prefix varlen prefill -- replaces metatoken_flash_attn_varlen_func
  *     (vllm_hymeta/attention/fa_kernel_metatoken.py:329-374 -> :198-285: two flash-attn
  *      launches + TorchScript LSE merge + concat, in ONE kernel).

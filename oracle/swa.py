@@ -242,3 +242,23 @@ def synth_swa_inputs(T: int, H: int, Hkv: int, D: int, seed: int, M: int = 0,
         k2 = torch.randn(M, Hkv, D, generator=gen).to(dtype)
         v2 = torch.randn(M, Hkv, D, generator=gen).to(dtype)
     return q, k, v, k2, v2
+
+
+# ---------------------------------------------------------------------------------- a10
+def advance_step(num_seqs, num_queries, block_size, input_tokens, sampled_token_ids,
+                 input_positions, seq_lens, slot_mapping, block_tables) -> None:
+    """vLLM 0.10.0 ``advance_step_flashattn`` (csrc/prepare_inputs/advance_step.cu; not vendored in
+    the reference, call site vllm_hymeta/attention/meta_attention.py:401-409) restated, in place:
+    live rows take their sampled token, grow by one position and get that position's slot through
+    the block table; CUDA-graph padding rows get slot -1."""
+    for i in range(num_seqs):
+        if i >= num_queries:
+            slot_mapping[i] = -1
+            continue
+        if input_tokens is not None and sampled_token_ids is not None:
+            input_tokens[i] = sampled_token_ids[i]
+        seq_lens[i] += 1
+        pos = int(seq_lens[i]) - 1
+        if input_positions is not None:
+            input_positions[i] = pos
+        slot_mapping[i] = int(block_tables[i][pos // block_size]) * block_size + pos % block_size

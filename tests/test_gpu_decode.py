@@ -348,3 +348,39 @@ def test_swa_decode_fused_write_padded_rows_by_slot_mapping(ops):
     with pytest.raises(ValueError):
         ops.swa_meta_decode_paged(q, kc_b, vc_b, full.to(DEV), d_lens, None, None, wl,
                                   new_slot_mapping=slot.to(DEV))
+
+
+# ------------------------------------------------------------------------------- a10 multi-step
+def test_advance_step_bit_exact_and_metadata_protocol(ops):
+    """``MetaAttentionMetadata.advance_step`` (reference meta_attention.py:338-409): three steps of
+    multi-step decode on a CUDA-graph padded batch, device tensors bit-exact against the restated
+    vLLM kernel, Python-side fields advanced as the reference does."""
+    from types import SimpleNamespace
+    from vllm_hymeta_b200.attention.meta_attention import MetaAttentionMetadataBuilder, SeqData
+    bs, nq, ns = 16, 5, 8
+    gen = torch.Generator().manual_seed(8)
+    lens = [15, 16, 17, 31, 200]
+    tables = [torch.randperm(64, generator=gen)[:16].tolist() for _ in lens]
+    graph_bt = torch.zeros(ns, 16, dtype=torch.int32).numpy()
+    b = MetaAttentionMetadataBuilder(block_size=bs, sliding_window=None, device=DEV, graph_block_tables=graph_bt)
+    for L, bt in zip(lens, tables):
+        b.add(SeqData(False, L, 1, L - 1, bt))
+    md = b.build(seq_lens=lens + [1] * (ns - nq), query_lens=[1] * nq, cuda_graph_pad_size=ns - nq, batch_size=ns)
+    assert md.use_cuda_graph and md.slot_mapping.shape == (ns,) and md.slot_mapping[nq:].tolist() == [-1] * 3
+    ref = dict(tok=torch.zeros(ns, dtype=torch.int64), pos=torch.zeros(ns, dtype=torch.int64),
+               seq=md.seq_lens_tensor.cpu().clone(), slot=md.slot_mapping.cpu().clone(),
+               bt=md.block_tables.cpu().clone())
+    mi = SimpleNamespace(input_tokens=torch.zeros(ns, dtype=torch.int64, device=DEV),
+                         input_positions=torch.zeros(ns, dtype=torch.int64, device=DEV))
+    md.context_lens_tensor = md.context_lens_tensor[:nq]
+    for step in range(3):
+        sampled = torch.randint(0, 50000, (nq,), generator=gen)
+        md.advance_step(mi, sampled.to(DEV), bs, ns, nq)
+        oswa.advance_step(ns, nq, bs, ref["tok"], sampled, ref["pos"], ref["seq"], ref["slot"], ref["bt"].tolist())
+        torch.cuda.synchronize()
+        assert torch.equal(md.seq_lens_tensor.cpu(), ref["seq"])
+        assert torch.equal(md.slot_mapping.cpu(), ref["slot"])
+        assert torch.equal(mi.input_tokens.cpu(), ref["tok"]) and torch.equal(mi.input_positions.cpu(), ref["pos"])
+        assert md.seq_lens[:nq] == [L + step + 1 for L in lens] and md.max_decode_seq_len == 200 + step + 1
+    with pytest.raises(ValueError):
+        ops.advance_step(4, 5, bs, md.seq_lens_tensor, md.slot_mapping, md.block_tables)

@@ -37,6 +37,7 @@ SIGNATURES = {
     "hymeta_swa_meta_decode_paged_fused": (_i, [_p] * 9 + [_sz] + [_i] * 8 + [_i64, _i, _f] + [_i64] * 14 +
                                            [_p, _p] + [_i64] * 4 + [_p, _p, _p]),
     "hymeta_swa_meta_prefill_varlen": (_i, [_p] * 10 + [_i64, _i] + [_i] * 9 + [_f] + [_i64] * 16 + [_p]),
+    "hymeta_advance_step": (_i, [_i, _i, _i, _p, _p, _p, _p, _p, _p, _i64, _p]),
     "hymeta_state_zero_slots": (_i, [_p, _p, _i, _i, _i64, _i64, _i64, _p]),
     "hymeta_state_copy_slot": (_i, [_p, _i, _i, _i, _i64, _i64, _i64, _p]),
     "hymeta_selftest_umma": (_i, [_p]),

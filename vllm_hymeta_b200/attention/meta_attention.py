@@ -18,6 +18,7 @@ from dataclasses import dataclass
 from itertools import accumulate
 from typing import Any, Dict, List, Optional, Tuple, Type
 
+import numpy as np
 import torch
 
 from ..slot_cache import PAD_SLOT_ID
@@ -171,6 +172,56 @@ class MetaAttentionMetadata(AttentionMetadata):
             block_tables=sl(self.block_tables, n), use_cuda_graph=self.use_cuda_graph)
         return self._cached_decode_metadata
 
+    def advance_step(self, model_input, sampled_token_ids: Optional[torch.Tensor], block_size: int,
+                     num_seqs: int, num_queries: int, turn_prefills_into_decodes: bool = False):
+        """Update the metadata in place to advance one decode step (multi-step scheduling; reference
+        :338-409, same assertions).  The device half -- seq_lens_tensor += 1, new slot_mapping through
+        the block tables, -1 for CUDA-graph padding rows, next input tokens / positions -- is ONE
+        launch of ``ops.advance_step`` (was ``ops.advance_step_flashattn``)."""
+        from .. import ops
+        if num_seqs != num_queries:
+            assert num_seqs > num_queries
+            assert self.use_cuda_graph
+        if turn_prefills_into_decodes:
+            assert self.num_decode_tokens + self.num_prefills == num_seqs
+            self.num_decode_tokens += self.num_prefills
+            self.num_prefills = 0
+            self.num_prefill_tokens = 0
+            self.max_prefill_seq_len = 0
+            self.max_query_len = 1
+            self.slot_mapping = self.slot_mapping[:num_seqs]
+        else:
+            assert self.seq_lens is not None
+            assert self.max_decode_seq_len == max(self.seq_lens)
+        assert self.num_prefills == 0
+        assert self.num_prefill_tokens == 0
+        assert self.num_decode_tokens == num_seqs
+        assert self.slot_mapping.shape == (num_seqs, )
+        assert self.seq_lens is not None
+        assert len(self.seq_lens) == num_seqs
+        assert self.seq_lens_tensor is not None
+        assert self.seq_lens_tensor.shape == (num_seqs, )
+        assert self.max_query_len == 1
+        assert self.max_prefill_seq_len == 0
+        assert self.query_start_loc is not None
+        assert self.query_start_loc.shape == (num_queries + 1, )
+        assert self.seq_start_loc is not None
+        assert self.seq_start_loc.shape == (num_seqs + 1, )
+        assert self.context_lens_tensor is not None
+        assert self.context_lens_tensor.shape == (num_queries, )
+        assert self.block_tables is not None
+        assert self.block_tables.shape[0] == num_seqs
+        # only the live queries advance: tensors may be padded to the captured batch size
+        for i in range(num_queries):
+            self.seq_lens[i] += 1
+        self.max_decode_seq_len = max(self.seq_lens)
+        self._cached_decode_metadata = None
+        ops.advance_step(num_seqs, num_queries, block_size, self.seq_lens_tensor, self.slot_mapping,
+                         self.block_tables,
+                         input_tokens=getattr(model_input, "input_tokens", None),
+                         sampled_token_ids=sampled_token_ids,
+                         input_positions=getattr(model_input, "input_positions", None))
+
 
 # ----------------------------------------------------------------------------------------------
 # slot-mapping helpers of vLLM 0.10.0 (vllm/attention/backends/utils.py), restated: they are vLLM
@@ -184,15 +235,24 @@ def compute_slot_mapping_start_idx(is_prompt: bool, query_len: int, context_len:
     return 0
 
 
-def compute_slot_mapping(is_profile_run: bool, slot_mapping: List[int], seq_len: int,
+def compute_slot_mapping(is_profile_run: bool, slot_mapping: List, seq_len: int,
                          context_len: int, start_idx: int, block_size: int,
                          block_table: Optional[List[int]]) -> None:
+    """Appends ONE int64 numpy chunk per sequence to ``slot_mapping`` (a list of chunks that
+    ``build`` concatenates): PAD for tokens that are never cached, else
+    ``block_table[i // block_size] * block_size + i % block_size`` for i in [context, seq_len) --
+    vectorised, a 8192-token prompt is one arange instead of 8192 Python iterations."""
     if is_profile_run:
-        slot_mapping.extend([PAD_SLOT_ID] * (seq_len - context_len))
+        slot_mapping.append(np.full(seq_len - context_len, PAD_SLOT_ID, dtype=np.int64))
         return
-    slot_mapping.extend([PAD_SLOT_ID] * max(0, start_idx - context_len))
-    for i in range(max(start_idx, context_len), seq_len):
-        slot_mapping.append(block_table[i // block_size] * block_size + i % block_size)
+    n_pad = max(0, start_idx - context_len)
+    lo = max(start_idx, context_len)
+    i = np.arange(lo, max(lo, seq_len), dtype=np.int64)
+    bt = np.asarray(block_table, dtype=np.int64)
+    chunk = bt[i // block_size] * block_size + i % block_size if i.size else i
+    if n_pad:
+        chunk = np.concatenate([np.full(n_pad, PAD_SLOT_ID, dtype=np.int64), chunk])
+    slot_mapping.append(chunk)
 
 
 @dataclass
@@ -238,7 +298,7 @@ class MetaAttentionMetadataBuilder:
         self.prepare()
 
     def prepare(self):
-        self.slot_mapping: List[int] = []
+        self.slot_mapping: List[np.ndarray] = []     # one int64 chunk per sequence
         self.prefill_seq_lens: List[int] = []
         self.context_lens: List[int] = []
         self.block_tables: List[List[int]] = []
@@ -301,7 +361,12 @@ class MetaAttentionMetadataBuilder:
         return t.to(device=self.device, non_blocking=True)
 
     def _h2d(self, data, dtype):
-        t = torch.tensor(data, dtype=dtype, pin_memory=self.pin_memory and torch.cuda.is_available())
+        pin = self.pin_memory and torch.cuda.is_available()
+        if isinstance(data, np.ndarray):
+            t = torch.from_numpy(data).to(dtype)
+            t = t.pin_memory() if pin else t
+        else:
+            t = torch.tensor(data, dtype=dtype, pin_memory=pin)
         return t.to(self.device, non_blocking=True)
 
     def build(self, seq_lens: Optional[List[int]] = None, query_lens: Optional[List[int]] = None,
@@ -322,9 +387,11 @@ class MetaAttentionMetadataBuilder:
         query_start_loc = list(accumulate(query_lens, initial=0))
         seq_start_loc = list(accumulate(seq_lens, initial=0))
         num_seqs = len(seq_lens)
-        slot_mapping = list(self.slot_mapping)
+        chunks = list(self.slot_mapping)
         if use_captured_graph:
-            slot_mapping.extend([PAD_SLOT_ID] * cuda_graph_pad_size)
+            chunks.append(np.full(cuda_graph_pad_size, PAD_SLOT_ID, dtype=np.int64))
+        slot_mapping = np.concatenate(chunks) if chunks else np.zeros(0, dtype=np.int64)
+        if use_captured_graph:
             num_decode_tokens = batch_size - self.num_prefill_tokens
             block_tables = self._get_graph_runner_block_tables(num_seqs, self.block_tables)
         else:

@@ -51,9 +51,49 @@ state_copy_kernel(uint4* __restrict__ state, int from_slot, int to_slot, int64_t
     dst[i] = src[i];
 }
 
+// Multi-step decode: advance the device-side metadata by one token per live request (vLLM's
+// advance_step_flashattn, called from MetaAttentionMetadata.advance_step, meta_attention.py:338-409).
+__global__ void __launch_bounds__(256)
+advance_step_kernel(int num_seqs, int num_queries, int block_size, int64_t* __restrict__ input_tokens,
+                    const int64_t* __restrict__ sampled_token_ids, int64_t* __restrict__ input_positions,
+                    int32_t* __restrict__ seq_lens, int64_t* __restrict__ slot_mapping,
+                    const int32_t* __restrict__ block_tables, int64_t bt_stride) {
+  pdl_wait();
+  pdl_launch_dependents();
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < num_seqs; i += gridDim.x * blockDim.x) {
+    if (i >= num_queries) {          // CUDA-graph padding rows: nothing is cached for them
+      slot_mapping[i] = -1;
+      continue;
+    }
+    if (input_tokens && sampled_token_ids) input_tokens[i] = sampled_token_ids[i];
+    const int next_len = seq_lens[i] + 1;
+    const int pos = next_len - 1;
+    seq_lens[i] = next_len;
+    if (input_positions) input_positions[i] = pos;
+    const int64_t blk = block_tables[(int64_t)i * bt_stride + pos / block_size];
+    slot_mapping[i] = blk * block_size + pos % block_size;
+  }
+}
+
 }  // namespace hymeta
 
 using namespace hymeta;
+
+extern "C" int hymeta_advance_step(int num_seqs, int num_queries, int block_size, int64_t* input_tokens,
+                                   const int64_t* sampled_token_ids, int64_t* input_positions,
+                                   int32_t* seq_lens, int64_t* slot_mapping,
+                                   const int32_t* block_tables, int64_t bt_stride, void* stream) {
+  if (num_seqs == 0) return HYMETA_OK;
+  if (num_seqs < 0 || num_queries < 0 || num_queries > num_seqs || block_size <= 0 || !seq_lens ||
+      !slot_mapping || !block_tables || bt_stride < 0)
+    return HYMETA_ERR_INVALID_ARG;
+  const int blocks = (num_seqs + 255) / 256;
+  launch_pdl(advance_step_kernel, dim3(blocks), dim3(256), 0, (cudaStream_t)stream, num_seqs,
+             num_queries, block_size, input_tokens, sampled_token_ids, input_positions, seq_lens,
+             slot_mapping, block_tables, bt_stride);
+  count_launch();
+  return check_launch();
+}
 
 extern "C" int hymeta_kv_write_paged(const void* key, const void* value, void* k_cache,
                                      void* v_cache, const int64_t* slot_mapping, int T, int Hkv,

@@ -4,6 +4,7 @@ memory, the current stream and dtype/shape checks.  Every function enqueues on
 """
 from __future__ import annotations
 
+import functools
 from typing import Optional
 
 import torch
@@ -32,12 +33,46 @@ def _req(t: torch.Tensor, name: str, dtype=None):
         raise ValueError(f"{name} must be contiguous in its last dimension")
 
 
+# Optional per-launch timing for bench.py: between timing_begin() and timing_end() every wrapped op
+# records a CUDA-event pair on the current stream around its launch (never during graph capture).
+_TIMING = None
+
+
+def timing_begin() -> None:
+    global _TIMING
+    _TIMING = []
+
+
+def timing_end():
+    """-> list of (op name, start event, end event) recorded since timing_begin()."""
+    global _TIMING
+    rec, _TIMING = _TIMING or [], None
+    return rec
+
+
+def _timed(name: str):
+    def deco(fn):
+        @functools.wraps(fn)
+        def wrapper(*args, **kwargs):
+            if _TIMING is None or torch.cuda.is_current_stream_capturing():
+                return fn(*args, **kwargs)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            r = fn(*args, **kwargs)
+            e1.record()
+            _TIMING.append((name, e0, e1))
+            return r
+        return wrapper
+    return deco
+
+
 def launch_count() -> int:
     """Kernels launched by the library so far in this process."""
     return int(lib().hymeta_launch_count())
 
 
 # ----------------------------------------------------------------------------------- a2
+@_timed("gla_decode")
 def gla_decode(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, g: torch.Tensor,
                state: torch.Tensor, slot_idx: torch.Tensor, scale: Optional[float] = None,
                out: Optional[torch.Tensor] = None, gnorm_weight: Optional[torch.Tensor] = None,
@@ -75,6 +110,7 @@ def gla_decode(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, g: torch.Tenso
 
 
 # ----------------------------------------------------------------------------------- a3
+@_timed("gla_prefill")
 def gla_prefill_varlen(q, k, v, g, state, cu_seqlens, slot_idx, init_mode,
                        meta_state: Optional[torch.Tensor] = None, scale: Optional[float] = None,
                        write_state: bool = True, max_seqlen: Optional[int] = None,
@@ -168,6 +204,7 @@ def gla_prefill_seg_len(chains: int, max_seqlen: int, device=None, min_seg: int 
 
 
 # ----------------------------------------------------------------------------------- a4
+@_timed("gla_gate_70b")
 def gla_gate_70b(q: torch.Tensor, k: torch.Tensor, lower_bound: Optional[torch.Tensor] = None,
                  clamp_max: float = 0.95, inplace_q: bool = False):
     """70B feature map + gate in one launch.  q [T,H,D], k [T,Hk,D] bf16 (strided views of the
@@ -195,6 +232,7 @@ def gla_gate_70b(q: torch.Tensor, k: torch.Tensor, lower_bound: Optional[torch.T
     return q_out, k_out, g_out
 
 
+@_timed("gla_gate_7b")
 def gla_gate_7b(q: torch.Tensor, k: torch.Tensor, gk: torch.Tensor, normalizer: float = 16.0,
                 inplace: bool = False):
     """7B feature map + gate in one launch.  q [T,H,D], k, gk [T,Hk,D] bf16.
@@ -215,6 +253,7 @@ def gla_gate_7b(q: torch.Tensor, k: torch.Tensor, gk: torch.Tensor, normalizer: 
 
 
 # ----------------------------------------------------------------------------------- a9
+@_timed("kv_write")
 def kv_write_paged(key, value, k_cache, v_cache, slot_mapping) -> None:
     """key,value [T,Hkv,D]; caches [nb,bs,Hkv,D]; slot_mapping [T] int64 (<0 = skip)."""
     T, Hkv, D = key.shape
@@ -230,6 +269,32 @@ def kv_write_paged(key, value, k_cache, v_cache, slot_mapping) -> None:
         v_cache.stride(0), v_cache.stride(1), v_cache.stride(2), _stream()), "hymeta_kv_write_paged")
 
 
+# ----------------------------------------------------------------------------------- a10
+def advance_step(num_seqs: int, num_queries: int, block_size: int, seq_lens: torch.Tensor,
+                 slot_mapping: torch.Tensor, block_tables: torch.Tensor,
+                 input_tokens: Optional[torch.Tensor] = None,
+                 sampled_token_ids: Optional[torch.Tensor] = None,
+                 input_positions: Optional[torch.Tensor] = None) -> None:
+    """Device-side metadata advance of multi-step decode (vLLM ``advance_step_flashattn``):
+    seq_lens [num_seqs] int32 += 1 for the live rows, slot_mapping [num_seqs] int64 = slot of the new
+    last position through block_tables [num_seqs, max_blocks] int32; padded rows get slot -1."""
+    _req(seq_lens, "seq_lens", torch.int32)
+    _req(slot_mapping, "slot_mapping", torch.int64)
+    _req(block_tables, "block_tables", torch.int32)
+    for n, t in (("input_tokens", input_tokens), ("sampled_token_ids", sampled_token_ids),
+                 ("input_positions", input_positions)):
+        if t is not None:
+            _req(t, n, torch.int64)
+            if t.numel() < num_queries:
+                raise ValueError(f"{n} shorter than num_queries")
+    if seq_lens.numel() < num_seqs or slot_mapping.numel() < num_seqs or block_tables.shape[0] < num_seqs:
+        raise ValueError("seq_lens / slot_mapping / block_tables shorter than num_seqs")
+    check(lib().hymeta_advance_step(int(num_seqs), int(num_queries), int(block_size), _ptr(input_tokens),
+                                    _ptr(sampled_token_ids), _ptr(input_positions), _ptr(seq_lens),
+                                    _ptr(slot_mapping), _ptr(block_tables), block_tables.stride(0),
+                                    _stream()), "hymeta_advance_step")
+
+
 # ----------------------------------------------------------------------------------- f3
 def rope_cos_sin_cache(head_dim: int, max_position: int, base: float, device=None,
                        dtype=torch.bfloat16) -> torch.Tensor:
@@ -240,6 +305,7 @@ def rope_cos_sin_cache(head_dim: int, max_position: int, base: float, device=Non
     return torch.cat((freqs.cos(), freqs.sin()), dim=-1).to(dtype).to(device)
 
 
+@_timed("rope_kv_write")
 def rope_kv_write_paged(q, k, v, cos_sin_cache, positions, pos_offset=0, k_cache=None, v_cache=None,
                         slot_mapping=None, meta_k=None, meta_v=None, n_meta=0, q_out=None,
                         k_out=None):
@@ -315,6 +381,7 @@ def branch_sumsq(x_attn: torch.Tensor, x_linear: torch.Tensor,
     return out
 
 
+@_timed("branch_norm_merge")
 def branch_norm_merge(x_attn: torch.Tensor, x_linear: torch.Tensor, w_attn: torch.Tensor,
                       w_linear: torch.Tensor, eps: float, tp_world: int = 1,
                       means: Optional[torch.Tensor] = None, group=None,
@@ -378,6 +445,7 @@ def _ticket_buffer(nbytes: int, device) -> torch.Tensor:
     return t
 
 
+@_timed("swa_decode")
 def swa_meta_decode_paged(q, k_cache, v_cache, block_tables, cache_seqlens, meta_k, meta_v,
                           window_left: int, scale: Optional[float] = None,
                           out: Optional[torch.Tensor] = None,
@@ -446,6 +514,7 @@ def swa_meta_decode_paged(q, k_cache, v_cache, block_tables, cache_seqlens, meta
 
 
 # ----------------------------------------------------------------------------------- a7
+@_timed("swa_prefill")
 def swa_meta_prefill_varlen(q1, k1, v1, q2, meta_k, meta_v, cu_seqlens_q, cu_seqlens_k,
                             max_seqlen_q: int, window_left: int, scale: Optional[float] = None,
                             block_tables: Optional[torch.Tensor] = None,
