@@ -196,8 +196,12 @@ int hymeta_kv_write_paged(const void* key, const void* value, void* k_cache, voi
  * q_in [T,H,D], k_in,v_in [T,Hkv,D] (views of the qkv_proj output); q_out,k_out may alias the
  * inputs (the reference op is in place).  cos_sin_cache: the module's bf16 table [max_pos, D]
  * = [cos(pos*inv_freq) | sin(pos*inv_freq)] (modeling_hymeta.py:210-218, cache_dtype bf16 :1187).
- * Arithmetic = the reference op instantiated for bf16: each product and the add/sub rounded to
- * bf16 (bit-exact against torch bf16 arithmetic).
+ * Arithmetic, fp32_math == 0: the rotary op of the vLLM the reference pins (0.10.0,
+ * csrc/pos_encoding_kernels.cu instantiated for c10::BFloat16): each product and the add/sub
+ * rounded to bf16 (bit-exact against torch bf16 arithmetic; that vLLM is not installable here, so
+ * this mode is pinned to the source text only).  fp32_math != 0: products and add/sub in fp32, ONE
+ * rounding to bf16 -- bit-identical to torch.ops._C.rotary_embedding of the vLLM 0.22 installed
+ * next to this package, checked live on B200 (tests/test_gpu_live_libs.py).
  * Tokens t < n_meta are the meta tokens of the first pass: position t, k/v rows stored into
  * meta_k/meta_v [n_meta,Hkv,D] instead of pages.  Token t >= n_meta: position
  * positions[t-n_meta] + pos_offset (pos_offset = num_meta_tokens, :1314), rotated k and v stored
@@ -211,7 +215,8 @@ int hymeta_rope_kv_write_paged(
     int64_t qi_st, int64_t qi_sh, int64_t ki_st, int64_t ki_sh, int64_t vi_st, int64_t vi_sh,
     int64_t qo_st, int64_t qo_sh, int64_t ko_st, int64_t ko_sh,
     int64_t kc_sblk, int64_t kc_stok, int64_t kc_sh, int64_t vc_sblk, int64_t vc_stok,
-    int64_t vc_sh, int64_t mk_st, int64_t mk_sh, int64_t mv_st, int64_t mv_sh, void* stream);
+    int64_t vc_sh, int64_t mk_st, int64_t mk_sh, int64_t mv_st, int64_t mv_sh, int fp32_math,
+    void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * a8  SWA + meta-prefix paged decode -- replaces metatoken_flash_attn_with_kvcache

@@ -263,10 +263,11 @@ def test_kv_write_vs_vllm_reshape_and_cache_flash(ops, vllm_ops):
 
 
 def test_rope_vs_vllm_rotary_embedding(ops, vllm_ops):
-    """Bit-equality of ``hymeta_rope_kv_write_paged``'s rotation with vLLM's NeoX rotary op on the
-    same bf16 cos|sin table.  The installed vLLM is 0.22, not the reference's 0.10.0: equality pins
-    f3 against THIS build of the op; a mismatch is reported with its size (the op's arithmetic
-    may have changed between the two versions) and f3 stays pinned to the oracle only."""
+    """``hymeta_rope_kv_write_paged`` against the rotary op of the INSTALLED vLLM (0.22) on the same
+    bf16 cos|sin table.  That build computes in fp32 and rounds once (tools/probe_rope_vllm.py), so
+    ``fp32_math=True`` must reproduce it BIT FOR BIT; the default mode restates the per-operation
+    bf16 rounding of vLLM 0.10.0's kernel (the version the reference pins, not installable here) and
+    may differ from the 0.22 op by the two extra roundings only (<= 2 bf16 ulp)."""
     T, H, Hkv = 333, 28, 4
     gen = torch.Generator().manual_seed(19)
     q = torch.randn(T, H * D, generator=gen).bfloat16()
@@ -276,9 +277,11 @@ def test_rope_vs_vllm_rotary_embedding(ops, vllm_ops):
     qa, ka = q.to(DEV).clone(), k.to(DEV).clone()
     vllm_ops.rotary_embedding(pos.to(DEV), qa, ka, D, table, True)
     qb, kb = q.to(DEV).clone(), k.to(DEV).clone()
-    ops.rope_kv_write_paged(qb.view(T, H, D), kb.view(T, Hkv, D), None, table, pos.to(DEV))
+    ops.rope_kv_write_paged(qb.view(T, H, D), kb.view(T, Hkv, D), None, table, pos.to(DEV), fp32_math=True)
+    qc, kc = q.to(DEV).clone(), k.to(DEV).clone()
+    ops.rope_kv_write_paged(qc.view(T, H, D), kc.view(T, Hkv, D), None, table, pos.to(DEV))
     torch.cuda.synchronize()
-    dq = (qa.float() - qb.float()).abs().max().item()
-    same = (qa == qb).float().mean().item()
-    assert torch.equal(qa, qb) and torch.equal(ka, kb), \
-        f"rotary mismatch vs vLLM op: max|d|={dq:.4g}, identical fraction {same:.5f}"
+    assert torch.equal(qa, qb) and torch.equal(ka, kb), "fp32 mode must equal the installed vLLM op"
+    ulp = torch.maximum(qa.float().abs(), torch.tensor(2.0 ** -126, device=DEV)) * 2.0 ** -7
+    assert ((qa.float() - qc.float()).abs() <= 2 * ulp).all()
+    assert (qa == qc).float().mean().item() > 0.5

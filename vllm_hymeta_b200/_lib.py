@@ -30,7 +30,7 @@ SIGNATURES = {
     "hymeta_gla_gate_70b": (_i, [_p] * 6 + [_i] * 5 + [_i64] * 10 + [_f, _p]),
     "hymeta_gla_gate_7b": (_i, [_p] * 6 + [_i] * 4 + [_i64] * 12 + [_f, _p]),
     "hymeta_kv_write_paged": (_i, [_p] * 5 + [_i] * 4 + [_i64] * 10 + [_p]),
-    "hymeta_rope_kv_write_paged": (_i, [_p] * 6 + [_i, _p, _i64] + [_p] * 5 + [_i] * 6 + [_i64] * 20 + [_p]),
+    "hymeta_rope_kv_write_paged": (_i, [_p] * 6 + [_i, _p, _i64] + [_p] * 5 + [_i] * 6 + [_i64] * 20 + [_i, _p]),
     "hymeta_swa_decode_workspace_bytes": (_sz, [_i] * 8),
     "hymeta_swa_meta_decode_paged": (_i, [_p] * 9 + [_sz] + [_i] * 8 + [_i64, _i, _f] + [_i64] * 14 + [_p]),
     "hymeta_swa_decode_ticket_bytes": (_sz, [_i] * 3),

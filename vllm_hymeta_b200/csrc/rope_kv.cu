@@ -17,12 +17,16 @@ struct RopeKvParams {
   const __nv_bfloat16 *q_in, *k_in, *v_in, *cos_sin;
   __nv_bfloat16 *q_out, *k_out, *k_cache, *v_cache, *meta_k, *meta_v;
   const int64_t *positions, *slot_mapping;
-  int T, H, Hkv, n_meta, block_size, max_pos;
+  int T, H, Hkv, n_meta, block_size, max_pos, fp32_math;
   int64_t pos_offset;
   int64_t qi_st, qi_sh, ki_st, ki_sh, vi_st, vi_sh, qo_st, qo_sh, ko_st, ko_sh;
   int64_t kc_sblk, kc_stok, kc_sh, vc_sblk, vc_stok, vc_sh, mk_st, mk_sh, mv_st, mv_sh;
 };
 
+// FP32: the products (exact in fp32) are combined in fp32 and rounded to bf16 ONCE -- the arithmetic of
+// the rotary op in the vLLM 0.22 installed next to this package (bit-identical to it on B200:
+// tests/test_gpu_live_libs.py).  !FP32: rounding after every operation (vLLM 0.10.0 source).
+template <bool FP32>
 __device__ __forceinline__ void rope8(const uint4& x, const uint4& y, const uint4& c,
                                       const uint4& s, uint4& xo, uint4& yo) {
   const uint32_t* xp = &x.x; const uint32_t* yp = &y.x;
@@ -32,6 +36,13 @@ __device__ __forceinline__ void rope8(const uint4& x, const uint4& y, const uint
   for (int i = 0; i < 4; ++i) {
     const float x0 = bf16_lo(xp[i]), x1 = bf16_hi(xp[i]), y0 = bf16_lo(yp[i]), y1 = bf16_hi(yp[i]);
     const float c0 = bf16_lo(cp[i]), c1 = bf16_hi(cp[i]), s0 = bf16_lo(sp[i]), s1 = bf16_hi(sp[i]);
+    if (FP32) {
+      xop[i] = pack_bf16(__fsub_rn(__fmul_rn(x0, c0), __fmul_rn(y0, s0)),
+                         __fsub_rn(__fmul_rn(x1, c1), __fmul_rn(y1, s1)));
+      yop[i] = pack_bf16(__fadd_rn(__fmul_rn(y0, c0), __fmul_rn(x0, s0)),
+                         __fadd_rn(__fmul_rn(y1, c1), __fmul_rn(x1, s1)));
+      continue;
+    }
     xop[i] = pack_bf16(__fsub_rn(round_bf16(__fmul_rn(x0, c0)), round_bf16(__fmul_rn(y0, s0))),
                        __fsub_rn(round_bf16(__fmul_rn(x1, c1)), round_bf16(__fmul_rn(y1, s1))));
     yop[i] = pack_bf16(__fadd_rn(round_bf16(__fmul_rn(y0, c0)), round_bf16(__fmul_rn(x0, s0))),
@@ -85,7 +96,8 @@ __global__ void __launch_bounds__(256) rope_kv_write_kernel(const RopeKvParams p
     // coherent loads: q_out/k_out may alias q_in/k_in (in-place, as the reference op)
     const uint4 x = ldg_v4(src + c * 8), y = ldg_v4(src + kD / 2 + c * 8);
     uint4 xo, yo;
-    rope8(x, y, cv, sv, xo, yo);
+    if (p.fp32_math) rope8<true>(x, y, cv, sv, xo, yo);
+    else rope8<false>(x, y, cv, sv, xo, yo);
     __nv_bfloat16* out = is_q ? p.q_out + t * p.qo_st + h * p.qo_sh
                               : p.k_out + t * p.ko_st + h * p.ko_sh;
     stg_v4(out + c * 8, xo);
@@ -118,7 +130,8 @@ extern "C" int hymeta_rope_kv_write_paged(
     int64_t qi_st, int64_t qi_sh, int64_t ki_st, int64_t ki_sh, int64_t vi_st, int64_t vi_sh,
     int64_t qo_st, int64_t qo_sh, int64_t ko_st, int64_t ko_sh,
     int64_t kc_sblk, int64_t kc_stok, int64_t kc_sh, int64_t vc_sblk, int64_t vc_stok,
-    int64_t vc_sh, int64_t mk_st, int64_t mk_sh, int64_t mv_st, int64_t mv_sh, void* stream) {
+    int64_t vc_sh, int64_t mk_st, int64_t mk_sh, int64_t mv_st, int64_t mv_sh, int fp32_math,
+    void* stream) {
   if (T == 0) return HYMETA_OK;
   if (!q_in || !k_in || !v_in || !q_out || !k_out || !cos_sin_cache || T < 0 || H <= 0 ||
       Hkv <= 0 || n_meta < 0 || n_meta > T || max_pos <= 0)
@@ -143,7 +156,7 @@ extern "C" int hymeta_rope_kv_write_paged(
   p.meta_k = (__nv_bfloat16*)meta_k; p.meta_v = (__nv_bfloat16*)meta_v;
   p.positions = positions; p.slot_mapping = slot_mapping;
   p.T = T; p.H = H; p.Hkv = Hkv; p.n_meta = n_meta; p.block_size = paged ? block_size : 1;
-  p.max_pos = max_pos; p.pos_offset = pos_offset;
+  p.max_pos = max_pos; p.pos_offset = pos_offset; p.fp32_math = fp32_math ? 1 : 0;
   p.qi_st = qi_st; p.qi_sh = qi_sh; p.ki_st = ki_st; p.ki_sh = ki_sh; p.vi_st = vi_st;
   p.vi_sh = vi_sh; p.qo_st = qo_st; p.qo_sh = qo_sh; p.ko_st = ko_st; p.ko_sh = ko_sh;
   p.kc_sblk = kc_sblk; p.kc_stok = kc_stok; p.kc_sh = kc_sh; p.vc_sblk = vc_sblk;

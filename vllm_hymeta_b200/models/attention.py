@@ -26,7 +26,8 @@ class HymetaRotaryEmbedding:
     reference config, :1181-1188)."""
 
     def __init__(self, head_size: int, rotary_dim: int, max_position: int, base: float,
-                 is_neox_style: bool = True, cache_dtype: torch.dtype = torch.bfloat16):
+                 is_neox_style: bool = True, cache_dtype: torch.dtype = torch.bfloat16,
+                 fp32_math: bool = False):
         if not is_neox_style or rotary_dim != head_size:
             raise NotImplementedError("only NeoX-style full-head rotary is on the Hymeta path")
         if cache_dtype != torch.bfloat16:
@@ -34,6 +35,9 @@ class HymetaRotaryEmbedding:
         self.head_size, self.rotary_dim = head_size, rotary_dim
         self.max_position_embeddings, self.base = max_position, base
         self.is_neox_style, self.cache_dtype = is_neox_style, cache_dtype
+        # False: per-operation bf16 rounding (vLLM 0.10.0's op, what the reference runs on);
+        # True: fp32 math with one rounding (the op of the vLLM 0.22 installed here, bit for bit)
+        self.fp32_math = fp32_math
         from .. import ops
         self.cos_sin_cache = ops.rope_cos_sin_cache(head_size, max_position, base, dtype=cache_dtype)
 
@@ -44,7 +48,7 @@ class HymetaRotaryEmbedding:
             self.cos_sin_cache = self.cos_sin_cache.to(positions.device)
         D = self.head_size
         ops.rope_kv_write_paged(query.view(query.shape[0], -1, D), key.view(key.shape[0], -1, D),
-                                None, self.cos_sin_cache, positions)
+                                None, self.cos_sin_cache, positions, fp32_math=self.fp32_math)
         return query, key
 
     __call__ = forward
@@ -253,7 +257,8 @@ class FlashAttention:
             positions, M, kv_cache[0] if paged else None, kv_cache[1] if paged else None,
             attn_metadata.slot_mapping.flatten() if paged else None,
             kv_caches.meta_fattn_cache[0] if first else None,
-            kv_caches.meta_fattn_cache[1] if first else None, n_meta)
+            kv_caches.meta_fattn_cache[1] if first else None, n_meta,
+            fp32_math=rotary_emb.fp32_math)
         q2 = q[:M].reshape(M, H, D) if first else None
         k2 = kv_caches.meta_fattn_cache[0] if M > 0 else None
         v2 = kv_caches.meta_fattn_cache[1] if M > 0 else None

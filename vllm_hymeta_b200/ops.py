@@ -308,10 +308,12 @@ def rope_cos_sin_cache(head_dim: int, max_position: int, base: float, device=Non
 @_timed("rope_kv_write")
 def rope_kv_write_paged(q, k, v, cos_sin_cache, positions, pos_offset=0, k_cache=None, v_cache=None,
                         slot_mapping=None, meta_k=None, meta_v=None, n_meta=0, q_out=None,
-                        k_out=None):
+                        k_out=None, fp32_math: bool = False):
     """NeoX RoPE of q [T,H,D] and k [T,Hkv,D] (in place unless q_out/k_out are given), rotated
     k and v [T,Hkv,D] written to their pages, the first ``n_meta`` tokens captured into
-    meta_k/meta_v instead -- one launch.  Returns (q_out, k_out)."""
+    meta_k/meta_v instead -- one launch.  Returns (q_out, k_out).
+    fp32_math=False: bf16 rounding after every product and sum (the vLLM 0.10.0 op the reference
+    pins); True: fp32 math, one rounding (bit-identical to the installed vLLM 0.22 op)."""
     T, H, D = q.shape
     Hkv = k.shape[1]
     q_out = q if q_out is None else q_out
@@ -360,7 +362,8 @@ def rope_kv_write_paged(q, k, v, cos_sin_cache, positions, pos_offset=0, k_cache
         _ptr(meta_k) if n_meta > 0 else None, _ptr(meta_v) if n_meta > 0 else None,
         n_meta, T, H, Hkv, D, bs, q.stride(0), q.stride(1), k.stride(0), k.stride(1),
         v.stride(0), v.stride(1), q_out.stride(0), q_out.stride(1), k_out.stride(0),
-        k_out.stride(1), *kc, *vc, *mk, *mv, _stream()), "hymeta_rope_kv_write_paged")
+        k_out.stride(1), *kc, *vc, *mk, *mv, int(bool(fp32_math)), _stream()),
+        "hymeta_rope_kv_write_paged")
     return q_out, k_out
 
 
