@@ -35,7 +35,18 @@ constexpr int PF_SK = 2 * PF_TILE;
 constexpr int PF_SV = PF_SK + PF_NKS * PF_TILE;
 constexpr int PF_BAR = PF_SV + PF_NVS * PF_TILE;        // mbarriers + tmem ptr
 constexpr int PF_SMEM = PF_BAR + 256;
-constexpr int PF_THREADS = 320;
+#ifndef PF_OPT_REGS
+#define PF_OPT_REGS 1     // 384 threads (3 warpgroups) and setmaxnreg: softmax warps PF_REG_HI registers, the rest PF_REG_LO
+#endif
+#ifndef PF_OPT_PSPLIT
+#define PF_OPT_PSPLIT 2   // P handed to the MMA warp in this many column groups (1, 2 or 4), each with its own mbarrier
+#endif
+#ifndef PF_REG_LO
+#define PF_REG_LO 72
+#define PF_REG_HI 216
+#endif
+constexpr int PF_THREADS = PF_OPT_REGS ? 384 : 320;
+constexpr int PF_PS = PF_OPT_PSPLIT;
 constexpr float PF_RESCALE_T = 8.f;                     // lazy rescale threshold (log2 domain)
 
 struct SwaPrefillParams {
@@ -51,7 +62,15 @@ struct SwaPrefillParams {
   int paged, block_size, box_rows;
 };
 
-struct QTile { int on, rows, pmin, pmax, lo, hi; };   // real key-tile range [lo, hi] (empty if hi < lo)
+struct QTile { int on, rows, pmin, pmax, lo, hi; };
+
+#ifdef HYMETA_TRACE
+__device__ long long* g_swa_trace = nullptr;   // [steps][16] clock64 stamps of one CTA; tools/trace_swa_prefill.py
+#define PF_TRACE(step, ev) do { if (g_swa_trace && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && (step) < 256) \
+    g_swa_trace[(step) * 16 + (ev)] = clock64(); } while (0)
+#else
+#define PF_TRACE(step, ev) do {} while (0)
+#endif   // real key-tile range [lo, hi] (empty if hi < lo)
 
 __global__ void __launch_bounds__(PF_THREADS, 1)
 swa_prefill_kernel(const SwaPrefillParams p, const __grid_constant__ CUtensorMap tmQ,
@@ -117,7 +136,8 @@ swa_prefill_kernel(const SwaPrefillParams p, const __grid_constant__ CUtensorMap
   const uint32_t sQ = sbase + PF_SQ, sK = sbase + PF_SK, sV = sbase + PF_SV;
   const uint32_t bars = sbase + PF_BAR;
   const uint32_t bar_q = bars, bar_kf = bars + 8, bar_ke = bar_kf + 8 * PF_NKS, bar_vf = bar_ke + 8 * PF_NKS,
-                 bar_ve = bar_vf + 8 * PF_NVS, bar_s = bar_ve + 8 * PF_NVS, bar_p = bar_s + 16, bar_o = bar_p + 16;
+                 bar_ve = bar_vf + 8 * PF_NVS, bar_s = bar_ve + 8 * PF_NVS, bar_o = bar_s + 16, bar_p = bar_o + 16;
+  // bar_p: [tile][column group] -- 2 * PF_PS barriers (<= 64 bytes), ends at offset 88 + 32 + 64 = 184 < 200
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + PF_BAR + 200);
 
   if (tid == 0) {
@@ -125,7 +145,8 @@ swa_prefill_kernel(const SwaPrefillParams p, const __grid_constant__ CUtensorMap
     mbar_init(bar_q, 1);
     for (int s = 0; s < PF_NKS; ++s) { mbar_init(bar_kf + 8 * s, 1); mbar_init(bar_ke + 8 * s, 1); }
     for (int s = 0; s < PF_NVS; ++s) { mbar_init(bar_vf + 8 * s, 1); mbar_init(bar_ve + 8 * s, 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(bar_s + 8 * i, 1); mbar_init(bar_p + 8 * i, 128); mbar_init(bar_o + 8 * i, 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(bar_s + 8 * i, 1); mbar_init(bar_o + 8 * i, 1); }
+    for (int i = 0; i < 2 * PF_PS; ++i) mbar_init(bar_p + 8 * i, 128);
     fence_mbar_init();
   }
   if (warp == 9) tmem_alloc<512>(smem_u32(tmem_slot));
@@ -137,6 +158,9 @@ swa_prefill_kernel(const SwaPrefillParams p, const __grid_constant__ CUtensorMap
 
   if (warp == 8) {
     // ================================================================== TMA producer
+#if PF_OPT_REGS
+    setmaxnreg_dec<PF_REG_LO>();
+#endif
     if (elect_one_sync()) {
       const CUtensorMap* tq = meta_q ? &tmQ2 : &tmQ;
       tma_prefetch_desc(tq); tma_prefetch_desc(&tmK); tma_prefetch_desc(&tmV);
@@ -176,17 +200,22 @@ swa_prefill_kernel(const SwaPrefillParams p, const __grid_constant__ CUtensorMap
           const int st = t % PF_NKS;
           if (t >= PF_NKS) mbar_wait(bar_ke + 8 * st, ((t / PF_NKS) - 1) & 1);
           load_tile(sK + st * PF_TILE, bar_kf + 8 * st, t < nm ? &tmMK : &tmK, &tmK, t);
+          PF_TRACE(t, 12);
         }
         {
           const int st = t % PF_NVS;
           if (t >= PF_NVS) mbar_wait(bar_ve + 8 * st, ((t / PF_NVS) - 1) & 1);
           load_tile(sV + st * PF_TILE, bar_vf + 8 * st, t < nm ? &tmMV : &tmV, &tmV, t);
+          PF_TRACE(t, 13);
         }
       }
     }
     __syncwarp();
   } else if (warp == 9) {
     // ================================================================== MMA issuer
+#if PF_OPT_REGS
+    setmaxnreg_dec<PF_REG_LO>();
+#endif
     if (elect_one_sync()) {
       const uint32_t idesc_s = umma_idesc_bf16(PF_BM, PF_BN, 0, 0);
       const uint32_t idesc_o = umma_idesc_bf16(PF_BM, kD, 0, 1);
@@ -200,10 +229,10 @@ swa_prefill_kernel(const SwaPrefillParams p, const __grid_constant__ CUtensorMap
         }
         umma_commit(bar_s + 8 * i);
       };
-      auto issue_pv = [&](int i, int t, bool acc) {   // O_i (+)= P_i V(t)
+      auto issue_pv = [&](int i, int t, bool acc, int g) {   // O_i (+)= P_i V(t), column group g
         const uint32_t vb = sV + (t % PF_NVS) * PF_TILE;
 #pragma unroll
-        for (int ks = 0; ks < 8; ++ks) {
+        for (int ks = g * (8 / PF_PS); ks < (g + 1) * (8 / PF_PS); ++ks) {
           const uint64_t db = umma_desc_sw128(vb + ks * 2048, 16384, 1024);
           umma_bf16_ts(tmem + 256 + i * 128, tmem + i * 128 + ks * 8, db, idesc_o, (acc || ks > 0) ? 1u : 0u);
         }
@@ -220,10 +249,14 @@ swa_prefill_kernel(const SwaPrefillParams p, const __grid_constant__ CUtensorMap
         bool v_ready = false, k_ready = false;
         for (int i = 0; i < 2; ++i) {
           if (active(i, t)) {
-            mbar_wait(bar_p + 8 * i, cnt[i] & 1);
-            if (!v_ready) { mbar_wait(bar_vf + 8 * (t % PF_NVS), (t / PF_NVS) & 1); v_ready = true; }
-            tc_fence_after();
-            issue_pv(i, t, cnt[i] > 0);
+#pragma unroll
+            for (int g = 0; g < PF_PS; ++g) {
+              mbar_wait(bar_p + 8 * (i * PF_PS + g), cnt[i] & 1);
+              if (g == 0) PF_TRACE(t, 8 + 2 * i);
+              if (!v_ready) { mbar_wait(bar_vf + 8 * (t % PF_NVS), (t / PF_NVS) & 1); v_ready = true; }
+              tc_fence_after();
+              issue_pv(i, t, cnt[i] > 0, g);
+            }
             ++cnt[i];
             if (t == last_step[i]) umma_commit(bar_o + 8 * i);   // last key tile of this query tile
           }
@@ -232,14 +265,18 @@ swa_prefill_kernel(const SwaPrefillParams p, const __grid_constant__ CUtensorMap
             tc_fence_after();
             issue_s(i, t + 1);
           }
+          PF_TRACE(t, 9 + 2 * i);
         }
         umma_commit(bar_ve + 8 * (t % PF_NVS));
         if (t + 1 < n_steps) umma_commit(bar_ke + 8 * ((t + 1) % PF_NKS));
       }
     }
     __syncwarp();
-  } else {
+  } else if (warp < 8) {
     // ================================================================== softmax warps
+#if PF_OPT_REGS
+    setmaxnreg_inc<PF_REG_HI>();
+#endif
     const int i = warp >> 2;                     // query tile
     const int r = (warp & 3) * 32 + lane;        // row inside the tile == TMEM lane
     const QTile T = qt[i];
@@ -253,12 +290,14 @@ swa_prefill_kernel(const SwaPrefillParams p, const __grid_constant__ CUtensorMap
         if (!active(i, t)) continue;
         mbar_wait(bar_s + 8 * i, cnt & 1);
         tc_fence_after();
+        if ((tid & 127) == 0) PF_TRACE(t, 4 * i);
         uint32_t sr[128];
         tmem_ld32_nowait(tS + 0, *reinterpret_cast<uint32_t(*)[32]>(&sr[0]));
         tmem_ld32_nowait(tS + 32, *reinterpret_cast<uint32_t(*)[32]>(&sr[32]));
         tmem_ld32_nowait(tS + 64, *reinterpret_cast<uint32_t(*)[32]>(&sr[64]));
         tmem_ld32_nowait(tS + 96, *reinterpret_cast<uint32_t(*)[32]>(&sr[96]));
         tmem_wait_ld();
+        if ((tid & 127) == 0) PF_TRACE(t, 4 * i + 1);
         // ---- mask (tile-uniform decision)
         bool need_mask;
         int kp0, lo, hi;   // visible key positions of this row: [lo, hi]
@@ -304,21 +343,8 @@ swa_prefill_kernel(const SwaPrefillParams p, const __grid_constant__ CUtensorMap
             }
           }
         }
+        if ((tid & 127) == 0) PF_TRACE(t, 4 * i + 2);
         const float msub = (m_ref == -INFINITY) ? 0.f : m_ref;
-        float rs0 = 0.f, rs1 = 0.f, rs2 = 0.f, rs3 = 0.f;
-#pragma unroll
-        for (int c = 0; c < 4; ++c) {
-          uint32_t w[16];
-#pragma unroll
-          for (int j = 0; j < 16; ++j) {
-            const float a = exp2f(fmaf(__uint_as_float(sr[32 * c + 2 * j]), p.scale_log2, -msub));
-            const float b = exp2f(fmaf(__uint_as_float(sr[32 * c + 2 * j + 1]), p.scale_log2, -msub));
-            if (j & 1) { rs2 += a; rs3 += b; } else { rs0 += a; rs1 += b; }
-            w[j] = pack_bf16(a, b);
-          }
-          tmem_st16(tS + 16 * c, w);
-        }
-        l_run += (rs0 + rs1) + (rs2 + rs3);
         if (p.paged && t >= nm && (kp0 + PF_BN > Lk || kp0 < lo_all)) {
           // paged boundary tile: key rows outside [lo_all, Lk) are masked for every query (P = 0)
           // but may hold recycled-page bytes (NaN patterns), and 0 * NaN would poison O -- clear
@@ -336,9 +362,26 @@ swa_prefill_kernel(const SwaPrefillParams p, const __grid_constant__ CUtensorMap
           }
           fence_proxy_async_smem();
         }
-        tmem_wait_st();
-        tc_fence_before();
-        mbar_arrive(bar_p + 8 * i);
+        float rs0 = 0.f, rs1 = 0.f, rs2 = 0.f, rs3 = 0.f;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          uint32_t w[16];
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            const float a = exp2f(fmaf(__uint_as_float(sr[32 * c + 2 * j]), p.scale_log2, -msub));
+            const float b = exp2f(fmaf(__uint_as_float(sr[32 * c + 2 * j + 1]), p.scale_log2, -msub));
+            if (j & 1) { rs2 += a; rs3 += b; } else { rs0 += a; rs1 += b; }
+            w[j] = pack_bf16(a, b);
+          }
+          tmem_st16(tS + 16 * c, w);
+          if ((c + 1) % (4 / PF_PS) == 0) {   // column group complete: hand it to the MMA warp
+            tmem_wait_st();
+            tc_fence_before();
+            mbar_arrive(bar_p + 8 * (i * PF_PS + c / (4 / PF_PS)));
+          }
+        }
+        l_run += (rs0 + rs1) + (rs2 + rs3);
+        if ((tid & 127) == 0) PF_TRACE(t, 4 * i + 3);
         ++cnt;
       }
       // ---- epilogue: normalise, bf16, one 256-byte row per thread
@@ -368,6 +411,9 @@ swa_prefill_kernel(const SwaPrefillParams p, const __grid_constant__ CUtensorMap
       }
     }
   }
+#if PF_OPT_REGS
+  else setmaxnreg_dec<PF_REG_LO>();   // warps 10-11 only complete the third warpgroup
+#endif
   tc_fence_before();
   __syncthreads();
   if (warp == 9) tmem_dealloc<512>(tmem);
@@ -376,6 +422,12 @@ swa_prefill_kernel(const SwaPrefillParams p, const __grid_constant__ CUtensorMap
 }  // namespace hymeta
 
 using namespace hymeta;
+
+#ifdef HYMETA_TRACE
+extern "C" int hymeta_debug_set_swa_trace(void* buf) {
+  return (int)cudaMemcpyToSymbol(g_swa_trace, &buf, sizeof(buf));
+}
+#endif
 
 extern "C" int hymeta_swa_meta_prefill_varlen(
     const void* q1, const void* k1, const void* v1, const void* q2, const void* meta_k,
