@@ -50,6 +50,19 @@ struct DynSmemAttr {
   }
 };
 
+// SMs of the current device (persistent kernels launch one CTA per SM); cached per device ordinal.
+inline int sm_count() {
+  static std::atomic<int> cache[64] = {};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  int n = cache[dev & 63].load(std::memory_order_relaxed);
+  if (n <= 0) {
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+    cache[dev & 63].store(n, std::memory_order_relaxed);
+  }
+  return n;
+}
+
 // ---- programmatic dependent launch (PDL) ------------------------------------------------------
 // The decode step is a chain of short kernels (kv write -> split-K -> combine -> next layer ...);
 // launched with programmaticStreamSerialization the next kernel's CTAs are scheduled while the

@@ -5,27 +5,38 @@
 // (fa_kernel_metatoken.py:198-285): the meta keys are simply the first key tiles of every query
 // tile's single online softmax.
 //
-// CTA = TWO 128-row query tiles of one q-head (256 consecutive queries) against 128-key tiles,
-// warp-specialised, one CTA per SM (all 512 TMEM columns, 224 KB of smem):
-//   warp 8      TMA producer: Q0/Q1 once, then K tiles (2-stage ring) and V tiles (3-stage ring),
-//               SWIZZLE_128B boxes straight from the packed [T, Hkv, D] tensors
+// PERSISTENT: one CTA per SM (all 512 TMEM columns, 224 KB of smem) walks work items
+// item = (q-head, pair of 128-row query tiles, request), longest pairs first, CTA c taking items
+// c, c + grid, ... -- consecutive items are the heads of one (pair, request), so the G heads of a GQA
+// group run side by side on neighbouring SMs and share K/V tiles through L2.  Barriers, the K/V
+// rings and TMEM live across items, and the roles run decoupled, so the next item's Q/K loads and
+// its first S = Q K^T are in flight while the softmax warps still normalise and store the current
+// item's output: the per-item fill/drain (the cost that dominated short prompts) is overlapped.
+//
+// Warp-specialised, 3 warpgroups, setmaxnreg gives the softmax warps 208 registers (their 128
+// scores stay in registers; the hot loop has no spills):
+//   warp 8      TMA producer: Q0/Q1 per item, then K tiles (2-stage ring) and V tiles (3-stage
+//               ring), SWIZZLE_128B boxes straight from the packed [T, Hkv, D] tensors or -- paged --
+//               from the [D, Hkv, block_size, num_blocks] cache through the block table
 //   warp 9      MMA issuer (one lane):  S_i = Q_i K^T          tcgen05.mma SS, fp32 S in TMEM
 //                                       O_i += P_i V           tcgen05.mma TS: A = bf16 P in TMEM
 //                                                              (aliases S_i), B = V MN-major as landed
 //   warps 0-3   softmax of query tile 0, warps 4-7 of tile 1 (thread = query row = TMEM lane):
 //               one tcgen05.ld of the 128 scores, masks only on boundary tiles, exp2 in the log2
-//               domain, bf16 P stored back over S with tcgen05.st.  O stays in TMEM for the whole
-//               key loop; it is rescaled in place only when a row maximum grows by more than 2^8
-//               (lazy rescale), so the common step touches neither O nor shared memory.
+//               domain, bf16 P stored back over S with tcgen05.st and handed to the MMA warp in
+//               PF_PS column groups (PV of the first group runs under the exp2 of the second).  O
+//               stays in TMEM for the whole key loop; it is rescaled in place only when a row
+//               maximum grows by more than 2^8 (lazy rescale).
+//   warps 10-11 idle (they complete the third warpgroup for setmaxnreg)
 // The issue order  PV0(t) S0(t+1) PV1(t) S1(t+1)  lets tile 1's softmax run under tile 0's MMAs and
-// vice versa; MMAs of one CTA complete in order, so "S_i(t) has landed" also means O_i holds every
-// PV up to t-1 and the rescale needs no extra barrier.
-// grid.x = q-head so the G heads of a GQA group run side by side and share K/V tiles through L2.
+// vice versa; at an item's last step S_i(t+1) is the NEXT item's first S.  MMAs of one CTA complete
+// in order, so "S_i(t) has landed" also means O_i holds every PV up to t-1 and the rescale needs no
+// extra barrier; O_i is handed back to the MMA warp (bar_of) once the epilogue has read it.
 #include "umma.cuh"
 
 namespace hymeta {
 
-constexpr int PF_BM = 128;    // query rows per tile (two tiles per CTA)
+constexpr int PF_BM = 128;    // query rows per tile (two tiles per item)
 constexpr int PF_BN = 128;    // keys per tile
 constexpr int PF_NKS = 2;     // K ring stages
 constexpr int PF_NVS = 3;     // V ring stages
@@ -35,17 +46,14 @@ constexpr int PF_SK = 2 * PF_TILE;
 constexpr int PF_SV = PF_SK + PF_NKS * PF_TILE;
 constexpr int PF_BAR = PF_SV + PF_NVS * PF_TILE;        // mbarriers + tmem ptr
 constexpr int PF_SMEM = PF_BAR + 256;
-#ifndef PF_OPT_REGS
-#define PF_OPT_REGS 1     // 384 threads (3 warpgroups) and setmaxnreg: softmax warps PF_REG_HI registers, the rest PF_REG_LO
-#endif
 #ifndef PF_OPT_PSPLIT
 #define PF_OPT_PSPLIT 2   // P handed to the MMA warp in this many column groups (1, 2 or 4), each with its own mbarrier
 #endif
 #ifndef PF_REG_LO
-#define PF_REG_LO 72
-#define PF_REG_HI 216
+#define PF_REG_LO 88      // producer / MMA / idle warps
+#define PF_REG_HI 208     // softmax warps: 256 * 208 + 128 * 88 = 64512 = 384 * 168 (the launch allocation)
 #endif
-constexpr int PF_THREADS = PF_OPT_REGS ? 384 : 320;
+constexpr int PF_THREADS = 384;
 constexpr int PF_PS = PF_OPT_PSPLIT;
 constexpr float PF_RESCALE_T = 8.f;                     // lazy rescale threshold (log2 domain)
 
@@ -53,6 +61,7 @@ struct SwaPrefillParams {
   const int32_t *cu_q, *cu_k;
   __nv_bfloat16* out;
   int N, H, Hkv, M, window_left, has_q2, n_qpairs;
+  int n_z, n_items;             // requests incl. the meta-query pseudo-request; H * n_qpairs * n_z
   float scale_log2;
   int64_t o_st, o_sh;
   // paged keys (prefix-cache / chunked prefill / multi-token decode): logical key position p of
@@ -62,15 +71,100 @@ struct SwaPrefillParams {
   int paged, block_size, box_rows;
 };
 
-struct QTile { int on, rows, pmin, pmax, lo, hi; };
+struct QTile { int on, rows, pmin, pmax, lo, hi; };   // real key-tile range [lo, hi] (empty if hi < lo)
+
+// Geometry of one work item, recomputed by every role from the same inputs.
+struct ItemGeo {
+  int valid;          // the item exists and holds query rows
+  int n_steps;        // key steps (meta tiles first, then real tiles u_lo ..); 0: no visible key at all
+  int h, hkv, n, meta_q;
+  int q_row;          // first query row of the pair in the packed q tensor (meta_q: in q2)
+  int64_t o_row;      // first output row of the pair
+  int k_row0, Lk, nm, u_lo, lo_all;
+  QTile qt[2];
+  int first_step[2], last_step[2];   // first / last key step each query tile takes part in (-1: none)
+};
+
+__device__ __forceinline__ ItemGeo make_geo(const SwaPrefillParams& p, int idx) {
+  ItemGeo g;
+  g.valid = 0; g.n_steps = 0; g.h = g.hkv = g.n = g.meta_q = g.q_row = 0; g.o_row = 0;
+  g.k_row0 = g.Lk = g.nm = g.u_lo = g.lo_all = 0;
+#pragma unroll
+  for (int i = 0; i < 2; ++i) {
+    g.qt[i].on = g.qt[i].rows = g.qt[i].pmin = g.qt[i].lo = 0; g.qt[i].pmax = g.qt[i].hi = -1;
+    g.first_step[i] = g.last_step[i] = -1;
+  }
+  if (idx >= p.n_items) return g;
+  const int r = idx / p.H;
+  g.h = idx - r * p.H; g.hkv = g.h / (p.H / p.Hkv);
+  const int lvl = r / p.n_z;
+  g.n = r - lvl * p.n_z;
+  const int qp = p.n_qpairs - 1 - lvl;          // long pairs first
+  g.meta_q = g.n == p.N;                        // pseudo-request of the M meta queries
+  int q_row0, Lq;
+  if (g.meta_q) { q_row0 = 0; Lq = p.M; g.Lk = 0; g.k_row0 = 0; }
+  else {
+    q_row0 = __ldg(p.cu_q + g.n); Lq = __ldg(p.cu_q + g.n + 1) - q_row0;
+    g.k_row0 = __ldg(p.cu_k + g.n); g.Lk = __ldg(p.cu_k + g.n + 1) - g.k_row0;
+  }
+  if (qp * 2 * PF_BM >= Lq) return g;
+  g.valid = 1;
+  g.q_row = q_row0 + qp * 2 * PF_BM;
+  g.o_row = (g.meta_q ? 0 : (int64_t)(p.has_q2 ? p.M : 0) + q_row0) + qp * 2 * PF_BM;
+  const int shift = g.Lk - Lq;                                 // queries sit at the END of the keys
+  g.nm = (p.M + PF_BN - 1) / PF_BN;                            // meta key tiles come first
+#pragma unroll
+  for (int i = 0; i < 2; ++i) {
+    const int row0 = qp * 2 * PF_BM + i * PF_BM;
+    QTile t;
+    t.on = row0 < Lq;
+    t.rows = t.on ? min(PF_BM, Lq - row0) : 0;
+    t.pmin = shift + row0; t.pmax = t.pmin + t.rows - 1;
+    t.lo = 0; t.hi = -1;
+    if (t.on && !g.meta_q && t.pmax >= 0 && g.Lk > 0) {
+      t.lo = p.window_left < 0 ? 0 : max(0, t.pmin - p.window_left) / PF_BN;
+      t.hi = min(t.pmax, g.Lk - 1) / PF_BN;
+    }
+    g.qt[i] = t;
+  }
+  int u_lo = 0, u_hi = -1;
+  if (g.qt[0].hi >= g.qt[0].lo) { u_lo = g.qt[0].lo; u_hi = g.qt[0].hi; }
+  if (g.qt[1].hi >= g.qt[1].lo) {
+    if (u_hi < u_lo) { u_lo = g.qt[1].lo; u_hi = g.qt[1].hi; }
+    else { u_lo = min(u_lo, g.qt[1].lo); u_hi = max(u_hi, g.qt[1].hi); }
+  }
+  g.u_lo = u_lo;
+  g.n_steps = g.nm + (u_hi >= u_lo ? u_hi - u_lo + 1 : 0);
+  // lowest key position any query of this item can see (rows below it / at or past Lk are masked for
+  // every query: in the paged form they may hold recycled-page bytes and are cleared before PV)
+  g.lo_all = p.window_left < 0 ? 0 : max(0, g.qt[0].pmin - p.window_left);
+#pragma unroll
+  for (int i = 0; i < 2; ++i) {
+    const bool real = g.qt[i].hi >= g.qt[i].lo;
+    g.last_step[i] = !g.qt[i].on ? -1 : (real ? g.nm + g.qt[i].hi - u_lo : g.nm - 1);
+    g.first_step[i] = !g.qt[i].on ? -1 : (g.nm > 0 ? 0 : (real ? g.qt[i].lo - u_lo : -1));
+  }
+  return g;
+}
+
+// does query tile i take part in key step t of the item
+__device__ __forceinline__ bool geo_active(const ItemGeo& g, const QTile& q, int t) {
+  if (!q.on || t >= g.n_steps) return false;
+  if (t < g.nm) return true;
+  const int jt = g.u_lo + t - g.nm;
+  return jt >= q.lo && jt <= q.hi;
+}
+__device__ __forceinline__ bool geo_active(const ItemGeo& g, int i, int t) {   // i must be a compile-time constant
+  return geo_active(g, g.qt[i], t);
+}
 
 #ifdef HYMETA_TRACE
-__device__ long long* g_swa_trace = nullptr;   // [steps][16] clock64 stamps of one CTA; tools/trace_swa_prefill.py
-#define PF_TRACE(step, ev) do { if (g_swa_trace && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && (step) < 256) \
+__device__ long long* g_swa_trace = nullptr;   // [steps][16] clock64 stamps of CTA 0's first 256 key steps; tools/trace_swa_prefill.py
+#define PF_TRACE(step, ev) do { if (g_swa_trace && blockIdx.x == 0 && (step) < 256) \
     g_swa_trace[(step) * 16 + (ev)] = clock64(); } while (0)
 #else
 #define PF_TRACE(step, ev) do {} while (0)
-#endif   // real key-tile range [lo, hi] (empty if hi < lo)
+#endif
 
 __global__ void __launch_bounds__(PF_THREADS, 1)
 swa_prefill_kernel(const SwaPrefillParams p, const __grid_constant__ CUtensorMap tmQ,
@@ -80,72 +174,25 @@ swa_prefill_kernel(const SwaPrefillParams p, const __grid_constant__ CUtensorMap
   extern __shared__ __align__(1024) uint8_t smem[];
   const int tid = threadIdx.x, lane = tid & 31;
   const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);   // warp-uniform for the compiler
-  const int h = blockIdx.x, hkv = h / (p.H / p.Hkv);
-  const int qp = p.n_qpairs - 1 - blockIdx.y;   // long pairs first
-  const int n = blockIdx.z;
-  const bool meta_q = n == p.N;                 // pseudo-sequence of the M meta queries
-
-  int q_row0, Lq, Lk, k_row0;
-  if (meta_q) { q_row0 = 0; Lq = p.M; Lk = 0; k_row0 = 0; }
-  else {
-    q_row0 = p.cu_q[n]; Lq = p.cu_q[n + 1] - q_row0;
-    k_row0 = p.cu_k[n]; Lk = p.cu_k[n + 1] - k_row0;
-  }
-  if (qp * 2 * PF_BM >= Lq) return;
-
-  // ---- geometry shared by every role ------------------------------------------------------------
-  const int shift = Lk - Lq;                                   // queries sit at the END of the keys
-  const int nm = (p.M + PF_BN - 1) / PF_BN;                    // meta key tiles come first
-  QTile qt[2];
-#pragma unroll
-  for (int i = 0; i < 2; ++i) {
-    const int row0 = qp * 2 * PF_BM + i * PF_BM;
-    QTile t;
-    t.on = row0 < Lq;
-    t.rows = t.on ? min(PF_BM, Lq - row0) : 0;
-    t.pmin = shift + row0; t.pmax = t.pmin + t.rows - 1;
-    t.lo = 0; t.hi = -1;
-    if (t.on && !meta_q && t.pmax >= 0 && Lk > 0) {
-      t.lo = p.window_left < 0 ? 0 : max(0, t.pmin - p.window_left) / PF_BN;
-      t.hi = min(t.pmax, Lk - 1) / PF_BN;
-    }
-    qt[i] = t;
-  }
-  int u_lo = 0, u_hi = -1;
-  if (qt[0].hi >= qt[0].lo) { u_lo = qt[0].lo; u_hi = qt[0].hi; }
-  if (qt[1].hi >= qt[1].lo) {
-    if (u_hi < u_lo) { u_lo = qt[1].lo; u_hi = qt[1].hi; }
-    else { u_lo = min(u_lo, qt[1].lo); u_hi = max(u_hi, qt[1].hi); }
-  }
-  const int n_steps = nm + (u_hi >= u_lo ? u_hi - u_lo + 1 : 0);
-  // lowest key position any query of this CTA can see (rows below it / at or past Lk are masked for
-  // every query: in the paged form they may hold recycled-page bytes and are cleared before PV)
-  const int lo_all = p.window_left < 0 ? 0 : max(0, qt[0].pmin - p.window_left);
-  int last_step[2];   // last key step each query tile takes part in (-1: none)
-#pragma unroll
-  for (int i = 0; i < 2; ++i)
-    last_step[i] = !qt[i].on ? -1 : (qt[i].hi >= qt[i].lo ? nm + qt[i].hi - u_lo : nm - 1);
-  auto active = [&](int i, int t) -> bool {
-    if (!qt[i].on || t >= n_steps) return false;
-    if (t < nm) return true;
-    const int jt = u_lo + t - nm;
-    return jt >= qt[i].lo && jt <= qt[i].hi;
-  };
+  const int G = gridDim.x;
 
   const uint32_t sbase = smem_u32(smem);
   const uint32_t sQ = sbase + PF_SQ, sK = sbase + PF_SK, sV = sbase + PF_SV;
   const uint32_t bars = sbase + PF_BAR;
-  const uint32_t bar_q = bars, bar_kf = bars + 8, bar_ke = bar_kf + 8 * PF_NKS, bar_vf = bar_ke + 8 * PF_NKS,
-                 bar_ve = bar_vf + 8 * PF_NVS, bar_s = bar_ve + 8 * PF_NVS, bar_o = bar_s + 16, bar_p = bar_o + 16;
-  // bar_p: [tile][column group] -- 2 * PF_PS barriers (<= 64 bytes), ends at offset 88 + 32 + 64 = 184 < 200
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + PF_BAR + 200);
+  // mbarriers (8 bytes each): Q full/empty per tile, K/V ring full/empty, S landed per tile, PV of
+  // the item complete per tile (bar_o), O read back by the epilogue per tile (bar_of), P column
+  // groups [tile][group]; 2+2+2+2+3+3+2+2+2+8 = 28 slots = 224 bytes, tmem pointer at +248
+  const uint32_t bar_qf = bars, bar_qe = bar_qf + 16, bar_kf = bar_qe + 16, bar_ke = bar_kf + 8 * PF_NKS,
+                 bar_vf = bar_ke + 8 * PF_NKS, bar_ve = bar_vf + 8 * PF_NVS, bar_s = bar_ve + 8 * PF_NVS,
+                 bar_o = bar_s + 16, bar_of = bar_o + 16, bar_p = bar_of + 16;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + PF_BAR + 248);
 
   if (tid == 0) {
     if (sbase & 1023) asm volatile("trap;");
-    mbar_init(bar_q, 1);
+    for (int i = 0; i < 2; ++i) { mbar_init(bar_qf + 8 * i, 1); mbar_init(bar_qe + 8 * i, 1); }
     for (int s = 0; s < PF_NKS; ++s) { mbar_init(bar_kf + 8 * s, 1); mbar_init(bar_ke + 8 * s, 1); }
     for (int s = 0; s < PF_NVS; ++s) { mbar_init(bar_vf + 8 * s, 1); mbar_init(bar_ve + 8 * s, 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(bar_s + 8 * i, 1); mbar_init(bar_o + 8 * i, 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(bar_s + 8 * i, 1); mbar_init(bar_o + 8 * i, 1); mbar_init(bar_of + 8 * i, 128); }
     for (int i = 0; i < 2 * PF_PS; ++i) mbar_init(bar_p + 8 * i, 128);
     fence_mbar_init();
   }
@@ -158,69 +205,82 @@ swa_prefill_kernel(const SwaPrefillParams p, const __grid_constant__ CUtensorMap
 
   if (warp == 8) {
     // ================================================================== TMA producer
-#if PF_OPT_REGS
     setmaxnreg_dec<PF_REG_LO>();
-#endif
     if (elect_one_sync()) {
-      const CUtensorMap* tq = meta_q ? &tmQ2 : &tmQ;
-      tma_prefetch_desc(tq); tma_prefetch_desc(&tmK); tma_prefetch_desc(&tmV);
-      const int nq = qt[1].on ? 2 : 1;
-      mbar_expect_tx(bar_q, nq * PF_TILE);
-      for (int i = 0; i < nq; ++i) {
-        const int row = q_row0 + qp * 2 * PF_BM + i * PF_BM;
-        tma_load_3d(sQ + i * PF_TILE, tq, bar_q, 0, h, row);
-        tma_load_3d(sQ + i * PF_TILE + 16384, tq, bar_q, 64, h, row);
-      }
-      const int32_t* bt = p.paged ? p.block_tables + (int64_t)n * p.bt_stride : nullptr;
-      // one K or V tile: a 3-D box of the packed tensor / meta rows, or -- paged -- box_rows-row
-      // boxes of the 4-D cache map, each resolved through the block table (a box never straddles a
-      // page: box_rows divides block_size and logical positions are box aligned)
-      auto load_tile = [&](uint32_t dst, uint32_t bar, const CUtensorMap* m3, const CUtensorMap* m4, int t) {
-        mbar_expect_tx(bar, PF_TILE);
-        if (t < nm || !p.paged) {
-          const int row = t < nm ? t * PF_BN : k_row0 + (u_lo + t - nm) * PF_BN;
-          tma_load_3d(dst, m3, bar, 0, hkv, row);
-          tma_load_3d(dst + 16384, m3, bar, 64, hkv, row);
-        } else {
-          const int pos0 = (u_lo + t - nm) * PF_BN, rb = p.box_rows;
-          for (int sub = 0; sub < PF_BN / rb; ++sub) {
-            // boxes wholly outside [lo_all, Lk) are redirected to the nearest box that holds a
-            // visible position (their rows are masked and their V rows cleared by the softmax warps)
-            const int pos = min(max(pos0 + sub * rb, lo_all / rb * rb), Lk - 1);
-            const int blk = bt[pos / p.block_size];
-            const int row = (pos % p.block_size) / rb * rb;
-            const uint32_t o = sub * rb * 128;
-            tma_load_4d(dst + o, m4, bar, 0, hkv, row, blk);
-            tma_load_4d(dst + 16384 + o, m4, bar, 64, hkv, row, blk);
+      tma_prefetch_desc(&tmQ); tma_prefetch_desc(&tmK); tma_prefetch_desc(&tmV);
+      int gt = 0;               // key steps issued so far (ring position of the item's first K / V tile)
+      int qc[2] = {0, 0};       // Q loads issued per tile
+      for (int it = blockIdx.x; it < p.n_items; it += G) {
+        const ItemGeo g = make_geo(p, it);
+        if (!g.valid || g.n_steps == 0) continue;
+        const CUtensorMap* tq = g.meta_q ? &tmQ2 : &tmQ;
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+          if (g.last_step[i] < 0) continue;
+          if (qc[i] > 0) mbar_wait(bar_qe + 8 * i, (qc[i] - 1) & 1);   // last S of the previous use has read it
+          mbar_expect_tx(bar_qf + 8 * i, PF_TILE);
+          const int row = g.q_row + i * PF_BM;
+          tma_load_3d(sQ + i * PF_TILE, tq, bar_qf + 8 * i, 0, g.h, row);
+          tma_load_3d(sQ + i * PF_TILE + 16384, tq, bar_qf + 8 * i, 64, g.h, row);
+          ++qc[i];
+        }
+        const int32_t* bt = p.paged ? p.block_tables + (int64_t)g.n * p.bt_stride : nullptr;
+        // one K or V tile: a 3-D box of the packed tensor / meta rows, or -- paged -- box_rows-row
+        // boxes of the 4-D cache map, each resolved through the block table (a box never straddles a
+        // page: box_rows divides block_size and logical positions are box aligned)
+        auto load_tile = [&](uint32_t dst, uint32_t bar, const CUtensorMap* m3, const CUtensorMap* m4, int t) {
+          mbar_expect_tx(bar, PF_TILE);
+          if (t < g.nm || !p.paged) {
+            const int row = t < g.nm ? t * PF_BN : g.k_row0 + (g.u_lo + t - g.nm) * PF_BN;
+            tma_load_3d(dst, m3, bar, 0, g.hkv, row);
+            tma_load_3d(dst + 16384, m3, bar, 64, g.hkv, row);
+          } else {
+            const int pos0 = (g.u_lo + t - g.nm) * PF_BN, rb = p.box_rows;
+            for (int sub = 0; sub < PF_BN / rb; ++sub) {
+              // boxes wholly outside [lo_all, Lk) are redirected to the nearest box that holds a
+              // visible position (their rows are masked and their V rows cleared by the softmax warps)
+              const int pos = min(max(pos0 + sub * rb, g.lo_all / rb * rb), g.Lk - 1);
+              const int blk = bt[pos / p.block_size];
+              const int row = (pos % p.block_size) / rb * rb;
+              const uint32_t o = sub * rb * 128;
+              tma_load_4d(dst + o, m4, bar, 0, g.hkv, row, blk);
+              tma_load_4d(dst + 16384 + o, m4, bar, 64, g.hkv, row, blk);
+            }
+          }
+        };
+        for (int t = 0; t < g.n_steps; ++t) {
+          const int gi = gt + t;
+          {
+            const int st = gi % PF_NKS;
+            if (gi >= PF_NKS) mbar_wait(bar_ke + 8 * st, ((gi / PF_NKS) - 1) & 1);
+            load_tile(sK + st * PF_TILE, bar_kf + 8 * st, t < g.nm ? &tmMK : &tmK, &tmK, t);
+            PF_TRACE(gi, 12);
+          }
+          {
+            const int st = gi % PF_NVS;
+            if (gi >= PF_NVS) mbar_wait(bar_ve + 8 * st, ((gi / PF_NVS) - 1) & 1);
+            load_tile(sV + st * PF_TILE, bar_vf + 8 * st, t < g.nm ? &tmMV : &tmV, &tmV, t);
+            PF_TRACE(gi, 13);
           }
         }
-      };
-      for (int t = 0; t < n_steps; ++t) {
-        {
-          const int st = t % PF_NKS;
-          if (t >= PF_NKS) mbar_wait(bar_ke + 8 * st, ((t / PF_NKS) - 1) & 1);
-          load_tile(sK + st * PF_TILE, bar_kf + 8 * st, t < nm ? &tmMK : &tmK, &tmK, t);
-          PF_TRACE(t, 12);
-        }
-        {
-          const int st = t % PF_NVS;
-          if (t >= PF_NVS) mbar_wait(bar_ve + 8 * st, ((t / PF_NVS) - 1) & 1);
-          load_tile(sV + st * PF_TILE, bar_vf + 8 * st, t < nm ? &tmMV : &tmV, &tmV, t);
-          PF_TRACE(t, 13);
-        }
+        gt += g.n_steps;
       }
     }
     __syncwarp();
   } else if (warp == 9) {
     // ================================================================== MMA issuer
-#if PF_OPT_REGS
     setmaxnreg_dec<PF_REG_LO>();
-#endif
     if (elect_one_sync()) {
       const uint32_t idesc_s = umma_idesc_bf16(PF_BM, PF_BN, 0, 0);
       const uint32_t idesc_o = umma_idesc_bf16(PF_BM, kD, 0, 1);
-      auto issue_s = [&](int i, int t) {   // S_i = Q_i K(t)^T
-        const uint32_t qb = sQ + i * PF_TILE, kb = sK + (t % PF_NKS) * PF_TILE;
+      int cnt[2] = {0, 0};      // softmax hand-offs consumed per tile (parity of bar_p)
+      int qc[2] = {0, 0};       // Q tiles consumed per tile (parity of bar_qf)
+      int oc[2] = {0, 0};       // items whose O_i was produced (parity of bar_of)
+      // S_i = Q_i K^T for key step t of item g, whose first key step is ring position gt0
+      auto issue_s = [&](const ItemGeo& g, int i, int t, int gt0) {
+        if (t == g.first_step[i]) { mbar_wait(bar_qf + 8 * i, qc[i] & 1); ++qc[i]; }
+        tc_fence_after();
+        const uint32_t qb = sQ + i * PF_TILE, kb = sK + ((gt0 + t) % PF_NKS) * PF_TILE;
 #pragma unroll
         for (int ks = 0; ks < 8; ++ks) {
           const uint64_t da = umma_desc_sw128(qb + (ks >> 2) * 16384 + (ks & 3) * 32, 16, 1024);
@@ -228,82 +288,109 @@ swa_prefill_kernel(const SwaPrefillParams p, const __grid_constant__ CUtensorMap
           umma_bf16(tmem + i * 128, da, db, idesc_s, ks > 0);
         }
         umma_commit(bar_s + 8 * i);
+        if (t == g.last_step[i]) umma_commit(bar_qe + 8 * i);   // Q_i is free once this S has completed
       };
-      auto issue_pv = [&](int i, int t, bool acc, int g) {   // O_i (+)= P_i V(t), column group g
-        const uint32_t vb = sV + (t % PF_NVS) * PF_TILE;
+      auto issue_pv = [&](int i, int gi, bool acc, int grp) {   // O_i (+)= P_i V, column group grp
+        const uint32_t vb = sV + (gi % PF_NVS) * PF_TILE;
 #pragma unroll
-        for (int ks = g * (8 / PF_PS); ks < (g + 1) * (8 / PF_PS); ++ks) {
+        for (int ks = grp * (8 / PF_PS); ks < (grp + 1) * (8 / PF_PS); ++ks) {
           const uint64_t db = umma_desc_sw128(vb + ks * 2048, 16384, 1024);
           umma_bf16_ts(tmem + 256 + i * 128, tmem + i * 128 + ks * 8, db, idesc_o, (acc || ks > 0) ? 1u : 0u);
         }
       };
-      int cnt[2] = {0, 0};
-      if (n_steps > 0) {
-        mbar_wait(bar_q, 0);
+      auto skip = [&](const ItemGeo& g) { return !g.valid || g.n_steps == 0; };
+      int it = blockIdx.x;
+      ItemGeo g = make_geo(p, it);
+      while (it < p.n_items && skip(g)) { it += G; g = make_geo(p, it); }
+      bool have = it < p.n_items;
+      int gt = 0;
+      if (have) {   // first item: its step-0 S has no previous item to ride on
         mbar_wait(bar_kf, 0);
-        tc_fence_after();
-        for (int i = 0; i < 2; ++i) if (active(i, 0)) issue_s(i, 0);
+#pragma unroll
+        for (int i = 0; i < 2; ++i) if (geo_active(g, i, 0)) issue_s(g, i, 0, 0);
         umma_commit(bar_ke);
       }
-      for (int t = 0; t < n_steps; ++t) {
-        bool v_ready = false, k_ready = false;
-        for (int i = 0; i < 2; ++i) {
-          if (active(i, t)) {
+      while (have) {
+        int nit = it + G;
+        ItemGeo ng = make_geo(p, nit);
+        while (nit < p.n_items && skip(ng)) { nit += G; ng = make_geo(p, nit); }
+        const bool have_next = nit < p.n_items;
+        int ci[2] = {0, 0};   // PVs issued for this item
+        for (int t = 0; t < g.n_steps; ++t) {
+          const int gi = gt + t;
+          const bool last = t == g.n_steps - 1;
+          bool v_ready = false, k_ready = false;
 #pragma unroll
-            for (int g = 0; g < PF_PS; ++g) {
-              mbar_wait(bar_p + 8 * (i * PF_PS + g), cnt[i] & 1);
-              if (g == 0) PF_TRACE(t, 8 + 2 * i);
-              if (!v_ready) { mbar_wait(bar_vf + 8 * (t % PF_NVS), (t / PF_NVS) & 1); v_ready = true; }
-              tc_fence_after();
-              issue_pv(i, t, cnt[i] > 0, g);
+          for (int i = 0; i < 2; ++i) {
+            if (geo_active(g, i, t)) {
+              // O_i of the previous item has been read back by the epilogue
+              if (ci[i] == 0 && oc[i] > 0) mbar_wait(bar_of + 8 * i, (oc[i] - 1) & 1);
+#pragma unroll
+              for (int grp = 0; grp < PF_PS; ++grp) {
+                mbar_wait(bar_p + 8 * (i * PF_PS + grp), cnt[i] & 1);
+                if (grp == 0) PF_TRACE(gi, 8 + 2 * i);
+                if (!v_ready) { mbar_wait(bar_vf + 8 * (gi % PF_NVS), (gi / PF_NVS) & 1); v_ready = true; }
+                tc_fence_after();
+                issue_pv(i, gi, ci[i] > 0, grp);
+              }
+              ++cnt[i]; ++ci[i];
+              if (t == g.last_step[i]) { umma_commit(bar_o + 8 * i); ++oc[i]; }   // last key tile of this query tile
             }
-            ++cnt[i];
-            if (t == last_step[i]) umma_commit(bar_o + 8 * i);   // last key tile of this query tile
+            // the next S of this tile: step t+1 of this item, or step 0 of the next item
+            const bool s_here = !last && geo_active(g, i, t + 1);
+            const bool s_next = last && have_next && geo_active(ng, i, 0);
+            if (s_here || s_next) {
+              if (!k_ready) { mbar_wait(bar_kf + 8 * ((gi + 1) % PF_NKS), ((gi + 1) / PF_NKS) & 1); k_ready = true; }
+              if (s_here) issue_s(g, i, t + 1, gt); else issue_s(ng, i, 0, gt + g.n_steps);
+            }
+            PF_TRACE(gi, 9 + 2 * i);
           }
-          if (active(i, t + 1)) {
-            if (!k_ready) { mbar_wait(bar_kf + 8 * ((t + 1) % PF_NKS), ((t + 1) / PF_NKS) & 1); k_ready = true; }
-            tc_fence_after();
-            issue_s(i, t + 1);
-          }
-          PF_TRACE(t, 9 + 2 * i);
+          umma_commit(bar_ve + 8 * (gi % PF_NVS));
+          if (!last || have_next) umma_commit(bar_ke + 8 * ((gi + 1) % PF_NKS));
         }
-        umma_commit(bar_ve + 8 * (t % PF_NVS));
-        if (t + 1 < n_steps) umma_commit(bar_ke + 8 * ((t + 1) % PF_NKS));
+        gt += g.n_steps;
+        it = nit; g = ng; have = have_next;
       }
     }
     __syncwarp();
   } else if (warp < 8) {
     // ================================================================== softmax warps
-#if PF_OPT_REGS
     setmaxnreg_inc<PF_REG_HI>();
-#endif
     const int i = warp >> 2;                     // query tile
     const int r = (warp & 3) * 32 + lane;        // row inside the tile == TMEM lane
-    const QTile T = qt[i];
     const uint32_t lane_off = (uint32_t)((warp & 3) * 32) << 16;
     const uint32_t tS = tmem + i * 128 + lane_off, tO = tmem + 256 + i * 128 + lane_off;
-    const int pq = T.pmin + r;                   // key position of my query
-    float m_ref = -INFINITY, l_run = 0.f;        // running reference max (scaled, log2 domain) / sum
-    int cnt = 0;
-    if (T.on) {
-      for (int t = 0; t < n_steps; ++t) {
-        if (!active(i, t)) continue;
+    int cnt = 0;      // S tiles consumed (parity of bar_s / bar_p)
+    int oc = 0;       // items with an O (parity of bar_o)
+    int gt = 0;       // ring position of the item's first key step
+    for (int it = blockIdx.x; it < p.n_items; it += G) {
+      const ItemGeo g = make_geo(p, it);
+      if (!g.valid) continue;
+      const QTile T = i ? g.qt[1] : g.qt[0];
+      if (!T.on) { gt += g.n_steps; continue; }
+      const int nm = g.nm, Lk = g.Lk;
+      const int pq = T.pmin + r;                   // key position of my query
+      float m_ref = -INFINITY, l_run = 0.f;        // running reference max (scaled, log2 domain) / sum
+      int ci = 0;                                  // key steps of this item done
+      for (int t = 0; t < g.n_steps; ++t) {
+        if (!geo_active(g, T, t)) continue;
+        const int gi = gt + t;
         mbar_wait(bar_s + 8 * i, cnt & 1);
         tc_fence_after();
-        if ((tid & 127) == 0) PF_TRACE(t, 4 * i);
+        if ((tid & 127) == 0) PF_TRACE(gi, 4 * i);
         uint32_t sr[128];
         tmem_ld32_nowait(tS + 0, *reinterpret_cast<uint32_t(*)[32]>(&sr[0]));
         tmem_ld32_nowait(tS + 32, *reinterpret_cast<uint32_t(*)[32]>(&sr[32]));
         tmem_ld32_nowait(tS + 64, *reinterpret_cast<uint32_t(*)[32]>(&sr[64]));
         tmem_ld32_nowait(tS + 96, *reinterpret_cast<uint32_t(*)[32]>(&sr[96]));
         tmem_wait_ld();
-        if ((tid & 127) == 0) PF_TRACE(t, 4 * i + 1);
+        if ((tid & 127) == 0) PF_TRACE(gi, 4 * i + 1);
         // ---- mask (tile-uniform decision)
         bool need_mask;
         int kp0, lo, hi;   // visible key positions of this row: [lo, hi]
         if (t < nm) { kp0 = t * PF_BN; need_mask = kp0 + PF_BN > p.M; lo = 0; hi = p.M - 1; }
         else {
-          kp0 = (u_lo + t - nm) * PF_BN;
+          kp0 = (g.u_lo + t - nm) * PF_BN;
           need_mask = (kp0 + PF_BN - 1 > T.pmin) || (kp0 + PF_BN > Lk) ||
                       (p.window_left >= 0 && kp0 < T.pmax - p.window_left);
           hi = min(pq, Lk - 1); lo = p.window_left < 0 ? 0 : pq - p.window_left;
@@ -331,7 +418,7 @@ swa_prefill_kernel(const SwaPrefillParams p, const __grid_constant__ CUtensorMap
             m_ref = mx;
             l_run *= alpha;
           }
-          if (cnt > 0) {   // O_i holds PV(0..cnt-1): all complete, since S_i(t) completed after them
+          if (ci > 0) {   // O_i holds PV(0..ci-1): all complete, since S_i(t) completed after them
 #pragma unroll
             for (int c = 0; c < 4; ++c) {
               uint32_t o[32];
@@ -343,16 +430,16 @@ swa_prefill_kernel(const SwaPrefillParams p, const __grid_constant__ CUtensorMap
             }
           }
         }
-        if ((tid & 127) == 0) PF_TRACE(t, 4 * i + 2);
+        if ((tid & 127) == 0) PF_TRACE(gi, 4 * i + 2);
         const float msub = (m_ref == -INFINITY) ? 0.f : m_ref;
-        if (p.paged && t >= nm && (kp0 + PF_BN > Lk || kp0 < lo_all)) {
+        if (p.paged && t >= nm && (kp0 + PF_BN > Lk || kp0 < g.lo_all)) {
           // paged boundary tile: key rows outside [lo_all, Lk) are masked for every query (P = 0)
           // but may hold recycled-page bytes (NaN patterns), and 0 * NaN would poison O -- clear
           // those V rows in the landed stage before PV is issued (generic -> async proxy fence)
-          const int st = t % PF_NVS;
-          mbar_wait(bar_vf + 8 * st, (t / PF_NVS) & 1);
+          const int st = gi % PF_NVS;
+          mbar_wait(bar_vf + 8 * st, (gi / PF_NVS) & 1);
           const int kp = kp0 + r;
-          if (kp >= Lk || kp < lo_all) {
+          if (kp >= Lk || kp < g.lo_all) {
             uint8_t* row = smem + PF_SV + st * PF_TILE + r * 128;
 #pragma unroll
             for (int c = 0; c < 8; ++c) {
@@ -381,39 +468,45 @@ swa_prefill_kernel(const SwaPrefillParams p, const __grid_constant__ CUtensorMap
           }
         }
         l_run += (rs0 + rs1) + (rs2 + rs3);
-        if ((tid & 127) == 0) PF_TRACE(t, 4 * i + 3);
-        ++cnt;
+        if ((tid & 127) == 0) PF_TRACE(gi, 4 * i + 3);
+        ++cnt; ++ci;
       }
-      // ---- epilogue: normalise, bf16, one 256-byte row per thread
-      if (cnt > 0) { mbar_wait(bar_o + 8 * i, 0); tc_fence_after(); }
+      // ---- epilogue: read O back (and release it to the MMA warp), normalise, bf16, one 256-byte
+      // row per thread
+      uint32_t o[128];
+      if (ci > 0) {
+        mbar_wait(bar_o + 8 * i, oc & 1);
+        tc_fence_after();
+        tmem_ld32_nowait(tO + 0, *reinterpret_cast<uint32_t(*)[32]>(&o[0]));
+        tmem_ld32_nowait(tO + 32, *reinterpret_cast<uint32_t(*)[32]>(&o[32]));
+        tmem_ld32_nowait(tO + 64, *reinterpret_cast<uint32_t(*)[32]>(&o[64]));
+        tmem_ld32_nowait(tO + 96, *reinterpret_cast<uint32_t(*)[32]>(&o[96]));
+        tmem_wait_ld();
+        tc_fence_before();
+        mbar_arrive(bar_of + 8 * i);
+        ++oc;
+      } else {
+#pragma unroll
+        for (int j = 0; j < 128; ++j) o[j] = 0u;
+      }
       const float inv = l_run > 0.f ? 1.f / l_run : 0.f;
-      const int64_t orow = (meta_q ? 0 : (int64_t)(p.has_q2 ? p.M : 0) + q_row0) + qp * 2 * PF_BM + i * PF_BM + r;
-      __nv_bfloat16* dst = p.out + orow * p.o_st + (int64_t)h * p.o_sh;
+      if (r < T.rows) {
+        __nv_bfloat16* dst = p.out + (g.o_row + i * PF_BM + r) * p.o_st + (int64_t)g.h * p.o_sh;
 #pragma unroll
-      for (int c = 0; c < 4; ++c) {
-        uint32_t o[32];
-        if (cnt > 0) { tmem_ld32_nowait(tO + 32 * c, o); tmem_wait_ld(); }
-        else {
-#pragma unroll
-          for (int j = 0; j < 32; ++j) o[j] = 0u;
-        }
-        if (r < T.rows) {
-#pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            uint4 v;
-            v.x = pack_bf16(__uint_as_float(o[8 * j + 0]) * inv, __uint_as_float(o[8 * j + 1]) * inv);
-            v.y = pack_bf16(__uint_as_float(o[8 * j + 2]) * inv, __uint_as_float(o[8 * j + 3]) * inv);
-            v.z = pack_bf16(__uint_as_float(o[8 * j + 4]) * inv, __uint_as_float(o[8 * j + 5]) * inv);
-            v.w = pack_bf16(__uint_as_float(o[8 * j + 6]) * inv, __uint_as_float(o[8 * j + 7]) * inv);
-            stg_v4(dst + 32 * c + 8 * j, v);
-          }
+        for (int j = 0; j < 16; ++j) {
+          uint4 v;
+          v.x = pack_bf16(__uint_as_float(o[8 * j + 0]) * inv, __uint_as_float(o[8 * j + 1]) * inv);
+          v.y = pack_bf16(__uint_as_float(o[8 * j + 2]) * inv, __uint_as_float(o[8 * j + 3]) * inv);
+          v.z = pack_bf16(__uint_as_float(o[8 * j + 4]) * inv, __uint_as_float(o[8 * j + 5]) * inv);
+          v.w = pack_bf16(__uint_as_float(o[8 * j + 6]) * inv, __uint_as_float(o[8 * j + 7]) * inv);
+          stg_v4(dst + 8 * j, v);
         }
       }
+      gt += g.n_steps;
     }
+  } else {
+    setmaxnreg_dec<PF_REG_LO>();   // warps 10-11 only complete the third warpgroup
   }
-#if PF_OPT_REGS
-  else setmaxnreg_dec<PF_REG_LO>();   // warps 10-11 only complete the third warpgroup
-#endif
   tc_fence_before();
   __syncthreads();
   if (warp == 9) tmem_dealloc<512>(tmem);
@@ -447,7 +540,6 @@ extern "C" int hymeta_swa_meta_prefill_varlen(
   const bool real = N > 0 && Tq > 0;
   if (real && (!q1 || !k1 || !v1 || !cu_q || !cu_k)) return HYMETA_ERR_INVALID_ARG;
   if (!real && !q2) return HYMETA_OK;
-  if (N > 65534 || H > 65535) return HYMETA_ERR_UNSUPPORTED;
 
   CUtensorMap tmQ, tmK, tmV, tmQ2, tmMK, tmMV;
   memset(&tmQ, 0, sizeof(tmQ)); tmK = tmV = tmQ2 = tmMK = tmMV = tmQ;
@@ -502,7 +594,11 @@ extern "C" int hymeta_swa_meta_prefill_varlen(
 
   static DynSmemAttr attr;
   attr.ensure(swa_prefill_kernel, PF_SMEM);
-  dim3 grid(H, p.n_qpairs, p.N + (q2 ? 1 : 0));
+  p.n_z = p.N + (q2 ? 1 : 0);
+  const int64_t n_items = (int64_t)H * p.n_qpairs * p.n_z;
+  if (n_items > 0x7fffffff) return HYMETA_ERR_UNSUPPORTED;
+  p.n_items = (int)n_items;
+  dim3 grid((unsigned)std::min<int64_t>(n_items, sm_count()));
   swa_prefill_kernel<<<grid, PF_THREADS, PF_SMEM, (cudaStream_t)stream>>>(p, tmQ, tmK, tmV, tmQ2, tmMK, tmMV);
   count_launch();
   return check_launch();
