@@ -39,12 +39,22 @@ namespace hymeta {
 constexpr int PF_BM = 128;    // query rows per tile (two tiles per item)
 constexpr int PF_BN = 128;    // keys per tile
 constexpr int PF_NKS = 2;     // K ring stages
-constexpr int PF_NVS = 3;     // V ring stages
+#ifndef PF_OPT_EPI
+#define PF_OPT_EPI 1      // 1: output rows staged per warp through smem and written as full 128-byte lines; 0: one 256-byte row per thread
+#endif
+#ifndef PF_OPT_MASK
+#define PF_OPT_MASK 1     // 1: boundary tiles masked from a per-row 128-bit visibility mask; 0: two compares per score
+#endif
+#ifndef PF_NVS_
+#define PF_NVS_ (PF_OPT_EPI ? 2 : 3)
+#endif
+constexpr int PF_NVS = PF_NVS_;   // V ring stages (the third stage's 32 KB is the output staging area when PF_OPT_EPI)
 constexpr int PF_TILE = 32768;                          // one [128][128] bf16 tile: 2 halves x [128][64]
 constexpr int PF_SQ = 0;                                // Q0, Q1
 constexpr int PF_SK = 2 * PF_TILE;
 constexpr int PF_SV = PF_SK + PF_NKS * PF_TILE;
-constexpr int PF_BAR = PF_SV + PF_NVS * PF_TILE;        // mbarriers + tmem ptr
+constexpr int PF_SO = PF_SV + PF_NVS * PF_TILE;         // output staging: 8 warps x 4 KB
+constexpr int PF_BAR = PF_SO + (PF_OPT_EPI ? 8 * 4096 : 0);   // mbarriers + tmem ptr
 constexpr int PF_SMEM = PF_BAR + 256;
 #ifndef PF_OPT_PSPLIT
 #define PF_OPT_PSPLIT 2   // P handed to the MMA warp in this many column groups (1, 2 or 4), each with its own mbarrier
@@ -214,16 +224,16 @@ swa_prefill_kernel(const SwaPrefillParams p, const __grid_constant__ CUtensorMap
         const ItemGeo g = make_geo(p, it);
         if (!g.valid || g.n_steps == 0) continue;
         const CUtensorMap* tq = g.meta_q ? &tmQ2 : &tmQ;
-#pragma unroll
-        for (int i = 0; i < 2; ++i) {
-          if (g.last_step[i] < 0) continue;
+        // Q_i goes out right before the K tile of the first step that needs it (tile 1 of the
+        // previous item is still using its Q while this item's Q_0 / K / V are already in flight)
+        auto load_q = [&](int i) {
           if (qc[i] > 0) mbar_wait(bar_qe + 8 * i, (qc[i] - 1) & 1);   // last S of the previous use has read it
           mbar_expect_tx(bar_qf + 8 * i, PF_TILE);
           const int row = g.q_row + i * PF_BM;
           tma_load_3d(sQ + i * PF_TILE, tq, bar_qf + 8 * i, 0, g.h, row);
           tma_load_3d(sQ + i * PF_TILE + 16384, tq, bar_qf + 8 * i, 64, g.h, row);
           ++qc[i];
-        }
+        };
         const int32_t* bt = p.paged ? p.block_tables + (int64_t)g.n * p.bt_stride : nullptr;
         // one K or V tile: a 3-D box of the packed tensor / meta rows, or -- paged -- box_rows-row
         // boxes of the 4-D cache map, each resolved through the block table (a box never straddles a
@@ -250,6 +260,8 @@ swa_prefill_kernel(const SwaPrefillParams p, const __grid_constant__ CUtensorMap
         };
         for (int t = 0; t < g.n_steps; ++t) {
           const int gi = gt + t;
+          if (t == g.first_step[0]) load_q(0);
+          if (t == g.first_step[1]) load_q(1);
           {
             const int st = gi % PF_NKS;
             if (gi >= PF_NKS) mbar_wait(bar_ke + 8 * st, ((gi / PF_NKS) - 1) & 1);
@@ -396,11 +408,27 @@ swa_prefill_kernel(const SwaPrefillParams p, const __grid_constant__ CUtensorMap
           hi = min(pq, Lk - 1); lo = p.window_left < 0 ? 0 : pq - p.window_left;
         }
         if (need_mask) {
+#if PF_OPT_MASK
+          // visible columns of my row are [lo - kp0, hi - kp0]: one 32-bit visibility word per 32
+          // columns, tested bit by bit (one predicate + select per score instead of two compares)
+          const int c_lo = lo - kp0, c_hi = hi - kp0;
+#pragma unroll
+          for (int w = 0; w < 4; ++w) {
+            const int a = min(max(c_lo - 32 * w, 0), 32), b = min(max(c_hi + 1 - 32 * w, 0), 32);   // [a, b)
+            const uint32_t below_b = b >= 32 ? 0xffffffffu : (1u << b) - 1u;
+            const uint32_t from_a = a >= 32 ? 0u : 0xffffffffu << a;
+            const uint32_t vis = below_b & from_a;
+#pragma unroll
+            for (int c = 0; c < 32; ++c)
+              if (!(vis & (1u << c))) sr[32 * w + c] = 0xff800000u;   // -inf
+          }
+#else
 #pragma unroll
           for (int c = 0; c < 128; ++c) {
             const int kp = kp0 + c;
             if (kp < lo || kp > hi) sr[c] = 0xff800000u;   // -inf
           }
+#endif
         }
         float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
 #pragma unroll
@@ -490,6 +518,38 @@ swa_prefill_kernel(const SwaPrefillParams p, const __grid_constant__ CUtensorMap
         for (int j = 0; j < 128; ++j) o[j] = 0u;
       }
       const float inv = l_run > 0.f ? 1.f / l_run : 0.f;
+#if PF_OPT_EPI
+      {
+        // Per warp: 32 rows x 64 columns (4 KB, 16-byte chunks XOR-swizzled by row) staged in smem,
+        // read back so that 8 lanes cover one 128-byte line: 4 full lines per store instruction
+        // instead of 32 scattered 16-byte pieces (which kept the LSU -- and with it every mbarrier
+        // poll of the other roles -- busy for thousands of cycles per item).
+        uint8_t* stg = smem + PF_SO + warp * 4096;
+        const int row_base = (warp & 3) * 32;
+        __nv_bfloat16* dst0 = p.out + (g.o_row + i * PF_BM + row_base) * p.o_st + (int64_t)g.h * p.o_sh;
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
+#pragma unroll
+          for (int c = 0; c < 8; ++c) {
+            const int j = 8 * half + c;
+            uint4 v;
+            v.x = pack_bf16(__uint_as_float(o[8 * j + 0]) * inv, __uint_as_float(o[8 * j + 1]) * inv);
+            v.y = pack_bf16(__uint_as_float(o[8 * j + 2]) * inv, __uint_as_float(o[8 * j + 3]) * inv);
+            v.z = pack_bf16(__uint_as_float(o[8 * j + 4]) * inv, __uint_as_float(o[8 * j + 5]) * inv);
+            v.w = pack_bf16(__uint_as_float(o[8 * j + 6]) * inv, __uint_as_float(o[8 * j + 7]) * inv);
+            *reinterpret_cast<uint4*>(stg + lane * 128 + ((c ^ (lane & 7)) << 4)) = v;
+          }
+          __syncwarp();
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const int row = 4 * j + (lane >> 3), c = lane & 7;
+            const uint4 v = *reinterpret_cast<const uint4*>(stg + row * 128 + ((c ^ (row & 7)) << 4));
+            if (row_base + row < T.rows) stg_v4(dst0 + row * p.o_st + 64 * half + 8 * c, v);
+          }
+          __syncwarp();
+        }
+      }
+#else
       if (r < T.rows) {
         __nv_bfloat16* dst = p.out + (g.o_row + i * PF_BM + r) * p.o_st + (int64_t)g.h * p.o_sh;
 #pragma unroll
@@ -502,6 +562,7 @@ swa_prefill_kernel(const SwaPrefillParams p, const __grid_constant__ CUtensorMap
           stg_v4(dst + 8 * j, v);
         }
       }
+#endif
       gt += g.n_steps;
     }
   } else {
