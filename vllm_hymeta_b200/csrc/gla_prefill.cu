@@ -27,7 +27,13 @@
 namespace hymeta {
 
 constexpr int GC = 16;                          // tokens per step
-constexpr int GP_KS = 4;                        // gate ring stages
+#ifndef GP_KS_
+#define GP_KS_ 3
+#endif
+#ifndef GP_EXP
+#define GP_EXP 0   // timing / bisection experiments of tools/trace_gla_prefill.py (bit mask); 0 in the product build
+#endif
+constexpr int GP_KS = GP_KS_;                   // gate ring stages
 constexpr int GP_SQ = 0;                        // q~  2 x [2][128][64] bf16            64 KB
 constexpr int GP_SS = 65536;                    // X   2 x [2][128 dk][64 dv] bf16      64 KB
 constexpr int GP_ST = 131072;                   // gate ring
@@ -40,7 +46,8 @@ constexpr int GP_RAW = GP_ST + GP_KS * GP_STAGE;   // raw g / k ring of the gate
 constexpr int GP_RS = 2;                        //   stages
 constexpr int GP_RAW_K = 8192;                  //   g [16][64 thr] 4|8 B (8 KB), k [16][64 thr] 4 B (4 KB)
 constexpr int GP_RAW_STAGE = 12288;
-constexpr int GP_BAR = GP_RAW + GP_RS * GP_RAW_STAGE;
+constexpr int GP_OST = GP_RAW + GP_RS * GP_RAW_STAGE;   // output staging: 8 q-tile warps x 2 KB
+constexpr int GP_BAR = GP_OST + ((GP_EXP & 128) ? 0 : 8 * 2048);
 constexpr int GP_SMEM = GP_BAR + 256;
 constexpr int GP_THREADS = 512;
 constexpr int GP_WS_ELEMS = kD * kD + kD;      // per (chain, segment): state [128][128] + decay [128]
@@ -72,9 +79,6 @@ __device__ long long* g_gla_trace = nullptr;   // [steps][16] clock64 stamps of 
     g_gla_trace[(step) * 16 + (ev)] = clock64(); } while (0)
 #else
 #define GP_TRACE(step, ev) do {} while (0)
-#endif
-#ifndef GP_EXP
-#define GP_EXP 0   // timing experiments of tools/trace_gla_prefill.py (bit mask); 0 in the product build
 #endif
 
 template <bool GF32, bool GN>
@@ -185,22 +189,43 @@ gla_prefill_kernel(const GlaPrefillParams p, const __grid_constant__ CUtensorMap
       // sequence's tokens: they neither decay nor contribute (k~ = 0)
       float2 b[GC];
       uint32_t kk[GC];
+      // every load is issued before the first use (no branch between them: the ragged tail is
+      // handled by selects, so the 32 shared-memory reads overlap instead of serialising)
+      if (GP_EXP & 256) {
+        float bx = 0.f, by = 0.f;
+#pragma unroll
+        for (int t = 0; t < GC; ++t) {
+          float2 g;
+          if (GF32) g = *reinterpret_cast<const float2*>(rawp + so + t * 512);
+          else {
+            const uint32_t u = *reinterpret_cast<const uint32_t*>(rawp + so + t * 256);
+            g = make_float2(bf16_lo(u), bf16_hi(u));
+          }
+          kk[t] = *reinterpret_cast<const uint32_t*>(rawkp + so + t * 256);
+          if (t < clen) { bx = fmaf(g.x, 1.4426950408889634f, bx); by = fmaf(g.y, 1.4426950408889634f, by); }
+          else kk[t] = 0;
+          b[t] = make_float2(bx, by);
+        }
+      } else {
+#pragma unroll
+      for (int t = 0; t < GC; ++t) {
+        if (GF32) b[t] = *reinterpret_cast<const float2*>(rawp + so + t * 512);
+        else {
+          const uint32_t u = *reinterpret_cast<const uint32_t*>(rawp + so + t * 256);
+          b[t] = make_float2(bf16_lo(u), bf16_hi(u));
+        }
+        kk[t] = *reinterpret_cast<const uint32_t*>(rawkp + so + t * 256);
+      }
       float bx = 0.f, by = 0.f;
 #pragma unroll
       for (int t = 0; t < GC; ++t) {
-        float2 g;
-        if (GF32) g = *reinterpret_cast<const float2*>(rawp + so + t * 512);
-        else {
-          const uint32_t u = *reinterpret_cast<const uint32_t*>(rawp + so + t * 256);
-          g = make_float2(bf16_lo(u), bf16_hi(u));
-        }
-        kk[t] = *reinterpret_cast<const uint32_t*>(rawkp + so + t * 256);
-        if (t < clen) { bx = fmaf(g.x, 1.4426950408889634f, bx); by = fmaf(g.y, 1.4426950408889634f, by); }
-        else kk[t] = 0;
+        const bool in = (GP_EXP & 64) ? true : t < clen;
+        bx = fmaf(in ? b[t].x : 0.f, 1.4426950408889634f, bx);
+        by = fmaf(in ? b[t].y : 0.f, 1.4426950408889634f, by);
+        kk[t] = in ? kk[t] : 0u;
         b[t] = make_float2(bx, by);
       }
-      asm volatile("bar.sync 1, 64;" ::: "memory");   // both gate warps are done with the raw slot
-      fetch(i + GP_RS);
+      }
       const float2 r = b[GC / 2 - 1];
       const float rfx = r.x - lscale, rfy = r.y - lscale;
       if (tid == 0) GP_TRACE(i, 2);
@@ -225,6 +250,11 @@ gla_prefill_kernel(const GlaPrefillParams p, const __grid_constant__ CUtensorMap
       uint8_t* sK = stage + GP_ST_K + kbase;
 #pragma unroll
       for (int t = 0; t < GC; ++t) {
+        if (GP_EXP & 8) {
+          *reinterpret_cast<float2*>(sF + t * (kD * 4)) = make_float2(b[t].x, b[t].y);
+          *reinterpret_cast<uint32_t*>(sK + t * 128 + ((kcx ^ (t & 7)) << 4)) = kk[t];
+          continue;
+        }
         *reinterpret_cast<float2*>(sF + t * (kD * 4)) = make_float2(exp2f(b[t].x - rfx), exp2f(b[t].y - rfy));
         *reinterpret_cast<uint32_t*>(sK + t * 128 + ((kcx ^ (t & 7)) << 4)) =
             pack_bf16(bf16_lo(kk[t]) * exp2f(r.x - b[t].x), bf16_hi(kk[t]) * exp2f(r.y - b[t].y));
@@ -234,6 +264,12 @@ gla_prefill_kernel(const GlaPrefillParams p, const __grid_constant__ CUtensorMap
       *reinterpret_cast<float2*>(sD + kD + c) = make_float2(exp2f(r.x), exp2f(r.y));
       fence_proxy_async_smem();
       mbar_arrive(bar_kf + 8 * st);
+      // The raw slot is refilled only now: the stores above consumed every value loaded from it, so
+      // no shared-memory read of this step can still be in flight when the TMA write lands (a
+      // barrier right after the loads is NOT enough -- the compiler schedules their first use
+      // behind it, and under LSU pressure the last rows were read after the refill).
+      asm volatile("bar.sync 1, 64;" ::: "memory");   // both gate warps are done with the raw slot
+      fetch(i + GP_RS);
       if (tid == 0) GP_TRACE(i, 0);
     }
    } else if (warp == 3) {
@@ -337,7 +373,7 @@ gla_prefill_kernel(const GlaPrefillParams p, const __grid_constant__ CUtensorMap
     const float* sD0 = reinterpret_cast<const float*>(smem + GP_ST + GP_ST_D);
     for (int i = -1; i < n_steps; ++i) {
       const bool first = i < 0, last = i + 1 == n_steps;
-      if (!first) {
+      if (!first && !(GP_EXP & 16)) {
         const uint32_t stg = sT + (i % GP_KS) * GP_STAGE;      // kf(i) was awaited in pass i-1
         uint32_t af[2][4];
 #pragma unroll
@@ -399,7 +435,7 @@ gla_prefill_kernel(const GlaPrefillParams p, const __grid_constant__ CUtensorMap
         // rows row0 + 8j all have (row & 7) == gid: eight slot bases, everything else is immediate
         uint8_t* sdst = smem + GP_SS + ((i + 1) & 1) * 32768 + row0 * 128 + tig * 4;
 #pragma unroll
-        for (int k = 0; k < 8; ++k) {
+        for (int k = 0; k < ((GP_EXP & 32) ? 0 : 8); ++k) {
           uint8_t* bk = sdst + (((uint32_t)(k ^ gid) & 7) << 4);
 #pragma unroll
           for (int mt = 0; mt < 2; ++mt)
@@ -438,7 +474,6 @@ gla_prefill_kernel(const GlaPrefillParams p, const __grid_constant__ CUtensorMap
     const uint32_t qo0 = (uint32_t)(qt0 * 128 + (((qc ^ qt0) & 7) << 4)), qo1 = qo0 + 1024;   // (qt0+8)&7 == qt0&7
     const __nv_bfloat16* qp = p.q + (int64_t)(tok_begin + qt0) * p.q_st + (int64_t)h0 * p.q_sh + qc * 8;
     const int q_steps = summary ? 0 : n_steps;      // the summary pass has no queries
-    __nv_bfloat16* op = p.o + (int64_t)(tok_begin + r_t) * p.o_st + (int64_t)(h0 + r_hh) * p.o_sh;
     uint4 qv[16];
     int cnt = 0;
     for (int i = w - 2; i < q_steps; i += 2) {
@@ -505,8 +540,6 @@ gla_prefill_kernel(const GlaPrefillParams p, const __grid_constant__ CUtensorMap
         tc_fence_after();
         if (tq == 0) GP_TRACE(i, 8);
         {
-          const bool live = r_hh < G && r_t < clen;
-          __nv_bfloat16* dst = op + (int64_t)i * GC * p.o_st;
           // 7B g_norm epilogue (model_for_7B/gla_attention.py:177,210): vLLM RMSNorm over the row's
           // 128 outputs of the bf16-rounded o, y = bf16(bf16(o * rstd) * w).  The thread owns the
           // whole row, so this is a first TMEM pass for the sum of squares and no exchange.
@@ -538,15 +571,43 @@ gla_prefill_kernel(const GlaPrefillParams p, const __grid_constant__ CUtensorMap
                 }
               }
             }
-            if (live) {
+            // 32 rows x 64 bytes staged per warp (chunks XOR-swizzled), read back so that four lanes
+            // cover 64 contiguous bytes of one (token, head) row: 8 half-lines per store instruction
+            // instead of 32 scattered 16-byte pieces, which kept the LSU -- and every other role's
+            // shared-memory and mbarrier traffic behind it -- busy for ~2300 cycles per step
+            uint8_t* stg = smem + GP_OST + (warp - 8) * 2048;
+            if (!(GP_EXP & 128)) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              uint4 o4;
+              o4.x = pack_bf16(t[8 * j + 0], t[8 * j + 1]); o4.y = pack_bf16(t[8 * j + 2], t[8 * j + 3]);
+              o4.z = pack_bf16(t[8 * j + 4], t[8 * j + 5]); o4.w = pack_bf16(t[8 * j + 6], t[8 * j + 7]);
+              *reinterpret_cast<uint4*>(stg + lane * 64 + (((j ^ (lane >> 1)) & 3) << 4)) = o4;
+            }
+            }
+            __syncwarp();
+            if (GP_EXP & 128) {
+              const int rq = (warp & 3) * 32 + lane, hh2 = rq >> 4, t2 = rq & 15;
+              if (hh2 < G && t2 < clen) {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                  uint4 o4;
+                  o4.x = pack_bf16(t[8 * j + 0], t[8 * j + 1]); o4.y = pack_bf16(t[8 * j + 2], t[8 * j + 3]);
+                  o4.z = pack_bf16(t[8 * j + 4], t[8 * j + 5]); o4.w = pack_bf16(t[8 * j + 6], t[8 * j + 7]);
+                  stg_v4(p.o + (int64_t)(tok_begin + i * GC + t2) * p.o_st + (int64_t)(h0 + hh2) * p.o_sh + 32 * cc + 8 * j, o4);
+                }
+              }
+            } else if (!(GP_EXP & 2)) {
 #pragma unroll
               for (int j = 0; j < 4; ++j) {
-                uint4 o4;
-                o4.x = pack_bf16(t[8 * j + 0], t[8 * j + 1]); o4.y = pack_bf16(t[8 * j + 2], t[8 * j + 3]);
-                o4.z = pack_bf16(t[8 * j + 4], t[8 * j + 5]); o4.w = pack_bf16(t[8 * j + 6], t[8 * j + 7]);
-                stg_v4(dst + 32 * cc + 8 * j, o4);
+                const int row = 8 * j + (lane >> 2), c = lane & 3;
+                const int rq = (warp & 3) * 32 + row, hh2 = rq >> 4, t2 = rq & 15;
+                const uint4 o4 = *reinterpret_cast<const uint4*>(stg + row * 64 + (((c ^ (row >> 1)) & 3) << 4));
+                if (hh2 < G && t2 < clen)
+                  stg_v4(p.o + (int64_t)(tok_begin + i * GC + t2) * p.o_st + (int64_t)(h0 + hh2) * p.o_sh + 32 * cc + 8 * c, o4);
               }
             }
+            __syncwarp();
           }
         }
         ++cnt;
