@@ -393,18 +393,20 @@ def run_gpu(args):
     kms = {k: sum(v) / len(v) for k, v in per_launch.items()}      # mean ms per launch
 
     # GLA decode kernel alone (the graph's GLA half also holds the gate launches and advance_step)
-    gq, gk_, gv_ = randn(B, H, D).relu_(), randn(B, Hkv, D).relu_(), randn(B, Hkv, D)
-    gg_ = (torch.nn.functional.logsigmoid(torch.randn(B, Hkv, D, device=dev)) / 16).to(bf)
+    # the product form: raw q / k / gk rows, feature map + gate inside the kernel (f2)
+    gq, gk_, gv_ = randn(B, H, D), randn(B, Hkv, D), randn(B, Hkv, D)
+    gg_ = randn(B, Hkv, D)
     og_ = torch.empty(B, H, D, device=dev, dtype=bf)
     gw = torch.ones(D, device=dev, dtype=bf)
     g_k = torch.cuda.CUDAGraph()
     for l in range(N_GLA_LAYERS):
-        ops.gla_decode(gq, gk_, gv_, gg_, gla_state[l], idx_buf, out=og_, gnorm_weight=gw)
+        ops.gla_decode(gq, gk_, gv_, gg_, gla_state[l], idx_buf, out=og_, gnorm_weight=gw, gate_normalizer=16.0)
     torch.cuda.synchronize()
     with torch.cuda.stream(side):
         with torch.cuda.graph(g_k, stream=side):
             for l in range(N_GLA_LAYERS):
-                ops.gla_decode(gq, gk_, gv_, gg_, gla_state[l], idx_buf, out=og_, gnorm_weight=gw)
+                ops.gla_decode(gq, gk_, gv_, gg_, gla_state[l], idx_buf, out=og_, gnorm_weight=gw,
+                               gate_normalizer=16.0)
     torch.cuda.synchronize()
     a, b = ev(), ev()
     g_k.replay(); a.record()
@@ -424,7 +426,7 @@ def run_gpu(args):
     swa_pf_flops = B * sum(H * 4 * D * min(i + 1, WINDOW_LEFT + 1) for i in range(Tp))
     gla_pf_bytes = T * (H * 2 * D * b2 + Hkv * D * (2 * b2 + 2))
     gla_pf_flops = T * H * (4 * D * D + 2 * 64 * 2 * D)
-    gate_bytes = T * (H + 2 * Hkv) * D * b2 * 2            # q,k,gk read + written
+    gate_bytes = T * Hkv * D * b2 * 2                      # gk read, g written (relu of q / k is in the GLA kernels)
     kvw_bytes = T * 2 * Hkv * D * b2 * 2
     us_dswa = t_dswa * 1e3 / (Sd * N_SWA_LAYERS)
 
@@ -442,8 +444,9 @@ def run_gpu(args):
         "gla_decode": K(t_dgla / step_ms, "hbm", gla_dec_bytes, t_gdk_us * 1e-6, peaks["hbm_gbs"], "GB/s",
                         us_per_layer_step_kernel=t_gdk_us,
                         us_per_layer_step_module=t_dgla * 1e3 / (Sd * N_GLA_LAYERS),
-                        what="kernel = recurrent update + g_norm epilogue (timed alone, graph of 14 launches); "
-                             "module = GatedLinearAttention.forward (gate launch + kernel) as replayed in the step"),
+                        what="kernel = feature map + gate + recurrent update + g_norm epilogue on raw projection rows "
+                             "(timed alone, graph of 14 launches); module = GatedLinearAttention.forward as "
+                             "replayed in the step"),
         "swa_prefill": K(t_pswa / step_ms, "tensor", swa_pf_flops, kms["swa_prefill"] * 1e-3,
                          peaks["bf16_tflops_sustained"], "TFLOP/s", ms_per_layer_kernel=kms["swa_prefill"],
                          ms_per_layer_module=t_pswa / N_SWA_LAYERS,
@@ -453,7 +456,8 @@ def run_gpu(args):
                          ms_per_layer_kernel=kms["gla_prefill"], ms_per_layer_module=t_pgla / N_GLA_LAYERS,
                          tensor_tflops=gla_pf_flops / (kms["gla_prefill"] * 1e-3) / 1e12,
                          tok_s_per_layer=T / (t_pgla * 1e-3 / N_GLA_LAYERS),
-                         what="kernel includes the fused g_norm epilogue; module adds the gate launch"),
+                         what="kernel applies relu(q), relu(k) and the fused g_norm epilogue; module adds the 2 KB/token "
+                              "logsigmoid(gk)/16 launch"),
         "gla_gate": K(kms["gla_gate_7b"] * N_GLA_LAYERS / step_ms, "hbm", gate_bytes, kms["gla_gate_7b"] * 1e-3,
                       peaks["hbm_gbs"], "GB/s", ms_per_layer_kernel=kms["gla_gate_7b"]),
         "kv_write": K(kms["kv_write"] * N_SWA_LAYERS / step_ms, "hbm", kvw_bytes, kms["kv_write"] * 1e-3,

@@ -34,8 +34,8 @@
 extern "C" {
 #endif
 
-#define HYMETA_ABI_VERSION 4   /* 3: + rope_kv_write, *_gnorm, branch_*, slot_mgr_*; 4: paged-key prefill,
-                                  new_slot_mapping in the fused decode */
+#define HYMETA_ABI_VERSION 5   /* 3: + rope_kv_write, *_gnorm, branch_*, slot_mgr_*; 4: paged-key prefill,
+                                  new_slot_mapping in the fused decode; 5: 7B gate folded into the GLA kernels (f2) */
 
 typedef enum {
   HYMETA_OK = 0,
@@ -174,6 +174,39 @@ int hymeta_gla_gate_7b(const void* q_in, const void* k_in, const void* gk_in, vo
                        int64_t gi_st, int64_t gi_sh, int64_t qo_st, int64_t qo_sh,
                        int64_t ko_st, int64_t ko_sh, int64_t go_st, int64_t go_sh,
                        float normalizer, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * f2  7B feature map + gate folded into the GLA kernels (vllm_hymeta/model_for_7B/
+ *     gla_attention.py:251-262 and its callers :179-235): the GLA kernels read the RAW qkv_proj /
+ *     gk_proj rows, so the 37 KB/token q / k / g round trip of hymeta_gla_gate_7b disappears.
+ *
+ * hymeta_gla_gate_7b_g:           g = bf16(bf16(logsigmoid(gk)) / normalizer) only (2 KB/token); the
+ *                                 prefill kernel takes it together with raw q / k and relu_qk = 1.
+ * hymeta_gla_prefill_varlen_fused: hymeta_gla_prefill_varlen_seg_gnorm plus relu_qk (0 / 1): relu is
+ *                                 applied to q and k as they are scaled into the MMA operands
+ *                                 (relu(x) * e == max(x * e, 0) for e > 0: bit-identical outputs).
+ * hymeta_gla_decode_gate7b:       hymeta_gla_decode_gnorm plus gate_normalizer: 0 = plain; > 0 = q, k
+ *                                 and g are raw q / k / gk rows (g bf16) and relu / logsigmoid /
+ *                                 division run in the kernel's operand conversion, bit-identical to
+ *                                 hymeta_gla_gate_7b followed by the plain kernel.
+ * ---------------------------------------------------------------------------------------------- */
+int hymeta_gla_gate_7b_g(const void* gk_in, void* g_out, int T, int Hk, int D, int64_t gi_st,
+                         int64_t gi_sh, int64_t go_st, int64_t go_sh, float normalizer, void* stream);
+int hymeta_gla_prefill_varlen_fused(
+    const void* q, const void* k, const void* v, const void* g, void* o, void* state,
+    const void* meta_state, const int32_t* cu_seqlens, const int32_t* slot_idx,
+    const int32_t* init_mode, int N, int T, int H, int Hk, int Hv, int Hs, int D, int64_t q_st,
+    int64_t q_sh, int64_t k_st, int64_t k_sh, int64_t v_st, int64_t v_sh, int64_t g_st,
+    int64_t g_sh, int64_t o_st, int64_t o_sh, int64_t st_ss, int64_t st_sh, int64_t meta_sh,
+    int g_is_fp32, float scale, int write_state, int max_seqlen, int seg_len, void* workspace,
+    size_t workspace_bytes, const void* gnorm_weight, float gnorm_eps, int relu_qk, void* stream);
+int hymeta_gla_decode_gate7b(const void* q, const void* k, const void* v, const void* g, void* o,
+                             void* state, const int32_t* slot_idx, int B, int H, int Hk, int Hv,
+                             int Hs, int D, int64_t q_sb, int64_t q_sh, int64_t k_sb, int64_t k_sh,
+                             int64_t v_sb, int64_t v_sh, int64_t g_sb, int64_t g_sh,
+                             int64_t o_sb, int64_t o_sh, int64_t st_ss, int64_t st_sh,
+                             int g_is_fp32, float scale, const void* gnorm_weight, float gnorm_eps,
+                             float gate_normalizer, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * a9  Paged-KV write -- replaces torch.ops._C_cache_ops.reshape_and_cache_flash

@@ -207,6 +207,38 @@ def test_gated_linear_attention_7b_mixed_batch(ops):
     assert_close(d_state, ref_state, "7B slot states")
 
 
+def test_gate_7b_folded_into_gla_kernels(ops):
+    """f2: raw q / k / gk rows through the fused paths give BIT-IDENTICAL outputs and states to
+    ``gla_gate_7b`` followed by the plain kernels (relu(x) * e == max(x * e, 0); the decode kernel
+    repeats the gate kernel's logsigmoid arithmetic)."""
+    H, Hkv = 28, 4
+    lens = [70, 33, 200]
+    T, B = sum(lens), 37
+    qkv = _qkv(T + B, H, Hkv, 31).to(DEV)
+    gen = torch.Generator().manual_seed(32)
+    gk = (torch.randn(T + B, Hkv, D, generator=gen) * 3).bfloat16().to(DEV)
+    w = (1 + 0.1 * torch.randn(D, generator=gen)).bfloat16().to(DEV)
+    state = (torch.randn(B + 4, Hkv, D, D, generator=gen) * 0.2).bfloat16().to(DEV)
+    q = qkv[:, :H * D].view(-1, H, D)
+    k = qkv[:, H * D:(H + Hkv) * D].view(-1, Hkv, D)
+    v = qkv[:, (H + Hkv) * D:].view(-1, Hkv, D)
+    rq, rk, rg = ops.gla_gate_7b(q, k, gk)
+    assert torch.equal(ops.gla_gate_7b_g(gk), rg)
+    i32 = lambda x: torch.tensor(x, dtype=torch.int32, device=DEV)
+    cu = i32([0, lens[0], lens[0] + lens[1], T])
+    sl, md = i32([1, -1, 3]), i32([1, 0, 1])
+    for gw in (None, w):
+        s1, s2 = state.clone(), state.clone()
+        o1 = ops.gla_prefill_varlen(rq[:T], rk[:T], v[:T], rg[:T], s1, cu, sl, md, gnorm_weight=gw)
+        o2 = ops.gla_prefill_varlen(q[:T], k[:T], v[:T], rg[:T], s2, cu, sl, md, gnorm_weight=gw, relu_qk=True)
+        assert torch.equal(o1, o2) and torch.equal(s1, s2)
+        slots = torch.arange(B, dtype=torch.int32, device=DEV) + 2
+        slots[5] = -1
+        d1 = ops.gla_decode(rq[T:], rk[T:], v[T:], rg[T:], s1, slots, gnorm_weight=gw)
+        d2 = ops.gla_decode(q[T:], k[T:], v[T:], gk[T:], s2, slots, gnorm_weight=gw, gate_normalizer=16.0)
+        assert torch.equal(d1, d2) and torch.equal(s1, s2)
+
+
 # ------------------------------------------------------------------------------------- a7-a10 (backend)
 def test_flash_attention_backend_warmup_then_decode(ops):
     from vllm_hymeta_b200.attention.meta_attention import MetaAttentionMetadataBuilder, SeqData

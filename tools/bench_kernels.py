@@ -215,7 +215,7 @@ def bench_gla_gnorm(N, T, B, H=28, Hkv=4, D=128):
           f"kernel + torch RMSNorm {t2*1e6:.1f} us")
 
 
-def bench_gla_prefill(N, T, H=28, Hkv=4, D=128, gdt=torch.bfloat16, iters=5):
+def bench_gla_prefill(N, T, H=28, Hkv=4, D=128, gdt=torch.bfloat16, iters=5, gn=False):
     dev = "cuda"
     q = torch.randn(N * T, H, D, device=dev).bfloat16().relu()
     k = torch.randn(N * T, Hkv, D, device=dev).bfloat16().relu()
@@ -226,11 +226,12 @@ def bench_gla_prefill(N, T, H=28, Hkv=4, D=128, gdt=torch.bfloat16, iters=5):
     slots = torch.arange(N, device=dev, dtype=torch.int32)
     init = torch.zeros(N, device=dev, dtype=torch.int32)
     out = torch.empty(N * T, H, D, device=dev, dtype=torch.bfloat16)
-    t = timeit(lambda: ops.gla_prefill_varlen(q, k, v, g, state, cu, slots, init, max_seqlen=T, out=out),
-               iters=iters, warmup=2)
+    gw = torch.ones(D, device=dev, dtype=torch.bfloat16) if gn else None
+    t = timeit(lambda: ops.gla_prefill_varlen(q, k, v, g, state, cu, slots, init, max_seqlen=T, out=out,
+                                              gnorm_weight=gw, relu_qk=gn), iters=iters, warmup=2)
     by = N * T * (H * 2 * D * 2 + Hkv * D * (4 + g.element_size()))
     fl = N * T * H * (4 * D * D + 2 * 64 * 2 * D)
-    print(f"gla_prefill N={N} T={T} H={H}/{Hkv}: {t*1e3:8.3f} ms  {by/t/1e9:7.1f} GB/s ({by/t/1e9/PEAK:.2%})  "
+    print(f"gla_prefill{' +relu +g_norm' if gn else ''} N={N} T={T} H={H}/{Hkv}: {t*1e3:8.3f} ms  {by/t/1e9:7.1f} GB/s ({by/t/1e9/PEAK:.2%})  "
           f"{fl/t/1e12:6.1f} TFLOP/s ({fl/t/1e12/TPEAK:.2%})  {N*T/t/1e6:.2f} Mtok/s")
 
 
@@ -257,6 +258,7 @@ if __name__ == "__main__":
         bench_swa_prefill(1, 32768, H=7, Hkv=1, wl=-1, M=128)
     if a.which in ("all", "gla_prefill"):
         bench_gla_prefill(64, 8192)
+        bench_gla_prefill(64, 8192, gn=True)
         bench_gla_prefill(8, 32768)
         bench_gla_prefill(1, 32768, H=7, Hkv=1, gdt=torch.float32)
     if a.which in ("all", "branch_merge"):

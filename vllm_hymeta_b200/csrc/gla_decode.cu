@@ -33,6 +33,11 @@ struct GlaDecodeParams {
   float scale;
   const __nv_bfloat16* gnorm_w;   // per-head RMSNorm weight [128] of the 7B g_norm epilogue, or null
   float gnorm_eps;
+  // > 0: q, k and g are the RAW projection outputs of the 7B layer and the feature map + gate
+  // (model_for_7B/gla_attention.py:251-262) run here: q = relu(q), k = relu(k),
+  // g = bf16(bf16(logsigmoid(gk)) / gate_norm) -- bit-identical to hymeta_gla_gate_7b's outputs
+  // (this file is compiled without --use_fast_math for that; the decay keeps the fast __expf)
+  float gate_norm;
 };
 
 typedef unsigned long long u64;
@@ -172,20 +177,29 @@ __global__ void __launch_bounds__(GD_THREADS, 2) gla_decode_kernel(const GlaDeco
     {  // warp-local conversion of the small operands of this warp's 16 rows
       const int row = warp * 16 + (lane & 15), hf = lane >> 4;
       const __nv_bfloat16* rq = reinterpret_cast<const __nv_bfloat16*>(sbase + GD_RAW_Q) + row;
+      const bool gate = p.gate_norm > 0.f;
+      const float qlo = gate ? 0.f : -INFINITY;     // relu as a max against 0 (identity against -inf)
       float4 t;
-      t.x = __bfloat162float(rq[(hf * 4 + 0) * kD]) * p.scale;
-      t.y = __bfloat162float(rq[(hf * 4 + 1) * kD]) * p.scale;
-      t.z = __bfloat162float(rq[(hf * 4 + 2) * kD]) * p.scale;
-      t.w = __bfloat162float(rq[(hf * 4 + 3) * kD]) * p.scale;
+      t.x = fmaxf(__bfloat162float(rq[(hf * 4 + 0) * kD]), qlo) * p.scale;
+      t.y = fmaxf(__bfloat162float(rq[(hf * 4 + 1) * kD]), qlo) * p.scale;
+      t.z = fmaxf(__bfloat162float(rq[(hf * 4 + 2) * kD]), qlo) * p.scale;
+      t.w = fmaxf(__bfloat162float(rq[(hf * 4 + 3) * kD]), qlo) * p.scale;
       *reinterpret_cast<float4*>(&s_q[row][hf * 4]) = t;
       if (hf == 0) {
-        const uint32_t kb = (uint32_t)reinterpret_cast<const uint16_t*>(sbase + GD_RAW_K)[row];
+        uint32_t kb = (uint32_t)reinterpret_cast<const uint16_t*>(sbase + GD_RAW_K)[row];
+        if (gate && (kb & 0x8000u)) kb = 0u;       // relu(k) on the bf16 bits
         s_kg[row].x = kb | (kb << 16);
       } else {
         float gv;
         if (GF32) gv = reinterpret_cast<const float*>(sbase + GD_RAW_G)[row];
         else gv = __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(sbase + GD_RAW_G)[row]);
-        s_kg[row].y = __float_as_uint(expf(gv));
+        if (!GF32 && gate) {
+          // logsigmoid(x) = min(x, 0) - log1p(exp(-|x|)) (ATen), rounded to bf16 before the division
+          // and again after it -- exactly what hymeta_gla_gate_7b stores (gla_gate.cu)
+          const float ls = fminf(gv, 0.f) - log1pf(expf(-fabsf(gv)));
+          gv = round_bf16(round_bf16(ls) / p.gate_norm);
+        }
+        s_kg[row].y = __float_as_uint(__expf(gv));
       }
     }
     const uint4 vraw = *reinterpret_cast<const uint4*>(sbase + GD_RAW_V + c * 16);
@@ -341,14 +355,15 @@ static void launch_gla_decode(const GlaDecodeParams& p, bool g_fp32, cudaStream_
 
 using namespace hymeta;
 
-extern "C" int hymeta_gla_decode_gnorm(const void* q, const void* k, const void* v, const void* g, void* o,
+extern "C" int hymeta_gla_decode_gate7b(const void* q, const void* k, const void* v, const void* g, void* o,
                                  void* state, const int32_t* slot_idx, int B, int H, int Hk, int Hv,
                                  int Hs, int D, int64_t q_sb, int64_t q_sh, int64_t k_sb, int64_t k_sh,
                                  int64_t v_sb, int64_t v_sh, int64_t g_sb, int64_t g_sh,
                                  int64_t o_sb, int64_t o_sh, int64_t st_ss, int64_t st_sh,
                                  int g_is_fp32, float scale, const void* gnorm_weight, float gnorm_eps,
-                                 void* stream) {
+                                 float gate_normalizer, void* stream) {
   if (B == 0) return HYMETA_OK;
+  if (gate_normalizer < 0.f || (gate_normalizer > 0.f && g_is_fp32)) return HYMETA_ERR_INVALID_ARG;
   if (!q || !k || !v || !g || !o || !state || !slot_idx || B < 0 || H <= 0 || Hk <= 0 || Hv <= 0 || Hs <= 0)
     return HYMETA_ERR_INVALID_ARG;
   if (D != kD) return HYMETA_ERR_UNSUPPORTED;
@@ -365,7 +380,7 @@ extern "C" int hymeta_gla_decode_gnorm(const void* q, const void* k, const void*
   GlaDecodeParams p{(const __nv_bfloat16*)q, (const __nv_bfloat16*)k, (const __nv_bfloat16*)v, g,
                     (__nv_bfloat16*)o, (__nv_bfloat16*)state, slot_idx, B, H, Hk, Hv, Hs, 0u, 0u,
                     q_sb, q_sh, k_sb, k_sh, v_sb, v_sh, g_sb, g_sh, o_sb, o_sh, st_ss, st_sh, scale,
-                    (const __nv_bfloat16*)gnorm_weight, gnorm_eps};
+                    (const __nv_bfloat16*)gnorm_weight, gnorm_eps, gate_normalizer};
   auto magic = [&](int div) -> uint32_t {   // exact for hs < Hs <= 4096 (verified below)
     const uint32_t m = (65536u + div - 1) / div;
     for (int x = 0; x < Hs; ++x)
@@ -384,6 +399,18 @@ extern "C" int hymeta_gla_decode_gnorm(const void* q, const void* k, const void*
   else launch_gla_decode<8>(p, f, st);
   count_launch();
   return check_launch();
+}
+
+extern "C" int hymeta_gla_decode_gnorm(const void* q, const void* k, const void* v, const void* g, void* o,
+                                 void* state, const int32_t* slot_idx, int B, int H, int Hk, int Hv,
+                                 int Hs, int D, int64_t q_sb, int64_t q_sh, int64_t k_sb, int64_t k_sh,
+                                 int64_t v_sb, int64_t v_sh, int64_t g_sb, int64_t g_sh,
+                                 int64_t o_sb, int64_t o_sh, int64_t st_ss, int64_t st_sh,
+                                 int g_is_fp32, float scale, const void* gnorm_weight, float gnorm_eps,
+                                 void* stream) {
+  return hymeta_gla_decode_gate7b(q, k, v, g, o, state, slot_idx, B, H, Hk, Hv, Hs, D, q_sb, q_sh, k_sb,
+                                  k_sh, v_sb, v_sh, g_sb, g_sh, o_sb, o_sh, st_ss, st_sh, g_is_fp32,
+                                  scale, gnorm_weight, gnorm_eps, 0.f, stream);
 }
 
 extern "C" int hymeta_gla_decode(const void* q, const void* k, const void* v, const void* g, void* o,

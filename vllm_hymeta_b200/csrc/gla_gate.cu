@@ -45,7 +45,8 @@ __device__ __forceinline__ uint4 relu8(const uint4& v) {
   return make_uint4(r(v.x), r(v.y), r(v.z), r(v.w));
 }
 
-// MODE 0: 70B without lower bound, 1: 70B with lower bound, 2: 7B
+// MODE 0: 70B without lower bound, 1: 70B with lower bound, 2: 7B, 3: 7B gate only (g from gk; relu of
+// q and k is left to the GLA kernels, which apply it on the fly to the raw projection outputs)
 template <int MODE>
 __global__ void __launch_bounds__(256) gla_gate_kernel(const GateParams p) {
   constexpr int CPR = kD / 8;   // 16-byte chunks per head row
@@ -63,9 +64,10 @@ __global__ void __launch_bounds__(256) gla_gate_kernel(const GateParams p) {
     const int c = (int)(j % CPR), ho = (int)((j / CPR) % p.Ho);
     const int64_t t = j / ((int64_t)CPR * p.Ho);
     const int hk = ho / (p.Ho / p.Hk);
-    const uint4 kraw = ldg_nc_v4(p.k_in + t * p.ki_st + hk * p.ki_sh + c * 8);
-    if (MODE == 2) {
-      stg_v4(p.k_out + t * p.ko_st + ho * p.ko_sh + c * 8, relu8(kraw));
+    uint4 kraw = make_uint4(0, 0, 0, 0);
+    if (MODE != 3) kraw = ldg_nc_v4(p.k_in + t * p.ki_st + hk * p.ki_sh + c * 8);
+    if (MODE >= 2) {
+      if (MODE == 2) stg_v4(p.k_out + t * p.ko_st + ho * p.ko_sh + c * 8, relu8(kraw));
       float x[8], g[8];
       unpack8(ldg_nc_v4(p.gk_in + t * p.gi_st + hk * p.gi_sh + c * 8), x);
 #pragma unroll
@@ -107,7 +109,8 @@ static int launch_gate(const GateParams& p, int mode, cudaStream_t st) {
   const int blocks = (int)(want < 148 * 16 ? want : 148 * 16);
   if (mode == 0) gla_gate_kernel<0><<<blocks, 256, 0, st>>>(p);
   else if (mode == 1) gla_gate_kernel<1><<<blocks, 256, 0, st>>>(p);
-  else gla_gate_kernel<2><<<blocks, 256, 0, st>>>(p);
+  else if (mode == 2) gla_gate_kernel<2><<<blocks, 256, 0, st>>>(p);
+  else gla_gate_kernel<3><<<blocks, 256, 0, st>>>(p);
   count_launch();
   return check_launch();
 }
@@ -164,4 +167,18 @@ extern "C" int hymeta_gla_gate_7b(const void* q_in, const void* k_in, const void
   p.qo_st = qo_st; p.qo_sh = qo_sh; p.ko_st = ko_st; p.ko_sh = ko_sh; p.go_st = go_st; p.go_sh = go_sh;
   p.clamp_max = 0.f; p.norm = normalizer;
   return launch_gate(p, 2, (cudaStream_t)stream);
+}
+
+extern "C" int hymeta_gla_gate_7b_g(const void* gk_in, void* g_out, int T, int Hk, int D, int64_t gi_st,
+                                    int64_t gi_sh, int64_t go_st, int64_t go_sh, float normalizer,
+                                    void* stream) {
+  if (T == 0) return HYMETA_OK;
+  if (!gk_in || !g_out || T < 0 || Hk <= 0 || normalizer == 0.f) return HYMETA_ERR_INVALID_ARG;
+  if (D != kD) return HYMETA_ERR_UNSUPPORTED;
+  if ((gi_st % 8) || (gi_sh % 8) || (go_st % 8) || (go_sh % 8)) return HYMETA_ERR_INVALID_ARG;
+  GateParams p{};
+  p.gk_in = (const __nv_bfloat16*)gk_in; p.g_out = g_out;
+  p.T = T; p.H = 0; p.Hk = Hk; p.Ho = Hk;
+  p.gi_st = gi_st; p.gi_sh = gi_sh; p.go_st = go_st; p.go_sh = go_sh; p.norm = normalizer;
+  return launch_gate(p, 3, (cudaStream_t)stream);
 }

@@ -47,8 +47,9 @@ constexpr int GP_RS = 2;                        //   stages
 constexpr int GP_RAW_K = 8192;                  //   g [16][64 thr] 4|8 B (8 KB), k [16][64 thr] 4 B (4 KB)
 constexpr int GP_RAW_STAGE = 12288;
 constexpr int GP_OST = GP_RAW + GP_RS * GP_RAW_STAGE;   // output staging: 8 q-tile warps x 2 KB
-constexpr int GP_BAR = GP_OST + ((GP_EXP & 128) ? 0 : 8 * 2048);
-constexpr int GP_SMEM = GP_BAR + 256;
+constexpr int GP_BAR = GP_OST + 8 * 2048;
+constexpr int GP_GW = GP_BAR + 256;             // g_norm weight [128] bf16 (7B epilogue)
+constexpr int GP_SMEM = GP_GW + 256;
 constexpr int GP_THREADS = 512;
 constexpr int GP_WS_ELEMS = kD * kD + kD;      // per (chain, segment): state [128][128] + decay [128]
 
@@ -65,7 +66,20 @@ struct GlaPrefillParams {
   int64_t q_st, q_sh, k_st, k_sh, v_st, v_sh, g_st, g_sh, o_st, o_sh, st_ss, st_sh, meta_sh;
   const __nv_bfloat16* gnorm_w;   // per-head RMSNorm weight [128] of the 7B g_norm epilogue, or null
   float gnorm_eps;
+  uint32_t relu_lim;              // bf16x2 lower limit applied to q and k: 0 = relu (7B feature map on raw
+                                  // projection outputs), 0xff80ff80 (-inf) = identity
 };
+
+__device__ __forceinline__ uint32_t hmul2_bf16(uint32_t a, uint32_t b) {   // exact products, one rounding each
+  uint32_t d;
+  asm("mul.rn.bf16x2 %0, %1, %2;" : "=r"(d) : "r"(a), "r"(b));
+  return d;
+}
+__device__ __forceinline__ uint32_t max_bf16x2(uint32_t a, uint32_t b) {
+  uint32_t d;
+  asm("max.bf16x2 %0, %1, %2;" : "=r"(d) : "r"(a), "r"(b));
+  return d;
+}
 
 __device__ __forceinline__ void tmem_st8(uint32_t taddr, const uint32_t (&r)[8]) {
   asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};"
@@ -144,6 +158,8 @@ gla_prefill_kernel(const GlaPrefillParams p, const __grid_constant__ CUtensorMap
     for (int s = 0; s < GP_RS; ++s) mbar_init(bar_raw + 8 * s, 1);
     fence_mbar_init();
   }
+  if (GN && tid >= 64 && tid < 80)   // g_norm weight -> smem once (read as broadcast words by every row owner)
+    *reinterpret_cast<uint4*>(smem + GP_GW + (tid - 64) * 16) = ldg_nc_v4(p.gnorm_w + (tid - 64) * 8);
   if (warp == 2) tmem_alloc<512>(smem_u32(tmem_slot));
   tc_fence_before();
   __syncthreads();
@@ -191,22 +207,6 @@ gla_prefill_kernel(const GlaPrefillParams p, const __grid_constant__ CUtensorMap
       uint32_t kk[GC];
       // every load is issued before the first use (no branch between them: the ragged tail is
       // handled by selects, so the 32 shared-memory reads overlap instead of serialising)
-      if (GP_EXP & 256) {
-        float bx = 0.f, by = 0.f;
-#pragma unroll
-        for (int t = 0; t < GC; ++t) {
-          float2 g;
-          if (GF32) g = *reinterpret_cast<const float2*>(rawp + so + t * 512);
-          else {
-            const uint32_t u = *reinterpret_cast<const uint32_t*>(rawp + so + t * 256);
-            g = make_float2(bf16_lo(u), bf16_hi(u));
-          }
-          kk[t] = *reinterpret_cast<const uint32_t*>(rawkp + so + t * 256);
-          if (t < clen) { bx = fmaf(g.x, 1.4426950408889634f, bx); by = fmaf(g.y, 1.4426950408889634f, by); }
-          else kk[t] = 0;
-          b[t] = make_float2(bx, by);
-        }
-      } else {
 #pragma unroll
       for (int t = 0; t < GC; ++t) {
         if (GF32) b[t] = *reinterpret_cast<const float2*>(rawp + so + t * 512);
@@ -219,12 +219,11 @@ gla_prefill_kernel(const GlaPrefillParams p, const __grid_constant__ CUtensorMap
       float bx = 0.f, by = 0.f;
 #pragma unroll
       for (int t = 0; t < GC; ++t) {
-        const bool in = (GP_EXP & 64) ? true : t < clen;
+        const bool in = t < clen;
         bx = fmaf(in ? b[t].x : 0.f, 1.4426950408889634f, bx);
         by = fmaf(in ? b[t].y : 0.f, 1.4426950408889634f, by);
-        kk[t] = in ? kk[t] : 0u;
+        kk[t] = in ? max_bf16x2(kk[t], p.relu_lim) : 0u;
         b[t] = make_float2(bx, by);
-      }
       }
       const float2 r = b[GC / 2 - 1];
       const float rfx = r.x - lscale, rfy = r.y - lscale;
@@ -467,7 +466,7 @@ gla_prefill_kernel(const GlaPrefillParams p, const __grid_constant__ CUtensorMap
     const int tq = tid - 256 - w * 128;             // 0..127
     const uint32_t lane_off = (uint32_t)((warp & 3) * 32) << 16;
     const int qc = tq & 15, qt0 = tq >> 4;          // builder view: 16-byte chunk qc, tokens qt0, qt0+8
-    const int r_hh = tq >> 4, r_t = tq & 15;        // row-owner view: head slot, token
+    const int r_t = tq & 15;                        // row-owner view: token (head slot = tq >> 4)
     const uint32_t tAw = tA + 16 * w + lane_off, tOw = tO + 128 * w + lane_off;
     // q~ row (hh*16 + t) of 16-byte chunk qc: byte offsets of tokens qt0 / qt0+8 for head slot 0
     uint8_t* sQw = smem + GP_SQ + w * 32768 + (qc >> 3) * 16384;
@@ -496,10 +495,11 @@ gla_prefill_kernel(const GlaPrefillParams p, const __grid_constant__ CUtensorMap
           const float* e = (it & 1) ? e1 : e0;
           const uint4 v4 = qv[it];
           uint4 o4;
-          o4.x = pack_bf16(bf16_lo(v4.x) * e[0], bf16_hi(v4.x) * e[1]);
-          o4.y = pack_bf16(bf16_lo(v4.y) * e[2], bf16_hi(v4.y) * e[3]);
-          o4.z = pack_bf16(bf16_lo(v4.z) * e[4], bf16_hi(v4.z) * e[5]);
-          o4.w = pack_bf16(bf16_lo(v4.w) * e[6], bf16_hi(v4.w) * e[7]);
+          // relu(q) * e == max(q * e, 0) because e > 0: one packed max per word (identity for -inf)
+          o4.x = max_bf16x2(pack_bf16(bf16_lo(v4.x) * e[0], bf16_hi(v4.x) * e[1]), p.relu_lim);
+          o4.y = max_bf16x2(pack_bf16(bf16_lo(v4.y) * e[2], bf16_hi(v4.y) * e[3]), p.relu_lim);
+          o4.z = max_bf16x2(pack_bf16(bf16_lo(v4.z) * e[4], bf16_hi(v4.z) * e[5]), p.relu_lim);
+          o4.w = max_bf16x2(pack_bf16(bf16_lo(v4.w) * e[6], bf16_hi(v4.w) * e[7]), p.relu_lim);
           if (!(GP_EXP & 4)) *reinterpret_cast<uint4*>(sQw + (it >> 1) * 2048 + ((it & 1) ? qo1 : qo0)) = o4;
         }
         fence_proxy_async_smem();
@@ -543,32 +543,49 @@ gla_prefill_kernel(const GlaPrefillParams p, const __grid_constant__ CUtensorMap
           // 7B g_norm epilogue (model_for_7B/gla_attention.py:177,210): vLLM RMSNorm over the row's
           // 128 outputs of the bf16-rounded o, y = bf16(bf16(o * rstd) * w).  The thread owns the
           // whole row, so this is a first TMEM pass for the sum of squares and no exchange.
+          // x = bf16(o) is what both the sum of squares and the scaling use: pass 1 rounds each
+          // 32-column chunk once, packs it (bf16x2) back over the consumed columns of the O region
+          // and accumulates the squares; pass 2 reads the 64 packed columns, scales in fp32, rounds,
+          // and applies the weight with one packed bf16 multiply (exact product, one rounding --
+          // the same value as the fp32 multiply + round of the reference op).
           float rstd = 0.f;
           if (GN) {
             float ss = 0.f;
 #pragma unroll 1
-            for (int cc = 0; cc < 4; ++cc) {
-              float t[32];
-              tmem_ld32(tOw + 32 * cc, t);
+            for (int cc = 0; cc < 8; ++cc) {   // 16 columns at a time: the q prefetch holds 64 registers here
+              float t[16];
+              tmem_ld16(tOw + 16 * cc, t);
+              uint32_t xb[8];
 #pragma unroll
-              for (int j = 0; j < 32; ++j) { const float xb = round_bf16(t[j]); ss = fmaf(xb, xb, ss); }
+              for (int j = 0; j < 8; ++j) {
+                xb[j] = pack_bf16(t[2 * j], t[2 * j + 1]);
+                ss = fmaf(bf16_lo(xb[j]), bf16_lo(xb[j]), ss);
+                ss = fmaf(bf16_hi(xb[j]), bf16_hi(xb[j]), ss);
+              }
+              tmem_st8(tOw + 8 * cc, xb);
             }
+            tmem_wait_st();
             rstd = rsqrtf(ss * (1.f / kD) + p.gnorm_eps);
           }
+          const uint32_t* gw = reinterpret_cast<const uint32_t*>(smem + GP_GW);
 #pragma unroll 1
           for (int cc = 0; cc < ((GP_EXP & 1) ? 0 : 4); ++cc) {
-            float t[32];
-            tmem_ld32(tOw + 32 * cc, t);
+            uint32_t ob[16];   // 32 output columns, packed bf16x2
             if (GN) {
+              float t[16];
+              tmem_ld16(tOw + 16 * cc, t);
 #pragma unroll
-              for (int j = 0; j < 4; ++j) {
-                const uint4 w4 = *reinterpret_cast<const uint4*>(p.gnorm_w + 32 * cc + 8 * j);
-                const uint32_t* wp = &w4.x;
+              for (int j = 0; j < 16; ++j) {
+                const uint32_t x = __float_as_uint(t[j]);
+                ob[j] = hmul2_bf16(pack_bf16(bf16_lo(x) * rstd, bf16_hi(x) * rstd), gw[16 * cc + j]);
+              }
+            } else {
 #pragma unroll
-                for (int e = 0; e < 4; ++e) {
-                  t[8 * j + 2 * e] = round_bf16(round_bf16(t[8 * j + 2 * e]) * rstd) * bf16_lo(wp[e]);
-                  t[8 * j + 2 * e + 1] = round_bf16(round_bf16(t[8 * j + 2 * e + 1]) * rstd) * bf16_hi(wp[e]);
-                }
+              for (int hf = 0; hf < 2; ++hf) {
+                float t[16];
+                tmem_ld16(tOw + 32 * cc + 16 * hf, t);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) ob[8 * hf + j] = pack_bf16(t[2 * j], t[2 * j + 1]);
               }
             }
             // 32 rows x 64 bytes staged per warp (chunks XOR-swizzled), read back so that four lanes
@@ -576,28 +593,12 @@ gla_prefill_kernel(const GlaPrefillParams p, const __grid_constant__ CUtensorMap
             // instead of 32 scattered 16-byte pieces, which kept the LSU -- and every other role's
             // shared-memory and mbarrier traffic behind it -- busy for ~2300 cycles per step
             uint8_t* stg = smem + GP_OST + (warp - 8) * 2048;
-            if (!(GP_EXP & 128)) {
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              uint4 o4;
-              o4.x = pack_bf16(t[8 * j + 0], t[8 * j + 1]); o4.y = pack_bf16(t[8 * j + 2], t[8 * j + 3]);
-              o4.z = pack_bf16(t[8 * j + 4], t[8 * j + 5]); o4.w = pack_bf16(t[8 * j + 6], t[8 * j + 7]);
-              *reinterpret_cast<uint4*>(stg + lane * 64 + (((j ^ (lane >> 1)) & 3) << 4)) = o4;
-            }
-            }
+            for (int j = 0; j < 4; ++j)
+              *reinterpret_cast<uint4*>(stg + lane * 64 + (((j ^ (lane >> 1)) & 3) << 4)) =
+                  make_uint4(ob[4 * j], ob[4 * j + 1], ob[4 * j + 2], ob[4 * j + 3]);
             __syncwarp();
-            if (GP_EXP & 128) {
-              const int rq = (warp & 3) * 32 + lane, hh2 = rq >> 4, t2 = rq & 15;
-              if (hh2 < G && t2 < clen) {
-#pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                  uint4 o4;
-                  o4.x = pack_bf16(t[8 * j + 0], t[8 * j + 1]); o4.y = pack_bf16(t[8 * j + 2], t[8 * j + 3]);
-                  o4.z = pack_bf16(t[8 * j + 4], t[8 * j + 5]); o4.w = pack_bf16(t[8 * j + 6], t[8 * j + 7]);
-                  stg_v4(p.o + (int64_t)(tok_begin + i * GC + t2) * p.o_st + (int64_t)(h0 + hh2) * p.o_sh + 32 * cc + 8 * j, o4);
-                }
-              }
-            } else if (!(GP_EXP & 2)) {
+            if (!(GP_EXP & 2)) {
 #pragma unroll
               for (int j = 0; j < 4; ++j) {
                 const int row = 8 * j + (lane >> 2), c = lane & 3;
@@ -664,14 +665,14 @@ extern "C" size_t hymeta_gla_prefill_workspace_bytes(int N, int Hs, int max_seql
   return (size_t)N * Hs * n_segs * GP_WS_ELEMS * sizeof(float);
 }
 
-extern "C" int hymeta_gla_prefill_varlen_seg_gnorm(
+extern "C" int hymeta_gla_prefill_varlen_fused(
     const void* q, const void* k, const void* v, const void* g, void* o, void* state,
     const void* meta_state, const int32_t* cu_seqlens, const int32_t* slot_idx,
     const int32_t* init_mode, int N, int T, int H, int Hk, int Hv, int Hs, int D, int64_t q_st, int64_t q_sh,
     int64_t k_st, int64_t k_sh, int64_t v_st, int64_t v_sh, int64_t g_st, int64_t g_sh, int64_t o_st,
     int64_t o_sh, int64_t st_ss, int64_t st_sh, int64_t meta_sh, int g_is_fp32, float scale,
     int write_state, int max_seqlen, int seg_len, void* workspace, size_t workspace_bytes,
-    const void* gnorm_weight, float gnorm_eps, void* stream) {
+    const void* gnorm_weight, float gnorm_eps, int relu_qk, void* stream) {
   if (N == 0) return HYMETA_OK;
   if (seg_len < 0 || seg_len % GC) return HYMETA_ERR_INVALID_ARG;
   int n_segs = 1;
@@ -702,6 +703,7 @@ extern "C" int hymeta_gla_prefill_varlen_seg_gnorm(
   p.meta_sh = meta_sh;
   if (gnorm_weight && ((uintptr_t)gnorm_weight & 15)) return HYMETA_ERR_INVALID_ARG;
   p.gnorm_w = (const __nv_bfloat16*)gnorm_weight; p.gnorm_eps = gnorm_eps;
+  p.relu_lim = relu_qk ? 0u : 0xff80ff80u;
   p.seg_len = seg_len; p.n_segs = n_segs; p.pass = 0; p.ws = (float*)workspace;
   // TMA maps: raw g / k rows ([16 tokens][128 channels] boxes) and v (SWIZZLE_128B 64-wide halves)
   const int64_t tvec[] = {k_st, k_sh, g_st * (g_is_fp32 ? 2 : 1), g_sh * (g_is_fp32 ? 2 : 1)};
@@ -750,6 +752,21 @@ extern "C" int hymeta_gla_prefill_varlen_seg_gnorm(
     launch(3, n_segs);
   }
   return check_launch();
+}
+
+extern "C" int hymeta_gla_prefill_varlen_seg_gnorm(
+    const void* q, const void* k, const void* v, const void* g, void* o, void* state,
+    const void* meta_state, const int32_t* cu_seqlens, const int32_t* slot_idx,
+    const int32_t* init_mode, int N, int T, int H, int Hk, int Hv, int Hs, int D, int64_t q_st, int64_t q_sh,
+    int64_t k_st, int64_t k_sh, int64_t v_st, int64_t v_sh, int64_t g_st, int64_t g_sh, int64_t o_st,
+    int64_t o_sh, int64_t st_ss, int64_t st_sh, int64_t meta_sh, int g_is_fp32, float scale,
+    int write_state, int max_seqlen, int seg_len, void* workspace, size_t workspace_bytes,
+    const void* gnorm_weight, float gnorm_eps, void* stream) {
+  return hymeta_gla_prefill_varlen_fused(q, k, v, g, o, state, meta_state, cu_seqlens, slot_idx, init_mode, N, T,
+                                         H, Hk, Hv, Hs, D, q_st, q_sh, k_st, k_sh, v_st, v_sh, g_st, g_sh,
+                                         o_st, o_sh, st_ss, st_sh, meta_sh, g_is_fp32, scale, write_state,
+                                         max_seqlen, seg_len, workspace, workspace_bytes, gnorm_weight,
+                                         gnorm_eps, 0, stream);
 }
 
 extern "C" int hymeta_gla_prefill_varlen_seg(

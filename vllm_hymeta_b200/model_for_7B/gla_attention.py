@@ -2,8 +2,12 @@
 (vllm_hymeta/model_for_7B/gla_attention.py:90-283) between the projections and ``o_proj``, same
 method names and argument meaning, on the sm_100a kernels:
 
-* feature map + gate (:251-267)          -> ONE launch, ``ops.gla_gate_7b`` (k / v / gk stay at the
-                                            kv-head count: no ``repeat_kv`` x7 materialisation)
+* feature map + gate (:251-267)          -> folded into the GLA kernels: they read the
+                                            raw ``qkv_proj`` / ``gk_proj`` rows, relu(q) / relu(k)
+                                            on the fly; the decode kernel also computes
+                                            logsigmoid(gk) / 16, prefill takes it from the 2 KB/token
+                                            ``ops.gla_gate_7b_g`` pass (k / v / gk stay at the kv-head
+                                            count: no ``repeat_kv`` x7 materialisation)
 * per-request ``fused_chunk_gla`` loop   -> ONE varlen launch over all prefill requests, slot
   (:179-211)                                states read and written in-kernel (no isnan() host sync)
 * decode (:223-235)                      -> ``ops.gla_decode``
@@ -72,10 +76,11 @@ class GatedLinearAttention:
                 mode = torch.where(ctx[:num_prefills] == 0, ops.INIT_ZERO, ops.INIT_SLOT).to(torch.int32)
             else:
                 mode = torch.full((num_prefills,), ops.INIT_SLOT, dtype=torch.int32, device=q.device)
-            ops.gla_prefill_varlen(q[:n_tok], k[:n_tok], v[:n_tok], gk[:n_tok], kv_cache, cu, slots,
+            g = ops.gla_gate_7b_g(gk[:n_tok], self.gate_logit_normalizer)
+            ops.gla_prefill_varlen(q[:n_tok], k[:n_tok], v[:n_tok], g, kv_cache, cu, slots,
                                    mode, max_seqlen=getattr(attn_metadata, "max_query_len", None) or n_tok,
                                    out=out[:n_tok], gnorm_weight=self._gnorm_w(q.device),
-                                   gnorm_eps=self.norm_eps)
+                                   gnorm_eps=self.norm_eps, relu_qk=True)
         if attn_metadata.num_decode_tokens > 0:
             self._decode(q, k, v, gk, kv_cache, state_indices_tensor, attn_metadata,
                          out=out[attn_metadata.num_prefill_tokens:])
@@ -89,7 +94,7 @@ class GatedLinearAttention:
         o = ops.gla_decode(q[start:], k[start:], v[start:], gk[start:], kv_cache,
                            slot_ids[:B].to(torch.int32), out=out,
                            gnorm_weight=self._gnorm_w(q.device) if norm else None,
-                           gnorm_eps=self.norm_eps)
+                           gnorm_eps=self.norm_eps, gate_normalizer=self.gate_logit_normalizer)
         return o.view(B, -1)
 
     def forward(self, qkv: torch.Tensor, gk: torch.Tensor, kv_caches: GLACacheParams,
@@ -106,9 +111,9 @@ class GatedLinearAttention:
         if gk.shape[1] != self.tp_kv_heads:
             s = self.tp_kv_heads * self.tp_rank
             gk = gk[:, s:s + self.tp_kv_heads]
-        q, k, g = ops.gla_gate_7b(q, k, gk, self.gate_logit_normalizer)
+        # q, k, gk stay RAW: the feature map and the gate are applied inside the GLA kernels
         kv_cache = kv_caches.gla_cache
         idx = kv_caches.state_indices_tensor
         if getattr(attn_metadata, "num_prefills", 0) != 0:
-            return self._prefill_and_mix_infer(q, k, v, g, kv_cache, idx, attn_metadata)
-        return self._decode(q, k, v, g, kv_cache, idx, attn_metadata)
+            return self._prefill_and_mix_infer(q, k, v, gk, kv_cache, idx, attn_metadata)
+        return self._decode(q, k, v, gk, kv_cache, idx, attn_metadata)

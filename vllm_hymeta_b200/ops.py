@@ -76,10 +76,12 @@ def launch_count() -> int:
 def gla_decode(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, g: torch.Tensor,
                state: torch.Tensor, slot_idx: torch.Tensor, scale: Optional[float] = None,
                out: Optional[torch.Tensor] = None, gnorm_weight: Optional[torch.Tensor] = None,
-               gnorm_eps: float = 1e-6) -> torch.Tensor:
+               gnorm_eps: float = 1e-6, gate_normalizer: Optional[float] = None) -> torch.Tensor:
     """q [B,H,D]; k,g [B,Hk,D]; v [B,Hv,D]; state [slots,Hs,D,D] bf16 (updated in place);
     slot_idx [B] int32 (-1 = skip).  Returns o [B,H,D] bf16.  gnorm_weight [D] bf16: the 7B
-    per-head ``g_norm`` RMSNorm applied as the kernel's epilogue."""
+    per-head ``g_norm`` RMSNorm applied as the kernel's epilogue.  gate_normalizer: q, k and g
+    are the RAW 7B projection rows (g = gk_proj output, bf16) and relu(q), relu(k),
+    logsigmoid(gk) / gate_normalizer run inside the kernel."""
     B, H, D = q.shape
     Hk, Hv, Hs = k.shape[1], v.shape[1], state.shape[1]
     if g.shape[1] != Hk:
@@ -100,12 +102,14 @@ def gla_decode(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, g: torch.Tenso
         _req(gnorm_weight, "gnorm_weight", torch.bfloat16)
         if gnorm_weight.numel() != D:
             raise ValueError("gnorm_weight must hold head_dim elements")
-    check(lib().hymeta_gla_decode_gnorm(
+    if gate_normalizer is not None and (gate_normalizer <= 0 or g.dtype != torch.bfloat16):
+        raise ValueError("the fused 7B gate needs a positive normalizer and bf16 gk rows")
+    check(lib().hymeta_gla_decode_gate7b(
         _ptr(q), _ptr(k), _ptr(v), _ptr(g), _ptr(out), _ptr(state), _ptr(slot_idx),
         B, H, Hk, Hv, Hs, D, q.stride(0), q.stride(1), k.stride(0), k.stride(1), v.stride(0), v.stride(1),
         g.stride(0), g.stride(1), out.stride(0), out.stride(1), state.stride(0), state.stride(1),
         int(g.dtype == torch.float32), float(scale), _ptr(gnorm_weight), float(gnorm_eps),
-        _stream()), "hymeta_gla_decode")
+        float(gate_normalizer or 0.0), _stream()), "hymeta_gla_decode")
     return out
 
 
@@ -116,10 +120,11 @@ def gla_prefill_varlen(q, k, v, g, state, cu_seqlens, slot_idx, init_mode,
                        write_state: bool = True, max_seqlen: Optional[int] = None,
                        out: Optional[torch.Tensor] = None, seg_len: Optional[int] = None,
                        gnorm_weight: Optional[torch.Tensor] = None,
-                       gnorm_eps: float = 1e-6) -> torch.Tensor:
+                       gnorm_eps: float = 1e-6, relu_qk: bool = False) -> torch.Tensor:
     """q [T,H,D]; k,g [T,Hk,D]; v [T,Hv,D]; state [slots,Hs,D,D]; cu_seqlens [N+1], slot_idx [N],
     init_mode [N] int32 device tensors.  Returns o [T,H,D] bf16; writes final states.
-    gnorm_weight [D] bf16: the 7B per-head ``g_norm`` RMSNorm applied as the kernel's epilogue."""
+    gnorm_weight [D] bf16: the 7B per-head ``g_norm`` RMSNorm applied as the kernel's epilogue.
+    relu_qk: q and k are raw projection rows, relu is applied in the kernel."""
     T, H, D = q.shape
     Hk, Hv, Hs = k.shape[1], v.shape[1], state.shape[1]
     if g.shape[1] != Hk:
@@ -148,14 +153,14 @@ def gla_prefill_varlen(q, k, v, g, state, cu_seqlens, slot_idx, init_mode,
         _req(gnorm_weight, "gnorm_weight", torch.bfloat16)
         if gnorm_weight.numel() != D:
             raise ValueError("gnorm_weight must hold head_dim elements")
-    check(lib().hymeta_gla_prefill_varlen_seg_gnorm(
+    check(lib().hymeta_gla_prefill_varlen_fused(
         _ptr(q), _ptr(k), _ptr(v), _ptr(g), _ptr(out), _ptr(state), _ptr(meta_state),
         _ptr(cu_seqlens), _ptr(slot_idx), _ptr(init_mode), N, T, H, Hk, Hv, Hs, D,
         q.stride(0), q.stride(1), k.stride(0), k.stride(1), v.stride(0), v.stride(1),
         g.stride(0), g.stride(1), out.stride(0), out.stride(1), state.stride(0), state.stride(1),
         0 if meta_state is None else meta_state.stride(0),
         int(g.dtype == torch.float32), float(scale), int(write_state), msl,
-        int(seg_len or 0), _ptr(ws), ws_bytes, _ptr(gnorm_weight), float(gnorm_eps),
+        int(seg_len or 0), _ptr(ws), ws_bytes, _ptr(gnorm_weight), float(gnorm_eps), int(bool(relu_qk)),
         _stream()), "hymeta_gla_prefill_varlen_seg")
     return out
 
@@ -250,6 +255,19 @@ def gla_gate_7b(q: torch.Tensor, k: torch.Tensor, gk: torch.Tensor, normalizer: 
         q_out.stride(0), q_out.stride(1), k_out.stride(0), k_out.stride(1),
         g_out.stride(0), g_out.stride(1), float(normalizer), _stream()), "hymeta_gla_gate_7b")
     return q_out, k_out, g_out
+
+
+@_timed("gla_gate_7b")
+def gla_gate_7b_g(gk: torch.Tensor, normalizer: float = 16.0, out: Optional[torch.Tensor] = None):
+    """Gate half of the 7B pre-processing only: g = bf16(bf16(logsigmoid(gk)) / normalizer), [T,Hk,D]
+    bf16.  relu(q) / relu(k) are applied by ``gla_prefill_varlen(relu_qk=True)`` on the raw rows."""
+    T, Hk, D = gk.shape
+    _req(gk, "gk", torch.bfloat16)
+    g_out = out if out is not None else torch.empty(T, Hk, D, dtype=gk.dtype, device=gk.device)
+    check(lib().hymeta_gla_gate_7b_g(_ptr(gk), _ptr(g_out), T, Hk, D, gk.stride(0), gk.stride(1),
+                                     g_out.stride(0), g_out.stride(1), float(normalizer), _stream()),
+          "hymeta_gla_gate_7b_g")
+    return g_out
 
 
 # ----------------------------------------------------------------------------------- a9
