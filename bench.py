@@ -313,7 +313,8 @@ def run_gpu(args):
 
     ev = lambda: torch.cuda.Event(enable_timing=True)
 
-    def one_step(rec=None, md=None, idx=None, before_gla=None, fresh_md_d=None):
+    def one_step(rec=None, md=None, idx=None, before_gla=None, fresh_md_d=None, swa_in=None):
+        sq, sk, sv = (swa_q, swa_k, swa_v) if swa_in is None else swa_in
         md = md_p if md is None else md
         idx = idx_buf if idx is None else idx
         if fresh_md_d is None:                     # same request set as before: rewind the decode metadata
@@ -327,7 +328,7 @@ def run_gpu(args):
         e = [ev() for _ in range(4)] if rec is not None else None
         if e: e[0].record()
         for l in range(N_SWA_LAYERS):
-            impl.forward(layers[l], swa_q, swa_k, swa_v, None, None, None, kv_caches[l], md, output=out_swa)
+            impl.forward(layers[l], sq, sk, sv, None, None, None, kv_caches[l], md, output=out_swa)
         if e: e[1].record()
         if before_gla is not None:
             before_gla()
@@ -498,37 +499,58 @@ def run_gpu(args):
                 md.context_lens_tensor, md.block_tables) if t is not None)
         h2d = sum(t.numel() * t.element_size() for t in dev_inputs)
         d2h = sum(t.numel() * t.element_size() for t in host_out)
-        # the SWA inputs must be resident before the first launch; the GLA inputs (half of the bytes)
-        # stream in on a copy stream underneath the SWA prefill and are awaited on the device just
-        # before the GLA prefill: every byte is still copied inside the timed region
-        late = {3, 4}                                 # gla_qkv, gla_gk
+        # Copy pipeline (every byte of every timed step is copied inside the timed region):
+        #  * decode inputs (small): main stream, start of the step;
+        #  * GLA prefill inputs (half of the bytes): copy stream, underneath this step's SWA prefill,
+        #    awaited on the device just before the GLA prefill;
+        #  * SWA prefill inputs: double-buffered on the device -- the NEXT step's rows go out on the
+        #    copy stream behind the GLA inputs, underneath this step's compute (what a serving loop
+        #    does with the next batch); the first timed step has nothing to ride on and copies its
+        #    own at its start, the last one prefetches nothing.
+        swa_sets = [(swa_q, swa_k, swa_v), tuple(torch.empty_like(t) for t in (swa_q, swa_k, swa_v))]
         copy_s = torch.cuda.Stream()
         main_s = torch.cuda.current_stream()
+        swa_ready = [None, None]                      # event per device buffer set
 
-        def e2e_step():
-            for i, (hbuf, dbuf) in enumerate(zip(host_inputs, dev_inputs)):
-                if i not in late:
+        def copy_swa(which, stream):
+            with torch.cuda.stream(stream):
+                for dbuf, hbuf in zip(swa_sets[which], host_inputs[:3]):
                     dbuf.copy_(hbuf, non_blocking=True)
-            copy_s.wait_stream(main_s)                # the previous step is done with the GLA inputs
+                evt = torch.cuda.Event()
+                evt.record(stream)
+            swa_ready[which] = evt
+
+        def e2e_step(s, prefetch_next):
+            cur = s & 1
+            if swa_ready[cur] is None:                # not prefetched: copy now, on the critical path
+                copy_swa(cur, main_s)
+            for i in range(5, len(dev_inputs)):       # decode inputs
+                dev_inputs[i].copy_(host_inputs[i], non_blocking=True)
+            copy_s.wait_stream(main_s)                # the previous step is done with the shared buffers
             with torch.cuda.stream(copy_s):
-                for i in sorted(late):
+                for i in (3, 4):                      # gla_qkv, gla_gk
                     dev_inputs[i].copy_(host_inputs[i], non_blocking=True)
                 gla_ready = torch.cuda.Event()
                 gla_ready.record(copy_s)
+            if prefetch_next:
+                copy_swa(cur ^ 1, copy_s)
             idx = admit_requests()                    # host: slot manager (release + admit 64 requests)
             mp, mdd = build_prefill_md(), build_decode_md()    # host: metadata builder + H2D of its tensors
             meta_bytes[0] = md_bytes(mp) + md_bytes(mdd) + idx.numel() * 4
-            one_step(md=mp, idx=idx, before_gla=lambda: main_s.wait_event(gla_ready), fresh_md_d=mdd)
+            main_s.wait_event(swa_ready[cur])
+            swa_ready[cur] = None
+            one_step(md=mp, idx=idx, before_gla=lambda: main_s.wait_event(gla_ready), fresh_md_d=mdd,
+                     swa_in=swa_sets[cur])
             host_out[0].copy_(dout_swa, non_blocking=True)
             host_out[1].copy_(dout_gla, non_blocking=True)
-        e2e_step()
+        e2e_step(0, False)                            # warm-up: prefetches nothing for the timed steps
         barrier()
         k = max(1, args.e2e_steps)
         s2, p2 = ev(), ev()
         tw0 = time.perf_counter()
         s2.record()
-        for _ in range(k):
-            e2e_step()
+        for s in range(k):
+            e2e_step(s + 1, s + 1 < k)
         p2.record()
         barrier()
         tw1 = time.perf_counter()
@@ -541,7 +563,9 @@ def run_gpu(args):
                "d2h_bytes_per_step": d2h, "steps": k, "ms_per_step": el / k * 1e3,
                "wall_ms_per_step": (tw1 - tw0) / k * 1e3,
                "note": "per step: activations (one layer-set of q/k/v and qkv/gk rows, decode inputs) copied "
-                       "from pinned host memory (GLA inputs on a copy stream under the SWA prefill); slot "
+                       "from pinned host memory inside the timed region (GLA inputs on a copy stream under the SWA "
+                       "prefill; the next step's SWA inputs double-buffered under this step's compute, the "
+                       "first timed step's on its critical path); slot "
                        "manager admits/releases the requests; MetaAttentionMetadataBuilder builds prefill and "
                        "decode metadata on the host and ships it; MetaAttentionImpl.forward / "
                        "GatedLinearAttention.forward per layer; last decode outputs read back"}
@@ -555,7 +579,7 @@ def run_gpu(args):
     if not args.no_extra:
         del swa_q, swa_k, swa_v, gla_qkv, gla_gk, out_swa, kv_caches
         if not args.no_e2e:
-            del dev_inputs, host_inputs
+            del dev_inputs, host_inputs, swa_sets
         import gc
         gc.collect()
         torch.cuda.empty_cache()
