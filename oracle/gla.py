@@ -237,9 +237,9 @@ def rms_norm_tp(x: torch.Tensor, weight: torch.Tensor, eps: float, tp_world: int
     """``HymetaRMSNormTP._forward`` (vllm_hymeta/models/modeling_hymeta.py:151-173) restated:
     fp32 x, variance = mean over the LOCAL hidden slice, summed over the tensor-parallel ranks by
     ``all_reduce`` and divided by tp_world, x * rsqrt(var + eps), cast back to the input dtype, times
-    the rank's fp32 weight slice (result promoted to fp32).  PARITY UNPINNED: the class imports vLLM
-    (not importable here) and its HF twin uses fla's RMSNorm (hf_model/modeling_hymeta.py:25,86-87),
-    so this follows the source text only."""
+    the rank's fp32 weight slice (result promoted to fp32).  Pinned bit-exactly to the unmodified
+    class at TP world 1 / 2 / 4 (tests/golden/hymeta_rmsnorm_tp.npz, made by oracle/make_golden.py
+    with the vLLM names the module imports stubbed; tests/test_oracle_golden.py)."""
     orig = x.dtype
     xf = x.to(torch.float32)
     var = xf.pow(2).mean(dim=-1, keepdim=True, dtype=torch.float32)

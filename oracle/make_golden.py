@@ -195,6 +195,128 @@ def golden_rope():
                         pos=pos[0].numpy(), qe=f32(qe[0]), ke=f32(ke[0]))
 
 
+def _import_reference_model_module():
+    """``vllm_hymeta.models.modeling_hymeta`` imported UNMODIFIED.  It is written against vLLM
+    0.10.0; the vLLM installed here (0.22) has moved or dropped most of what it imports, so every
+    ``vllm.*`` / ``fla.*`` name it asks for that does not resolve is satisfied by a stub (third-party
+    symbols only: ``CustomOp`` becomes ``torch.nn.Module``, everything else an inert placeholder).
+    The reference's own classes and arithmetic run as written."""
+    import importlib
+    import importlib.abc
+    import importlib.machinery
+    import types
+
+    class _AnyMeta(type):
+        def __getattr__(cls, name):
+            if name.startswith("__"):
+                raise AttributeError(name)
+            return name
+
+    class _AnyObj:
+        def __getattr__(self, name):
+            if name.startswith("__"):
+                raise AttributeError(name)
+            return _AnyObj()
+
+        def __call__(self, *a, **k):
+            return None
+
+    class _Stub(types.ModuleType):
+        __path__ = []
+
+        def __getattr__(self, name):
+            if name.startswith("__"):
+                raise AttributeError(name)
+            if name == "CustomOp":
+                obj = torch.nn.Module
+            elif name[:1].islower():      # functions / singletons (direct_register_custom_op, current_platform): inert
+                obj = _AnyObj()
+            else:                         # classes / enums: any class attribute resolves, any call constructs
+                obj = _AnyMeta(name, (), {"__init__": lambda self, *a, **k: None})
+            setattr(self, name, obj)
+            return obj
+
+    class _Finder(importlib.abc.MetaPathFinder, importlib.abc.Loader):
+        def find_spec(self, fullname, path=None, target=None):
+            if fullname.split(".")[0] in ("vllm", "fla", "flash_attn"):
+                return importlib.machinery.ModuleSpec(fullname, self, is_package=True)
+            return None
+
+        def create_module(self, spec):
+            return _Stub(spec.name)
+
+        def exec_module(self, module):
+            pass
+
+    saved = {k: v for k, v in sys.modules.items() if k.split(".")[0] in ("vllm", "fla", "flash_attn")}
+    for k in saved:
+        del sys.modules[k]
+    finder = _Finder()
+    sys.meta_path.insert(0, finder)     # ahead of the real vllm: the module only needs names to exist
+    try:
+        return importlib.import_module("vllm_hymeta.models.modeling_hymeta")
+    finally:
+        sys.meta_path.remove(finder)
+        for k in [k for k in sys.modules if k.split(".")[0] in ("vllm", "fla", "flash_attn")]:
+            del sys.modules[k]
+        sys.modules.update(saved)
+
+
+def golden_rmsnorm_tp():
+    """``HymetaRMSNormTP`` (modeling_hymeta.py:120-180, unmodified) at tensor-parallel world sizes
+    1, 2 and 4 -- the ranks run as threads and ``tensor_model_parallel_all_reduce`` is a barrier
+    that sums what the ranks deposit -- followed by the decoder layer's merge of the two branches
+    ``((norm1(out_attn) + norm2(out_linear)) / 2).to(bfloat16)`` (:909-917, restated here in one
+    line because it sits in the middle of the layer's forward).  Pins oracle.gla.rms_norm_tp /
+    branch_norm_merge, the checker of f1."""
+    import threading
+    mh = _import_reference_model_module()
+    gen = torch.Generator().manual_seed(17)
+    T, hidden, eps = 37, 512, 1e-6
+    x1 = (torch.randn(T, hidden, generator=gen) * 1.7).bfloat16()
+    x2 = (torch.randn(T, hidden, generator=gen) * 0.6).bfloat16()
+    w1 = 1 + 0.2 * torch.randn(hidden, generator=gen)
+    w2 = 1 + 0.2 * torch.randn(hidden, generator=gen)
+    out = {"x_attn": f32(x1), "x_linear": f32(x2), "w1": f32(w1), "w2": f32(w2), "eps": np.float32(eps)}
+    for W in (1, 2, 4):
+        barrier = threading.Barrier(W)
+        box, lock = {}, threading.Lock()
+
+        def all_reduce(v):
+            tag = all_reduce.calls[threading.get_ident()] = all_reduce.calls.get(threading.get_ident(), 0) + 1
+            with lock:
+                box.setdefault(tag, []).append(v)
+            barrier.wait()
+            tot = torch.stack(box[tag]).sum(0)
+            barrier.wait()
+            return tot
+        all_reduce.calls = {}
+        mh.tensor_model_parallel_all_reduce = all_reduce
+        mh.get_tensor_model_parallel_world_size = lambda: W
+        res = [None] * W
+
+        def run(rank):
+            mh.get_tensor_model_parallel_rank = lambda: rank
+            n1, n2 = mh.HymetaRMSNormTP(hidden, eps), mh.HymetaRMSNormTP(hidden, eps)
+            mh.HymetaRMSNormTP.weight_loader(n1.weight, w1)      # slices by the patched rank getter
+            mh.HymetaRMSNormTP.weight_loader(n2.weight, w2)
+            sl = slice(rank * hidden // W, (rank + 1) * hidden // W)
+            res[rank] = (n1, n2, sl)
+        for r in range(W):          # construction reads the rank getter: one rank at a time
+            run(r)
+
+        def fwd(rank):
+            n1, n2, sl = res[rank]
+            a = n1._forward(x1[:, sl])
+            b = n2._forward(x2[:, sl])
+            res[rank] = ((a + b) / 2).to(torch.bfloat16)
+        th = [threading.Thread(target=fwd, args=(r,)) for r in range(W)]
+        [t.start() for t in th]
+        [t.join() for t in th]
+        out[f"merged_tp{W}"] = f32(torch.cat(res, dim=1))
+    np.savez_compressed(os.path.join(OUT, "hymeta_rmsnorm_tp.npz"), **out)
+
+
 def main():
     sys.path.insert(0, REF)
     sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), ".."))
@@ -206,6 +328,7 @@ def main():
     golden_hf7b_gla_module()
     golden_hf70b_linear_module()
     golden_rope()
+    golden_rmsnorm_tp()
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))
 

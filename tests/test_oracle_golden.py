@@ -92,6 +92,24 @@ def test_gate_70b_vs_hf_module(golden):
         close(o.transpose(0, 1), g[f"{tag}_o"], 2e-5, 1e-5)
 
 
+def test_rmsnorm_tp_branch_merge_vs_reference_class(golden):
+    """f1: oracle.gla.rms_norm_tp / branch_norm_merge against the UNMODIFIED ``HymetaRMSNormTP``
+    (modeling_hymeta.py:120-180) run at TP world 1, 2 and 4 by oracle/make_golden.py (ranks as
+    threads, the all-reduce a summing barrier).  Bit-exact: same torch ops in the same order."""
+    g = golden("hymeta_rmsnorm_tp.npz")
+    x1, x2 = T(g["x_attn"]).bfloat16(), T(g["x_linear"]).bfloat16()
+    w1, w2, eps = T(g["w1"]), T(g["w2"]), float(g["eps"])
+    hidden = x1.shape[1]
+    for W in (1, 2, 4):
+        sl = [slice(r * hidden // W, (r + 1) * hidden // W) for r in range(W)]
+        # what the summing all-reduce returns: the sum over ranks of each rank's local mean of squares
+        tot1 = sum(x1[:, s].float().pow(2).mean(-1, keepdim=True, dtype=torch.float32) for s in sl)
+        tot2 = sum(x2[:, s].float().pow(2).mean(-1, keepdim=True, dtype=torch.float32) for s in sl)
+        got = torch.cat([gla.branch_norm_merge(x1[:, s], x2[:, s], w1[s], w2[s], eps, W,
+                                               (lambda v, t=tot1: t, lambda v, t=tot2: t)) for s in sl], dim=1)
+        assert torch.equal(got.float(), T(g[f"merged_tp{W}"])), W
+
+
 def test_rope_vs_hf(golden):
     g = golden("rope.npz")
     pos = T(g["pos"])

@@ -2,7 +2,7 @@
 # Run on the GPU box under gpurun: plain run first, then the ncu launch list and one --set full
 # capture per hot kernel (B200_PROFILING.md).  Outputs land in gpurun_out/.
 set -o pipefail
-CMD="python bench.py --steps 1 --warmup 1 --decode 4 --no-e2e --no-cpu-baseline"
+CMD="python bench.py --steps 1 --warmup 1 --decode 4 --no-e2e --no-cpu-baseline --no-extra"
 mkdir -p gpurun_out
 $CMD > gpurun_out/plain.log 2>&1 || { echo "plain run failed"; tail -20 gpurun_out/plain.log; exit 1; }
 ncu --metrics gpu__time_duration.sum --clock-control none -c 800 --csv \
