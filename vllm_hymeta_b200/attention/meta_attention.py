@@ -357,8 +357,7 @@ class MetaAttentionMetadataBuilder:
             if bt:
                 n = min(len(bt), max_blocks)      # look-ahead blocks beyond the graph width are unused
                 g[i, :n] = bt[:n]
-        t = torch.from_numpy(g) if not isinstance(g, torch.Tensor) else g
-        return t.to(device=self.device, non_blocking=True)
+        return self._h2d(g if isinstance(g, np.ndarray) else g.numpy(), torch.int32)
 
     def _h2d(self, data, dtype):
         pin = self.pin_memory and torch.cuda.is_available()
@@ -397,8 +396,7 @@ class MetaAttentionMetadataBuilder:
         else:
             width = max((len(b) for b in self.block_tables), default=0)
             rows = [b + [0] * (width - len(b)) for b in self.block_tables]
-            block_tables = torch.tensor(rows, dtype=torch.int32).reshape(len(rows), width).to(
-                self.device, non_blocking=True)
+            block_tables = self._h2d(np.asarray(rows, dtype=np.int32).reshape(len(rows), width), torch.int32)
         assert max_query_len > 0, "query_lens: {}".format(query_lens)
         return MetaAttentionMetadata(
             num_prefills=self.num_prefills, slot_mapping=self._h2d(slot_mapping, torch.long),

@@ -46,15 +46,22 @@ class GLACacheManager(NativeSlotAllocator):
         if not slots:
             return
         from .. import ops
-        ops.state_zero_slots(self._gla_cache, torch.tensor(slots, dtype=torch.int32,
-                                                           device=self._gla_cache.device))
+        ops.state_zero_slots(self._gla_cache, self._to_device(slots))
+
+    def _to_device(self, slots: List[int], stage_only: bool = False) -> torch.Tensor:
+        """Slot indices -> int32 device tensor through PINNED staging memory: a copy from pageable
+        memory makes the driver synchronise the stream first, which would serialise the host side of
+        the next step behind the whole GPU step in flight."""
+        dev = self._gla_cache.device
+        pin = dev.type == "cuda"
+        t = torch.tensor(slots, dtype=torch.int32, pin_memory=pin)
+        return t if stage_only else t.to(dev, non_blocking=True)
 
     def current_run_tensors(self, **kwargs):
         if "seqlen_agnostic_capture_inputs" not in kwargs:
             slots = self.prepare(kwargs["request_ids_to_seq_ids"], kwargs["finished_requests_ids"],
                                  self._copy_cache)
-            idx = torch.as_tensor(slots, dtype=torch.int32, device=self._gla_cache.device)
-            return self._gla_cache, idx
+            return self._gla_cache, self._to_device(slots)
         return kwargs["seqlen_agnostic_capture_inputs"]
 
     def copy_inputs_before_cuda_graphs(self, input_buffers, **kwargs):
@@ -63,8 +70,7 @@ class GLACacheManager(NativeSlotAllocator):
         _, idx_buf = input_buffers["seqlen_agnostic_capture_inputs"]
         pad = idx_buf.numel() - len(slots)
         assert pad >= 0
-        idx_buf.copy_(torch.as_tensor(slots + [PAD_SLOT_ID] * pad, dtype=torch.int32),
-                      non_blocking=True)
+        idx_buf.copy_(self._to_device(slots + [PAD_SLOT_ID] * pad, stage_only=True), non_blocking=True)
 
     def get_seqlen_agnostic_capture_inputs(self, batch_size):
         return self._gla_cache, torch.as_tensor([PAD_SLOT_ID] * batch_size, dtype=torch.int32,

@@ -58,6 +58,14 @@ class HymetaCacheManager(NativeSlotAllocator):
         from .. import ops
         ops.state_copy_slot(self._hymeta_cache[0], from_index, to_index)
 
+    def _to_device(self, slots: List[int], stage_only: bool = False) -> torch.Tensor:
+        """Slot indices -> int32 device tensor through PINNED staging memory (a copy from pageable
+        memory makes the driver synchronise the stream first, serialising the host side of the next
+        step behind the GPU step in flight)."""
+        dev = self._hymeta_cache[0].device
+        t = torch.tensor(slots, dtype=torch.int32, pin_memory=dev.type == "cuda")
+        return t if stage_only else t.to(dev, non_blocking=True)
+
     def clear_slots(self, slots: List[int]) -> None:
         """Zero the states of newly admitted requests (reference ``_clear_prefill_cache``,
         modeling_hymeta.py:1202-1227) with one launch over all layers."""
@@ -65,7 +73,7 @@ class HymetaCacheManager(NativeSlotAllocator):
             return
         from .. import ops
         state = self._hymeta_cache[0]
-        ops.state_zero_slots(state, torch.tensor(slots, dtype=torch.int32, device=state.device))
+        ops.state_zero_slots(state, self._to_device(slots))
 
     def current_run_tensors(self, **kwargs):
         """-> (state, meta_linear, meta_fattn, state_indices[B] int32).  Outside CUDA graphs the
@@ -75,7 +83,7 @@ class HymetaCacheManager(NativeSlotAllocator):
         if "seqlen_agnostic_capture_inputs" not in kwargs:
             slots = self.prepare(kwargs["request_ids_to_seq_ids"], kwargs["finished_requests_ids"],
                                  self._copy_cache)
-            idx = torch.as_tensor(slots, dtype=torch.int32, device=self._hymeta_cache[0].device)
+            idx = self._to_device(slots)
             c = self._hymeta_cache
         else:
             c, idx = kwargs["seqlen_agnostic_capture_inputs"]
@@ -89,7 +97,7 @@ class HymetaCacheManager(NativeSlotAllocator):
         _, idx_buf = input_buffers["seqlen_agnostic_capture_inputs"]
         pad = idx_buf.numel() - len(slots)
         assert pad >= 0, "captured batch smaller than the live batch"
-        idx_buf.copy_(torch.as_tensor(slots + [PAD_SLOT_ID] * pad, dtype=torch.int32),
+        idx_buf.copy_(self._to_device(slots + [PAD_SLOT_ID] * pad, stage_only=True),
                       non_blocking=True)
 
     def get_seqlen_agnostic_capture_inputs(self, batch_size):
