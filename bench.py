@@ -520,29 +520,48 @@ def run_gpu(args):
                 evt.record(stream)
             swa_ready[which] = evt
 
+        dbg = os.environ.get("HYMETA_BENCH_DEBUG") == "1"
+        dbg_rec, dbg_copy = [], []
+
         def e2e_step(s, prefetch_next):
+            th = [time.perf_counter()]
             cur = s & 1
             if swa_ready[cur] is None:                # not prefetched: copy now, on the critical path
                 copy_swa(cur, main_s)
             for i in range(5, len(dev_inputs)):       # decode inputs
                 dev_inputs[i].copy_(host_inputs[i], non_blocking=True)
+            th.append(time.perf_counter())
+            idx = admit_requests()                    # host: slot manager (release + admit 64 requests)
+            th.append(time.perf_counter())
+            mp, mdd = build_prefill_md(), build_decode_md()    # host: metadata builder + H2D of its tensors
+            th.append(time.perf_counter())
+            meta_bytes[0] = md_bytes(mp) + md_bytes(mdd) + idx.numel() * 4
+            # the bulk copies are enqueued AFTER the step's small ones (decode inputs, metadata, slot
+            # indices): all host->device copies share one DMA queue, and a 4 MB metadata copy enqueued
+            # behind 10 GB of activations held the step's first kernel back by ~180 ms
             copy_s.wait_stream(main_s)                # the previous step is done with the shared buffers
             with torch.cuda.stream(copy_s):
+                c0 = ev(); c0.record(copy_s)
                 for i in (3, 4):                      # gla_qkv, gla_gk
                     dev_inputs[i].copy_(host_inputs[i], non_blocking=True)
-                gla_ready = torch.cuda.Event()
+                gla_ready = ev()
                 gla_ready.record(copy_s)
             if prefetch_next:
                 copy_swa(cur ^ 1, copy_s)
-            idx = admit_requests()                    # host: slot manager (release + admit 64 requests)
-            mp, mdd = build_prefill_md(), build_decode_md()    # host: metadata builder + H2D of its tensors
-            meta_bytes[0] = md_bytes(mp) + md_bytes(mdd) + idx.numel() * 4
+            if dbg:
+                c2 = ev(); c2.record(copy_s)
+                dbg_copy.append((c0, gla_ready, c2))
             main_s.wait_event(swa_ready[cur])
             swa_ready[cur] = None
-            one_step(md=mp, idx=idx, before_gla=lambda: main_s.wait_event(gla_ready), fresh_md_d=mdd,
-                     swa_in=swa_sets[cur])
+            one_step(rec=dbg_rec if dbg else None, md=mp, idx=idx,
+                     before_gla=lambda: main_s.wait_event(gla_ready), fresh_md_d=mdd, swa_in=swa_sets[cur])
+            th.append(time.perf_counter())
             host_out[0].copy_(dout_swa, non_blocking=True)
             host_out[1].copy_(dout_gla, non_blocking=True)
+            th.append(time.perf_counter())
+            if dbg and rank == 0:
+                sys.stderr.write("e2e host ms: copies %.1f  slot mgr %.1f  metadata %.1f  launches %.1f  d2h %.1f\n" %
+                                 tuple((b - a) * 1e3 for a, b in zip(th, th[1:])))
         e2e_step(0, False)                            # warm-up: prefetches nothing for the timed steps
         barrier()
         k = max(1, args.e2e_steps)
@@ -555,6 +574,18 @@ def run_gpu(args):
         barrier()
         tw1 = time.perf_counter()
         el = s2.elapsed_time(p2) * 1e-3
+        if dbg and rank == 0:
+            gb = lambda idxs: sum(dev_inputs[i].numel() * 2 for i in idxs) / 1e9
+            for (e, marks), (c0, c1, c2) in zip(dbg_rec, dbg_copy):
+                sys.stderr.write("e2e copy stream: starts %.1f ms after the step's first kernel; GLA inputs %.1f ms "
+                                 "(%.1f GB/s); next SWA inputs %.1f ms (%.1f GB/s)\n" %
+                                 (ms(e[0], c0), ms(c0, c1), gb((3, 4)) / max(ms(c0, c1), 1e-3) * 1e3, ms(c1, c2),
+                                  gb((0, 1, 2)) / max(ms(c1, c2), 1e-3) * 1e3))
+            for e, marks in dbg_rec:
+                sys.stderr.write("e2e gpu ms: swa prefill %.1f  gla prefill (incl. input wait) %.1f  decode %.1f "
+                                 "(swa %.1f gla %.1f)\n" % (ms(e[0], e[1]), ms(e[1], e[2]), ms(e[2], e[3]),
+                                                           sum(ms(a, b) for a, b, c in marks),
+                                                           sum(ms(b, c) for a, b, c in marks)))
         if world > 1:
             t = torch.tensor([el], device=dev)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
