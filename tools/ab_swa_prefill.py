@@ -28,9 +28,16 @@ def lib_path(tag):
 
 def build(tag, defs, src="swa_prefill"):
     obj = os.path.join(BUILD, f"ab_{tag}.o")
+    flags = defs.split()
+    fast = [] if "-PRECISE" in flags else ["--use_fast_math"]     # "-PRECISE": as __graft_entry__.PRECISE_SOURCES
+    flags = [f for f in flags if f != "-PRECISE"]
+    srcfile = os.path.join(CSRC, src + ".cu")
+    for f in list(flags):                                          # "-SRC=path": compile another copy of the source
+        if f.startswith("-SRC="):
+            srcfile = f[5:]
+            flags.remove(f)
     cmd = ["nvcc", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
-           "--use_fast_math", "-Xcompiler", "-fPIC", "-Xptxas", "-v", *defs.split(), "-c",
-           os.path.join(CSRC, src + ".cu"), "-o", obj]
+           *fast, "-Xcompiler", "-fPIC", "-Xptxas", "-v", "-I", CSRC, *flags, "-c", srcfile, "-o", obj]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode:
         sys.exit(r.stderr)

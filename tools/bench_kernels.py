@@ -62,7 +62,8 @@ def time_graph(fns, reps=5):
     return ts[len(ts) // 2] * 1e-3 / len(fns)
 
 
-def bench_gla_decode(B, H=28, Hkv=4, D=128, layout="compact", gdt=torch.bfloat16, flush=None):
+def bench_gla_decode(B, H=28, Hkv=4, D=128, layout="compact", gdt=torch.bfloat16, flush=None, mode="plain"):
+    """mode: plain | gn (g_norm epilogue) | gate (g_norm + the 7B feature map / gate on raw rows)"""
     dev = "cuda"
     Hs = Hkv if layout == "compact" else H
     Hk = Hkv if layout == "compact" else H
@@ -78,10 +79,12 @@ def bench_gla_decode(B, H=28, Hkv=4, D=128, layout="compact", gdt=torch.bfloat16
         state = torch.zeros(B, Hs, D, D, device=dev, dtype=torch.bfloat16)
         slots = torch.randperm(B, device=dev).to(torch.int32)
         out = torch.empty(B, H, D, device=dev, dtype=torch.bfloat16)
+        gw = torch.ones(D, device=dev, dtype=torch.bfloat16) if mode != "plain" else None
+        gate = 16.0 if mode == "gate" else None
         fns.append(lambda q=q, k=k, v=v, g=g, state=state, slots=slots, out=out:
-                   ops.gla_decode(q, k, v, g, state, slots, out=out))
+                   ops.gla_decode(q, k, v, g, state, slots, out=out, gnorm_weight=gw, gate_normalizer=gate))
     t = time_graph(fns)
-    print(f"gla_decode B={B} layout={layout}: {t*1e6:8.1f} us  {alg/t/1e9:8.1f} GB/s "
+    print(f"gla_decode[{mode}] B={B} layout={layout}: {t*1e6:8.1f} us  {alg/t/1e9:8.1f} GB/s "
           f"({alg/t/1e9/PEAK:.2%} of measured {PEAK:.0f})  alg={alg/1e6:.1f} MB  [graph of {nrot} rotating buffers]")
 
 
@@ -242,7 +245,8 @@ if __name__ == "__main__":
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
     if a.which in ("all", "gla_decode"):
         for B in (64, 256, 1000):
-            bench_gla_decode(B, flush=flush)
+            for mode in ("plain", "gn", "gate"):
+                bench_gla_decode(B, flush=flush, mode=mode)
         bench_gla_decode(64, layout="reference", flush=flush)
         bench_gla_decode(1000, layout="reference", gdt=torch.float32, flush=flush)
     if a.which in ("all", "swa_decode"):

@@ -10,7 +10,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "csrc", "libhymeta_b200.so")
+# HYMETA_B200_LIB: development override (A/B builds of the kernel library, tools/ab_swa_prefill.py)
+LIB_PATH = os.environ.get("HYMETA_B200_LIB") or os.path.join(_HERE, "csrc", "libhymeta_b200.so")
 
 _i, _i64, _f, _p, _sz = C.c_int, C.c_int64, C.c_float, C.c_void_p, C.c_size_t
 

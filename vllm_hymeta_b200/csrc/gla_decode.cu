@@ -19,6 +19,10 @@
 
 #include <cstdlib>
 
+// libdevice's accurate single-precision functions (what expf / log1pf resolve to without fast-math)
+extern "C" __device__ float __nv_expf(float);
+extern "C" __device__ float __nv_log1pf(float);
+
 namespace hymeta {
 
 struct GlaDecodeParams {
@@ -35,8 +39,10 @@ struct GlaDecodeParams {
   float gnorm_eps;
   // > 0: q, k and g are the RAW projection outputs of the 7B layer and the feature map + gate
   // (model_for_7B/gla_attention.py:251-262) run here: q = relu(q), k = relu(k),
-  // g = bf16(bf16(logsigmoid(gk)) / gate_norm) -- bit-identical to hymeta_gla_gate_7b's outputs
-  // (this file is compiled without --use_fast_math for that; the decay keeps the fast __expf)
+  // g = bf16(bf16(logsigmoid(gk)) / gate_norm) -- bit-identical to hymeta_gla_gate_7b's outputs: this
+  // file is compiled with --use_fast_math, so the gate calls libdevice's accurate expf / log1pf and
+  // the IEEE division by name (flush-to-zero only matters where exp(-|x|) is denormal, and there
+  // log1p of it vanishes against x either way)
   float gate_norm;
 };
 
@@ -196,8 +202,8 @@ __global__ void __launch_bounds__(GD_THREADS, 2) gla_decode_kernel(const GlaDeco
         if (!GF32 && gate) {
           // logsigmoid(x) = min(x, 0) - log1p(exp(-|x|)) (ATen), rounded to bf16 before the division
           // and again after it -- exactly what hymeta_gla_gate_7b stores (gla_gate.cu)
-          const float ls = fminf(gv, 0.f) - log1pf(expf(-fabsf(gv)));
-          gv = round_bf16(round_bf16(ls) / p.gate_norm);
+          const float ls = fminf(gv, 0.f) - __nv_log1pf(__nv_expf(-fabsf(gv)));
+          gv = round_bf16(__fdiv_rn(round_bf16(ls), p.gate_norm));
         }
         s_kg[row].y = __float_as_uint(__expf(gv));
       }
