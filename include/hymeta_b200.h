@@ -392,6 +392,23 @@ int hymeta_branch_norm_merge(const void* x_attn, const void* x_linear, const flo
                              int hidden_local, int tp_world, float eps, int64_t xa_st,
                              int64_t xl_st, int64_t o_st, void* stream);
 
+/* f1, tensor-parallel form in ONE kernel (compute -> exchange over NVLink peer memory -> merge; replaces
+ * hymeta_branch_sumsq + the caller's all-reduce + hymeta_branch_norm_merge at tp_world >= 2):
+ * every rank owns an exchange buffer of hymeta_branch_merge_tp_buffer_bytes(tp_world, t_cap) bytes,
+ * zero-filled once, mapped into every peer (CUDA IPC / symmetric memory); peer_buffers is a HOST array
+ * of the tp_world device addresses, indexed by rank, as seen from this process.  A warp reduces a row,
+ * stores {mean_attn, epoch, mean_linear, epoch} into each peer's buffer with one 16-byte store, polls
+ * its own buffer for the peers' slots of that row, sums the means in rank order and finishes the row
+ * (its second touch is an L2 hit: x is read from DRAM once).  epoch: any non-zero value that changes by one between consecutive
+ * calls on the group (two slot parities); every rank passes the same T, hidden_local and epoch.  All
+ * CTAs are co-resident (grid <= SMs x occupancy).  A peer that never arrives traps after ~4M polls. */
+size_t hymeta_branch_merge_tp_buffer_bytes(int tp_world, int64_t t_cap);
+int hymeta_branch_norm_merge_tp(const void* x_attn, const void* x_linear, const float* w_attn,
+                                const float* w_linear, void* out, int T, int hidden_local,
+                                int tp_world, int tp_rank, const uint64_t* peer_buffers,
+                                int64_t t_cap, uint32_t epoch, float eps, int64_t xa_st,
+                                int64_t xl_st, int64_t o_st, void* stream);
+
 /* ------------------------------------------------------------------------------------------------
  * f4  Host-side state-slot manager -- replaces the bookkeeping of vLLM 0.10.0's ConstantSizeCache
  *     inherited by HymetaCacheManager / GLACacheManager (vllm_hymeta/models/hymeta_cache.py:24-63,

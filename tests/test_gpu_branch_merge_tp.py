@@ -1,0 +1,78 @@
+"""f1 at tensor-parallel world size 2 on real GPUs (skips on a single-GPU box): the fused
+compute -> NVLink exchange -> merge kernel (``hymeta_branch_norm_merge_tp`` through
+``ops.branch_norm_merge(exchange=...)``) and the NCCL form (``branch_sumsq`` + all-reduce + merge)
+against the oracle's HymetaRMSNormTP restatement on every rank's hidden slice."""
+import os
+import sys
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _worker(rank: int, world: int, port: int, q):
+    try:
+        sys.path.insert(0, ROOT)
+        import torch.distributed as dist
+        from oracle import gla as ogla                      # checker only
+        from vllm_hymeta_b200 import ops
+        torch.cuda.set_device(rank)
+        dist.init_process_group("nccl", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world,
+                                device_id=torch.device("cuda", rank))
+        eps = 1e-6
+        ex = ops.BranchMergeExchange(None, t_cap=4096)
+        worst = 0.0
+        for T, hidden in ((1, 3584), (257, 3584), (4096, 3584), (64, 2048)):
+            gen = torch.Generator().manual_seed(T)           # same data on every rank
+            xa = (torch.randn(T, hidden, generator=gen) * 3).bfloat16()
+            xl = (torch.randn(T, hidden, generator=gen) * 0.2).bfloat16()
+            w1 = 1 + 0.1 * torch.randn(hidden, generator=gen)
+            w2 = 1 + 0.1 * torch.randn(hidden, generator=gen)
+            hl = hidden // world
+            sl = [slice(r * hl, (r + 1) * hl) for r in range(world)]
+            s = sl[rank]
+            tot = [sum(x[:, qq].float().pow(2).mean(-1, keepdim=True, dtype=torch.float32) for qq in sl)
+                   for x in (xa, xl)]
+            ref = ogla.branch_norm_merge(xa[:, s], xl[:, s], w1[s], w2[s], eps, world,
+                                         (lambda v: tot[0], lambda v: tot[1]))
+            dxa, dxl = xa[:, s].cuda().contiguous(), xl[:, s].cuda().contiguous()
+            dw1, dw2 = w1[s].cuda().contiguous(), w2[s].cuda().contiguous()
+            for rep in range(3):                             # epochs advance, both slot parities get used
+                fused = ops.branch_norm_merge(dxa, dxl, dw1, dw2, eps, tp_world=world, exchange=ex)
+            nccl = ops.branch_norm_merge(dxa, dxl, dw1, dw2, eps, tp_world=world)
+            torch.cuda.synchronize()
+            for name, got in (("fused", fused), ("nccl", nccl)):
+                diff = (got.float().cpu() - ref.float()).abs()
+                bad = int((diff > 2.0 ** -6 * ref.float().abs().clamp(min=1.0)).sum())
+                assert bad == 0, (name, T, hidden, bad, diff.max().item())
+                worst = max(worst, diff.max().item())
+            # world 2: a + b in either order is the same float, so the two forms agree bit for bit
+            if world == 2:
+                assert torch.equal(fused, nccl), (T, hidden)
+        dist.barrier()
+        dist.destroy_process_group()
+        q.put((rank, "ok", worst))
+    except Exception as e:  # pragma: no cover - reported to the parent
+        import traceback
+        q.put((rank, "fail", traceback.format_exc()))
+
+
+def test_branch_merge_tp2_fused_and_nccl():
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29500 + os.getpid() % 1000
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = []
+    for _ in procs:
+        res.append(q.get(timeout=300))
+    for p in procs:
+        p.join(timeout=60)
+    for rank, status, info in res:
+        assert status == "ok", f"rank {rank}:\n{info}"

@@ -92,13 +92,12 @@ def config3(plan, world, tp_group, prompts, T, iters):
         ops.rope_kv_write_paged(sq, sk, sv, table, pos, M, kv[0], kv[1], slot_map)
         o_swa = ops.swa_meta_prefill_varlen(sq, sk, sv, None, mk, mv, cu, cu, T, 4095)
         xa, xl = o_swa.view(Tt, h * D), o_gla.view(Tt, h * D)
-        if tp > 1:
-            ops.branch_sumsq(xa, xl, out=means)
-            dist.all_reduce(means, group=tp_group)
-            ops.branch_norm_merge(xa, xl, w1, w2, 1e-6, tp_world=tp, means=means, out=out)
+        if tp > 1:     # one kernel: local means -> NVLink peer-memory exchange -> merge (f1)
+            ops.branch_norm_merge(xa, xl, w1, w2, 1e-6, tp_world=tp, out=out, exchange=exchange)
         else:
             ops.branch_norm_merge(xa, xl, w1, w2, 1e-6, out=out)
 
+    exchange = ops.BranchMergeExchange(tp_group, t_cap=Tt) if tp > 1 else None
     t = timed(layer, iters, 2, world)
     parts = {}
     parts["gla (gate+prefill)"] = timed(lambda: ops.gla_prefill_varlen(

@@ -262,12 +262,11 @@ def extra_configs(dev="cuda", world=1, rank=0, tp_group=None, plan=None):
         ops.rope_kv_write_paged(sq, sk, sv, table, pos, M, kv[0], kv[1], slot_map)
         ops.swa_meta_prefill_varlen(sq, sk, sv, None, mk, mv, cu, cu, T, 4095, out=o_swa)
         xa, xl = o_swa.view(Tt, h * D), o_gla.view(Tt, h * D)
-        if tp > 1:
-            ops.branch_sumsq(xa, xl, out=means)
-            dist.all_reduce(means, group=tp_group)
-            ops.branch_norm_merge(xa, xl, w1, w2, 1e-6, tp_world=tp, means=means, out=merged)
+        if tp > 1:     # one kernel: local means -> NVLink peer-memory exchange -> merge (f1)
+            ops.branch_norm_merge(xa, xl, w1, w2, 1e-6, tp_world=tp, out=merged, exchange=exchange)
         else:
             ops.branch_norm_merge(xa, xl, w1, w2, 1e-6, out=merged)
+    exchange = ops.BranchMergeExchange(tp_group, t_cap=Tt) if tp > 1 else None
     if world > 1:
         dist.barrier()
     t = tmax(_time(layer, 3, 1))
@@ -275,7 +274,7 @@ def extra_configs(dev="cuda", world=1, rank=0, tp_group=None, plan=None):
     out["config3_70b_hybrid_layer_32k"] = {
         "plan": f"tp{plan.tp} x dp{plan.dp}", "heads_per_gpu": [h, hkv], "prompts": plan.dp * P, "prompt_len": T,
         "meta_tokens": M, "layer_ms": t * 1e3, "tok_s_per_layer": plan.dp * Tt / t,
-        "exchange": "one all-reduce of 8*T bytes per layer (f1)" if tp > 1 else "none",
+        "exchange": "fused branch-merge kernel: 16 B per token and peer over NVLink peer memory (f1)" if tp > 1 else "none",
         "swa_flops_per_gpu": P * h * 4 * D * n_keys}
     del qkv_g, qkv_s, kv, o_gla, o_swa, merged, slot_map
     torch.cuda.empty_cache()

@@ -21,7 +21,7 @@ def main():
     torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", 0)))
     if world > 1:
         dist.init_process_group("nccl")
-    T, hidden, eps = 4096, 3584, 1e-6
+    T, hidden, eps = int(os.environ.get("BM_T", "65536")), 3584, 1e-6
     gen = torch.Generator().manual_seed(0)           # same data on every rank
     xa = (torch.randn(T, hidden, generator=gen) * 3).bfloat16()
     xl = (torch.randn(T, hidden, generator=gen) * 0.2).bfloat16()
@@ -36,6 +36,13 @@ def main():
     dxa, dxl = xa[:, s].cuda().contiguous(), xl[:, s].cuda().contiguous()
     dw1, dw2 = w1[s].cuda().contiguous(), w2[s].cuda().contiguous()
     got = ops.branch_norm_merge(dxa, dxl, dw1, dw2, eps, tp_world=world)      # all-reduce inside
+    ex = ops.BranchMergeExchange(None, t_cap=T) if world > 1 else None
+    if ex is not None:
+        fused = ops.branch_norm_merge(dxa, dxl, dw1, dw2, eps, tp_world=world, exchange=ex)
+        torch.cuda.synchronize()
+        dfu = (fused.float() - got.float()).abs().max().item()
+        if rank == 0:
+            print(f"fused NVLink-exchange kernel vs NCCL form: max|d| = {dfu:.3e}", flush=True)
     torch.cuda.synchronize()
     diff = (got.float().cpu() - ref.float()).abs()
     bad = int((diff > 2.0 ** -6 * ref.float().abs().clamp(min=1.0)).sum())
@@ -56,7 +63,26 @@ def main():
     if world > 1:
         dist.all_reduce(us, op=dist.ReduceOp.MAX)
     print(f"rank {rank}/{world}: slice [{s.start}:{s.stop}] bad={bad} differing={neq:.3%} "
-          f"merge+exchange {us.item():.1f} us (max over ranks, T={T})", flush=True)
+          f"sumsq + NCCL all-reduce + merge {us.item():.1f} us (max over ranks, T={T})", flush=True)
+    if ex is not None:
+        for Tn in (64, 4096, T):
+            for name, fn in (("NCCL form ", lambda: ops.branch_norm_merge(dxa[:Tn], dxl[:Tn], dw1, dw2, eps, tp_world=world)),
+                             ("fused form", lambda: ops.branch_norm_merge(dxa[:Tn], dxl[:Tn], dw1, dw2, eps, tp_world=world,
+                                                                          exchange=ex))):
+                for _ in range(3):
+                    fn()
+                dist.barrier()
+                torch.cuda.synchronize()
+                ev0.record()
+                for _ in range(20):
+                    fn()
+                ev1.record()
+                torch.cuda.synchronize()
+                u = torch.tensor([ev0.elapsed_time(ev1) / 20 * 1e3], device="cuda")
+                dist.all_reduce(u, op=dist.ReduceOp.MAX)
+                if rank == 0:
+                    by = Tn * hl * 2 * 3
+                    print(f"  T={Tn:6d} {name}: {u.item():8.1f} us  ({by / u.item() / 1e3:7.1f} GB/s of 2R+1W per GPU)", flush=True)
     ok = torch.tensor([int(bad == 0 and neq <= 0.02)], device="cuda")
     if world > 1:
         dist.all_reduce(ok, op=dist.ReduceOp.MIN)

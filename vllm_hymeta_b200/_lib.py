@@ -48,6 +48,8 @@ SIGNATURES = {
     "hymeta_selftest_umma": (_i, [_p]),
     "hymeta_branch_sumsq": (_i, [_p, _p, _p, _i, _i, _i64, _i64, _p]),
     "hymeta_branch_norm_merge": (_i, [_p] * 6 + [_i, _i, _i, _f, _i64, _i64, _i64, _p]),
+    "hymeta_branch_merge_tp_buffer_bytes": (_sz, [_i, _i64]),
+    "hymeta_branch_norm_merge_tp": (_i, [_p] * 5 + [_i] * 4 + [_p, _i64, C.c_uint32, _f, _i64, _i64, _i64, _p]),
     "hymeta_slot_mgr_create": (_p, [_i]),
     "hymeta_slot_mgr_destroy": (None, [_p]),
     "hymeta_slot_mgr_release": (_i, [_p, _p, _i]),

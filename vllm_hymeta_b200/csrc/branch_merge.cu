@@ -183,6 +183,128 @@ branch_norm_merge_reg_kernel(const __nv_bfloat16* x1, const __nv_bfloat16* x2, c
   }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Tensor-parallel form, ONE kernel: local mean of squares -> exchange over NVLink peer memory ->
+// normalise + merge (x is read from DRAM once: the second touch of a row, a few microseconds after
+// the first, is an L2 hit).
+//
+// Exchange = the low-latency flag-in-data protocol: every rank owns a peer-mapped buffer
+//   uint4 slots[2 parities][world][t_cap]     slot = {mean_attn bits, epoch, mean_linear bits, epoch}
+// and a warp that has reduced row t writes its slot [epoch & 1][rank][t] INTO EVERY PEER'S buffer with
+// one 16-byte store (each 8-byte half carries its own epoch, so a torn store is still detected), then
+// polls the peers' slots for row t in its OWN buffer until their epochs match.  No fence, no separate
+// flag, no grid-wide synchronisation: rows are independent, and the warps in flight on an SM hide the
+// ~3 us NVLink round trip.  The sum over ranks is taken in rank order on every rank (bit-identical
+// variance everywhere).  Two parities: a peer may start call n+1 (and overwrite its slots) while this
+// rank still reads call n, but cannot reach call n+2 before this rank has finished call n+1.
+struct TpPeers { uint4* buf[8]; };
+
+constexpr int TP_K = 4;   // rows per warp between "push" and "poll": the exchange latency of a row is
+                          // covered by the other rows' loads; the second touch of the rows hits L2
+
+__global__ void __launch_bounds__(128)
+branch_norm_merge_tp_kernel(const __nv_bfloat16* x1, const __nv_bfloat16* x2,
+                            const float* __restrict__ w1, const float* __restrict__ w2,
+                            __nv_bfloat16* out, int T, int hidden, int world, int rank, uint32_t epoch,
+                            int64_t t_cap, const TpPeers peers, float eps, int64_t x1_st, int64_t x2_st,
+                            int64_t o_st) {
+  const int lane = threadIdx.x & 31, wpb = blockDim.x >> 5;
+  const int chunks = hidden / 8;
+  const float inv = 1.f / (float)hidden, inv_tp = 1.f / (float)world;
+  const int64_t par = (int64_t)(epoch & 1u) * world;
+  // lane r < world talks to rank r: where my slot lives in r's buffer, where r's slot lives in mine
+  uint4* push = nullptr;
+  const uint4* poll = nullptr;
+  if (lane < world && lane != rank) {
+    push = peers.buf[lane] + (par + rank) * t_cap;
+    poll = peers.buf[rank] + (par + lane) * t_cap;
+  }
+  const int stride = gridDim.x * wpb;
+  for (int t0 = blockIdx.x * wpb + (threadIdx.x >> 5); t0 < T; t0 += stride * TP_K) {
+    float m1[TP_K], m2[TP_K];
+    // (A) local means of TP_K rows, each pushed to every peer as soon as it is reduced
+#pragma unroll
+    for (int j = 0; j < TP_K; ++j) {
+      const int t = t0 + j * stride;
+      m1[j] = m2[j] = 0.f;
+      if (t < T) {
+        float s1, s2;
+        row_sumsq2(x1 + t * x1_st, x2 + t * x2_st, chunks, lane, s1, s2);
+        m1[j] = s1 * inv; m2[j] = s2 * inv;
+        if (push)
+          asm volatile("st.volatile.global.v4.u32 [%0], {%1,%2,%3,%4};"
+                       :: "l"(push + t), "r"(__float_as_uint(m1[j])), "r"(epoch), "r"(__float_as_uint(m2[j])),
+                          "r"(epoch) : "memory");
+      }
+    }
+    // (B) the peers' means of the same rows (lane r polls rank r's slots in this rank's buffer)
+#pragma unroll
+    for (int j = 0; j < TP_K; ++j) {
+      const int t = t0 + j * stride;
+      if (t < T) {
+        float a = m1[j], b = m2[j];
+        if (poll) {
+          uint32_t x, ex, y, ey, spins = 0;
+          do {
+            asm volatile("ld.volatile.global.v4.u32 {%0,%1,%2,%3}, [%4];"
+                         : "=r"(x), "=r"(ex), "=r"(y), "=r"(ey) : "l"(poll + t) : "memory");
+            if (++spins > (1u << 22)) asm volatile("trap;");   // a peer never arrived: fail loudly, do not hang
+          } while (ex != epoch || ey != epoch);
+          a = __uint_as_float(x); b = __uint_as_float(y);
+        }
+        float t1 = 0.f, t2 = 0.f;
+        for (int r = 0; r < world; ++r) {                        // rank order: the same sum on every rank
+          t1 += __shfl_sync(0xffffffffu, a, r);
+          t2 += __shfl_sync(0xffffffffu, b, r);
+        }
+        m1[j] = rsqrtf(t1 * inv_tp + eps); m2[j] = rsqrtf(t2 * inv_tp + eps);
+      }
+    }
+    // (C) normalise + merge: the rows were read a few microseconds ago and come from L2
+#pragma unroll
+    for (int j = 0; j < TP_K; ++j) {
+      const int t = t0 + j * stride;
+      if (t >= T) break;
+      const __nv_bfloat16* r1 = x1 + t * x1_st;
+      const __nv_bfloat16* r2 = x2 + t * x2_st;
+      const float rs1 = m1[j], rs2 = m2[j];
+      __nv_bfloat16* o = out + t * o_st;
+      for (int c0 = lane; c0 < chunks; c0 += 32 * BM_B) {
+        uint4 av[BM_B], bv[BM_B];
+#pragma unroll
+        for (int i = 0; i < BM_B; ++i) {
+          const int c = c0 + 32 * i;
+          if (c < chunks) { av[i] = ldg_v4(r1 + c * 8); bv[i] = ldg_v4(r2 + c * 8); }
+        }
+#pragma unroll
+        for (int i = 0; i < BM_B; ++i) {
+          const int c = c0 + 32 * i;
+          if (c >= chunks) break;
+          const float4 wa0 = *reinterpret_cast<const float4*>(w1 + c * 8);
+          const float4 wa1 = *reinterpret_cast<const float4*>(w1 + c * 8 + 4);
+          const float4 wb0 = *reinterpret_cast<const float4*>(w2 + c * 8);
+          const float4 wb1 = *reinterpret_cast<const float4*>(w2 + c * 8 + 4);
+          const float wa[8] = {wa0.x, wa0.y, wa0.z, wa0.w, wa1.x, wa1.y, wa1.z, wa1.w};
+          const float wb[8] = {wb0.x, wb0.y, wb0.z, wb0.w, wb1.x, wb1.y, wb1.z, wb1.w};
+          const uint32_t* ap = &av[i].x;
+          const uint32_t* bp = &bv[i].x;
+          uint4 r;
+          uint32_t* rp = &r.x;
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const float y0 = __fadd_rn(__fmul_rn(round_bf16(__fmul_rn(bf16_lo(ap[e]), rs1)), wa[2 * e]),
+                                       __fmul_rn(round_bf16(__fmul_rn(bf16_lo(bp[e]), rs2)), wb[2 * e]));
+            const float y1 = __fadd_rn(__fmul_rn(round_bf16(__fmul_rn(bf16_hi(ap[e]), rs1)), wa[2 * e + 1]),
+                                       __fmul_rn(round_bf16(__fmul_rn(bf16_hi(bp[e]), rs2)), wb[2 * e + 1]));
+            rp[e] = pack_bf16(y0 * 0.5f, y1 * 0.5f);
+          }
+          stg_v4(o + c * 8, r);
+        }
+      }
+    }
+  }
+}
+
 static int check_common(const void* x1, const void* x2, int T, int hidden, int64_t x1_st,
                         int64_t x2_st) {
   if (!x1 || !x2 || T < 0 || hidden <= 0) return HYMETA_ERR_INVALID_ARG;
@@ -239,6 +361,45 @@ extern "C" int hymeta_branch_norm_merge(const void* x_attn, const void* x_linear
         (const __nv_bfloat16*)x_attn, (const __nv_bfloat16*)x_linear, means, w_attn, w_linear,
         (__nv_bfloat16*)out, T, hidden_local, inv_tp, eps, xa_st, xl_st, o_st);
   }
+  count_launch();
+  return check_launch();
+}
+
+extern "C" size_t hymeta_branch_merge_tp_buffer_bytes(int tp_world, int64_t t_cap) {
+  if (tp_world <= 1 || tp_world > 8 || t_cap <= 0) return 0;
+  return (size_t)2 * tp_world * (size_t)t_cap * sizeof(uint4);
+}
+
+extern "C" int hymeta_branch_norm_merge_tp(const void* x_attn, const void* x_linear, const float* w_attn,
+                                           const float* w_linear, void* out, int T, int hidden_local,
+                                           int tp_world, int tp_rank, const uint64_t* peer_buffers,
+                                           int64_t t_cap, uint32_t epoch, float eps, int64_t xa_st,
+                                           int64_t xl_st, int64_t o_st, void* stream) {
+  if (T == 0) return HYMETA_OK;
+  const int rc = check_common(x_attn, x_linear, T, hidden_local, xa_st, xl_st);
+  if (rc) return rc;
+  if (!w_attn || !w_linear || !out || !peer_buffers || o_st % 8) return HYMETA_ERR_INVALID_ARG;
+  if (tp_world < 2 || tp_world > 8 || tp_rank < 0 || tp_rank >= tp_world || T > t_cap || epoch == 0)
+    return HYMETA_ERR_INVALID_ARG;
+  if (((uintptr_t)out | (uintptr_t)w_attn | (uintptr_t)w_linear) & 15) return HYMETA_ERR_INVALID_ARG;
+  TpPeers peers{};
+  for (int r = 0; r < tp_world; ++r) {
+    if (!peer_buffers[r] || (peer_buffers[r] & 15)) return HYMETA_ERR_INVALID_ARG;
+    peers.buf[r] = reinterpret_cast<uint4*>(peer_buffers[r]);
+  }
+  const int want = (T + 3) / 4;                  // 4 warps (rows) per CTA
+  auto go = [&](auto kernel) {
+    // every CTA of the grid must be resident at once (a warp polls for rows a peer's CTA of the same
+    // index produces): grid <= SMs x occupancy; the rows in flight per SM hide the exchange latency
+    int occ = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, 128, 0) != cudaSuccess || occ < 1) occ = 1;
+    const int cap = sm_count() * occ;
+    const int grid = want < cap ? want : cap;
+    kernel<<<grid, 128, 0, (cudaStream_t)stream>>>(
+        (const __nv_bfloat16*)x_attn, (const __nv_bfloat16*)x_linear, w_attn, w_linear, (__nv_bfloat16*)out, T,
+        hidden_local, tp_world, tp_rank, epoch, t_cap, peers, eps, xa_st, xl_st, o_st);
+  };
+  go(branch_norm_merge_tp_kernel);
   count_launch();
   return check_launch();
 }

@@ -4,6 +4,7 @@ memory, the current stream and dtype/shape checks.  Every function enqueues on
 """
 from __future__ import annotations
 
+import ctypes as C
 import functools
 from typing import Optional
 
@@ -402,16 +403,48 @@ def branch_sumsq(x_attn: torch.Tensor, x_linear: torch.Tensor,
     return out
 
 
+class BranchMergeExchange:
+    """Peer-mapped exchange buffers of the fused tensor-parallel branch merge (f1): one buffer per rank
+    of the TP group, allocated as torch symmetric memory (CUDA peer mapping over NVLink) and handed
+    to ``hymeta_branch_norm_merge_tp`` as raw addresses.  Create it once per group (collective call:
+    every rank of ``group`` must construct it with the same ``t_cap``); each ``branch_norm_merge(...,
+    exchange=ex)`` call advances the epoch, so every rank must make the same sequence of calls."""
+
+    def __init__(self, group, t_cap: int, device=None):
+        import torch.distributed as dist
+        import torch.distributed._symmetric_memory as symm_mem
+        self.group = group if group is not None else dist.group.WORLD
+        self.world, self.rank = dist.get_world_size(self.group), dist.get_rank(self.group)
+        if not 2 <= self.world <= 8:
+            raise ValueError("the fused exchange serves tensor-parallel groups of 2..8 ranks")
+        self.t_cap = int(t_cap)
+        nbytes = lib().hymeta_branch_merge_tp_buffer_bytes(self.world, self.t_cap)
+        device = torch.device("cuda", torch.cuda.current_device()) if device is None else device
+        self.buf = symm_mem.empty(nbytes, dtype=torch.uint8, device=device)
+        self.buf.zero_()
+        self.handle = symm_mem.rendezvous(self.buf, self.group)
+        self.ptrs = (C.c_uint64 * self.world)(*[int(self.handle.buffer_ptrs[r]) for r in range(self.world)])
+        torch.cuda.synchronize(device)
+        dist.barrier(self.group)        # every buffer is zeroed before any peer may write into it
+        self.epoch = 0
+
+    def next_epoch(self) -> int:
+        self.epoch = self.epoch % 0x7fffffff + 1      # never 0 (the zero fill), +1 per call
+        return self.epoch
+
+
 @_timed("branch_norm_merge")
 def branch_norm_merge(x_attn: torch.Tensor, x_linear: torch.Tensor, w_attn: torch.Tensor,
                       w_linear: torch.Tensor, eps: float, tp_world: int = 1,
                       means: Optional[torch.Tensor] = None, group=None,
-                      out: Optional[torch.Tensor] = None) -> torch.Tensor:
+                      out: Optional[torch.Tensor] = None,
+                      exchange: Optional[BranchMergeExchange] = None) -> torch.Tensor:
     """``((norm1(out_attn) + norm2(out_linear)) / 2).to(bfloat16)`` of the 70B layer
     (modeling_hymeta.py:909-919, HymetaRMSNormTP :151-173).  x_* [T, hidden/tp] bf16, w_* the
-    rank's fp32 weight slice.  tp_world > 1: the per-token means are computed by
-    ``branch_sumsq`` and summed over ``group`` with ONE all-reduce of 8*T bytes (pass ``means``
-    to supply an already reduced buffer)."""
+    rank's fp32 weight slice.  tp_world > 1 with ``exchange``: ONE kernel computes the local means,
+    exchanges them through NVLink peer memory and merges with the rows still in registers.  Without
+    it: ``branch_sumsq`` + ONE NCCL all-reduce of 8*T bytes over ``group`` + the merge kernel (pass
+    ``means`` to supply an already reduced buffer)."""
     T, Hd = x_attn.shape
     for n, t in (("x_attn", x_attn), ("x_linear", x_linear)):
         _req(t, n, torch.bfloat16)
@@ -421,6 +454,16 @@ def branch_norm_merge(x_attn: torch.Tensor, x_linear: torch.Tensor, w_attn: torc
             raise ValueError(f"{n} must hold hidden/tp = {Hd} elements")
     if x_linear.shape != x_attn.shape:
         raise ValueError("the two branches must have the same shape")
+    if tp_world > 1 and exchange is not None and means is None:
+        if exchange.world != tp_world or T > exchange.t_cap:
+            raise ValueError("exchange was built for another group size or a smaller token capacity")
+        if out is None:
+            out = torch.empty(T, Hd, dtype=torch.bfloat16, device=x_attn.device)
+        check(lib().hymeta_branch_norm_merge_tp(
+            _ptr(x_attn), _ptr(x_linear), _ptr(w_attn), _ptr(w_linear), _ptr(out), T, Hd, tp_world,
+            exchange.rank, exchange.ptrs, exchange.t_cap, exchange.next_epoch(), float(eps),
+            x_attn.stride(0), x_linear.stride(0), out.stride(0), _stream()), "hymeta_branch_norm_merge_tp")
+        return out
     if tp_world > 1 and means is None:
         import torch.distributed as dist
         means = branch_sumsq(x_attn, x_linear)
