@@ -262,11 +262,25 @@ def extra_configs(dev="cuda", world=1, rank=0, tp_group=None, plan=None):
         ops.rope_kv_write_paged(sq, sk, sv, table, pos, M, kv[0], kv[1], slot_map)
         ops.swa_meta_prefill_varlen(sq, sk, sv, None, mk, mv, cu, cu, T, 4095, out=o_swa)
         xa, xl = o_swa.view(Tt, h * D), o_gla.view(Tt, h * D)
-        if tp > 1:     # one kernel: local means -> NVLink peer-memory exchange -> merge (f1)
+        if tp > 1 and exchange is not None:   # one kernel: local means -> NVLink peer-memory exchange -> merge (f1)
             ops.branch_norm_merge(xa, xl, w1, w2, 1e-6, tp_world=tp, out=merged, exchange=exchange)
+        elif tp > 1:
+            ops.branch_norm_merge(xa, xl, w1, w2, 1e-6, tp_world=tp, out=merged, group=tp_group)
         else:
             ops.branch_norm_merge(xa, xl, w1, w2, 1e-6, out=merged)
-    exchange = ops.BranchMergeExchange(tp_group, t_cap=Tt) if tp > 1 else None
+    exchange = None
+    if tp > 1:
+        # the peer-memory exchange is collective: every rank of the job agrees on whether it came up
+        # (symmetric memory needs P2P access inside the TP group); otherwise all fall back to the NCCL form
+        try:
+            exchange = ops.BranchMergeExchange(tp_group, t_cap=Tt)
+            ok = 1
+        except Exception:
+            ok = 0
+        flag = torch.tensor([ok], device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        if flag.item() == 0:
+            exchange = None
     if world > 1:
         dist.barrier()
     t = tmax(_time(layer, 3, 1))
@@ -274,7 +288,8 @@ def extra_configs(dev="cuda", world=1, rank=0, tp_group=None, plan=None):
     out["config3_70b_hybrid_layer_32k"] = {
         "plan": f"tp{plan.tp} x dp{plan.dp}", "heads_per_gpu": [h, hkv], "prompts": plan.dp * P, "prompt_len": T,
         "meta_tokens": M, "layer_ms": t * 1e3, "tok_s_per_layer": plan.dp * Tt / t,
-        "exchange": "fused branch-merge kernel: 16 B per token and peer over NVLink peer memory (f1)" if tp > 1 else "none",
+        "exchange": ("none" if tp == 1 else "fused branch-merge kernel: 16 B per token and peer over NVLink peer memory (f1)"
+                     if exchange is not None else "one NCCL all-reduce of 8*T bytes per layer (f1; peer memory unavailable)"),
         "swa_flops_per_gpu": P * h * 4 * D * n_keys}
     del qkv_g, qkv_s, kv, o_gla, o_swa, merged, slot_map
     torch.cuda.empty_cache()
