@@ -188,7 +188,8 @@ int hymeta_gla_gate_7b(const void* q_in, const void* k_in, const void* gk_in, vo
  * hymeta_gla_decode_gate7b:       hymeta_gla_decode_gnorm plus gate_normalizer: 0 = plain; > 0 = q, k
  *                                 and g are raw q / k / gk rows (g bf16) and relu / logsigmoid /
  *                                 division run in the kernel's operand conversion, bit-identical to
- *                                 hymeta_gla_gate_7b followed by the plain kernel.
+ *                                 hymeta_gla_gate_7b followed by the plain kernel.  gate_normalizer
+ *                                 must be a power of two (the model's 16; else HYMETA_ERR_UNSUPPORTED).
  * ---------------------------------------------------------------------------------------------- */
 int hymeta_gla_gate_7b_g(const void* gk_in, void* g_out, int T, int Hk, int D, int64_t gi_st,
                          int64_t gi_sh, int64_t go_st, int64_t go_sh, float normalizer, void* stream);

@@ -40,10 +40,10 @@ struct GlaDecodeParams {
   // > 0: q, k and g are the RAW projection outputs of the 7B layer and the feature map + gate
   // (model_for_7B/gla_attention.py:251-262) run here: q = relu(q), k = relu(k),
   // g = bf16(bf16(logsigmoid(gk)) / gate_norm) -- bit-identical to hymeta_gla_gate_7b's outputs: this
-  // file is compiled with --use_fast_math, so the gate calls libdevice's accurate expf / log1pf and
-  // the IEEE division by name (flush-to-zero only matters where exp(-|x|) is denormal, and there
-  // log1p of it vanishes against x either way)
-  float gate_norm;
+  // file is compiled with --use_fast_math, so the gate calls libdevice's accurate expf / log1pf by
+  // name (flush-to-zero only matters where exp(-|x|) is denormal, and there log1p of it vanishes
+  // against x either way); gate_norm must be a power of two so that / gate_norm == * gate_inv exactly
+  float gate_norm, gate_inv;
 };
 
 typedef unsigned long long u64;
@@ -203,7 +203,10 @@ __global__ void __launch_bounds__(GD_THREADS, 2) gla_decode_kernel(const GlaDeco
           // logsigmoid(x) = min(x, 0) - log1p(exp(-|x|)) (ATen), rounded to bf16 before the division
           // and again after it -- exactly what hymeta_gla_gate_7b stores (gla_gate.cu)
           const float ls = fminf(gv, 0.f) - __nv_log1pf(__nv_expf(-fabsf(gv)));
-          gv = round_bf16(__fdiv_rn(round_bf16(ls), p.gate_norm));
+          // gate_norm is a power of two (checked on the host): the division is an exact multiply, and
+          // the kernel stays free of the IEEE-division slow-path call (its mere presence cost the
+          // main loop 23 % at B = 1000)
+          gv = round_bf16(round_bf16(ls) * p.gate_inv);
         }
         s_kg[row].y = __float_as_uint(__expf(gv));
       }
@@ -370,6 +373,10 @@ extern "C" int hymeta_gla_decode_gate7b(const void* q, const void* k, const void
                                  float gate_normalizer, void* stream) {
   if (B == 0) return HYMETA_OK;
   if (gate_normalizer < 0.f || (gate_normalizer > 0.f && g_is_fp32)) return HYMETA_ERR_INVALID_ARG;
+  if (gate_normalizer > 0.f) {   // power of two only (the model's 16): see the kernel
+    int e = 0;
+    if (frexpf(gate_normalizer, &e) != 0.5f) return HYMETA_ERR_UNSUPPORTED;
+  }
   if (!q || !k || !v || !g || !o || !state || !slot_idx || B < 0 || H <= 0 || Hk <= 0 || Hv <= 0 || Hs <= 0)
     return HYMETA_ERR_INVALID_ARG;
   if (D != kD) return HYMETA_ERR_UNSUPPORTED;
@@ -386,7 +393,8 @@ extern "C" int hymeta_gla_decode_gate7b(const void* q, const void* k, const void
   GlaDecodeParams p{(const __nv_bfloat16*)q, (const __nv_bfloat16*)k, (const __nv_bfloat16*)v, g,
                     (__nv_bfloat16*)o, (__nv_bfloat16*)state, slot_idx, B, H, Hk, Hv, Hs, 0u, 0u,
                     q_sb, q_sh, k_sb, k_sh, v_sb, v_sh, g_sb, g_sh, o_sb, o_sh, st_ss, st_sh, scale,
-                    (const __nv_bfloat16*)gnorm_weight, gnorm_eps, gate_normalizer};
+                    (const __nv_bfloat16*)gnorm_weight, gnorm_eps, gate_normalizer,
+                    gate_normalizer > 0.f ? 1.f / gate_normalizer : 0.f};
   auto magic = [&](int div) -> uint32_t {   // exact for hs < Hs <= 4096 (verified below)
     const uint32_t m = (65536u + div - 1) / div;
     for (int x = 0; x < Hs; ++x)
@@ -401,7 +409,9 @@ extern "C" int hymeta_gla_decode_gate7b(const void* q, const void* k, const void
   const bool f = g_is_fp32 != 0;
   if (G == 1) launch_gla_decode<1>(p, f, st);
   else if (G <= 4) launch_gla_decode<4>(p, f, st);
-  else if (G == 7) launch_gla_decode<7>(p, f, st);
+  // G == 7 runs the 8-head instantiation: 7 x 4 packed accumulators spill under the 128-register
+  // cap of 2 CTAs per SM (23 STL / 39 LDL in the loop), 8 x 4 allocate cleanly -- 90 -> 69 us at
+  // B = 1000 with the g_norm epilogue, 9.5 -> 8.8 us at B = 64
   else launch_gla_decode<8>(p, f, st);
   count_launch();
   return check_launch();

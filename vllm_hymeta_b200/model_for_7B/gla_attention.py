@@ -15,6 +15,7 @@ method names and argument meaning, on the sm_100a kernels:
 """
 from __future__ import annotations
 
+import math
 from typing import Optional
 
 import torch
@@ -91,10 +92,16 @@ class GatedLinearAttention:
         start = attn_metadata.num_prefill_tokens
         slot_ids = state_indices_tensor[getattr(attn_metadata, "num_prefills", 0):]
         B = q.shape[0] - start
-        o = ops.gla_decode(q[start:], k[start:], v[start:], gk[start:], kv_cache,
+        qd, kd, gd, fused = q[start:], k[start:], gk[start:], self.gate_logit_normalizer
+        if math.frexp(float(fused))[0] != 0.5:
+            # the in-kernel gate divides by an exact power of two only (the model's 16): any other
+            # normalizer goes through the gate kernel first
+            qd, kd, gd = ops.gla_gate_7b(qd, kd, gd, fused)
+            fused = None
+        o = ops.gla_decode(qd, kd, v[start:], gd, kv_cache,
                            slot_ids[:B].to(torch.int32), out=out,
                            gnorm_weight=self._gnorm_w(q.device) if norm else None,
-                           gnorm_eps=self.norm_eps, gate_normalizer=self.gate_logit_normalizer)
+                           gnorm_eps=self.norm_eps, gate_normalizer=fused)
         return o.view(B, -1)
 
     def forward(self, qkv: torch.Tensor, gk: torch.Tensor, kv_caches: GLACacheParams,
