@@ -4,11 +4,11 @@
 //   S <- bf16(k (x) v) + exp(g)[:,None] * S        (fp32 math, bf16 store)
 //   o  = (q * scale)^T S                            (all q-heads sharing the state)
 //
-// Grid (D/DVS, Hs, B), 128 threads.  One CTA owns all 128 d_k rows of a DVS-wide d_v slice of one
-// state; a lane owns 8 consecutive d_v columns (one 128-bit load / store per row it visits) and warp
-// w owns rows [32w, 32w+32), so every lane has DVS/8 independent 16-byte loads in flight before the
-// first use and every state byte is touched by exactly one thread.  The G = H/Hs q-heads of a GQA
-// group are all served from the single state read.
+// Persistent grid (<= 2 CTAs of 256 threads per SM), item = one (request, state-head) state; item
+// i+2 streams into a 3-stage shared-memory ring with cp.async while item i is computed (see the
+// kernel comment).  Warp w owns d_k rows [16w, 16w+16), a lane owns 8 consecutive d_v columns, so
+// every state byte is touched by exactly one thread and stored back from registers with 128-bit
+// stores.  The G = H/Hs q-heads of a GQA group are all served from the single state read.
 // Instruction diet (the kernel is issue-bound long before it is FLOP-bound: 7 heads x 128 x 128 FMAs
 // per 32 KB of state): the bf16 product k*v is ONE packed HMUL2.BF16 per column pair (bit-identical
 // to the reference's bf16 `b_k[:, None] * b_v[None, :]`, my_fused_recurrent.py:65), the decay and the

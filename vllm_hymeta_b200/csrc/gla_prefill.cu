@@ -7,21 +7,26 @@
 // dimension: row = head*16 + token (G <= 8 -> M = 128).  With b_t = cumsum(g) inside the step and
 // the per-channel reference r = b_7 (mid-step, so every exponent is bounded by 8 steps of decay):
 //     q~_t = q_t * scale * exp(b_t - r)      k~_s = k_s * exp(r - b_s)
-//     A    = q~ k~^T  (causal, s <= t)               MMA  M128 N16  K128   (K-major x K-major)
-//     O    = q~ X  +  P v      (P = bf16 causal A)    MMA  M128 N128 K128 (SS) + K16 (TS, P in TMEM)
-//     Y    = X + k~^T v                               MMA  M128 N128 K16    (MN-major x MN-major)
-//     X'   = exp(b_15 - r + r') (.) Y                 fp32 master in TMEM, rescaled in place
-// where X = exp(r) (.) S is the state expressed in the step's reference frame.  The fp32 master
-// never leaves TMEM; a bf16 copy (the MN-major B operand of the next step's q~ X) is rewritten to
-// shared memory by the same pass that rescales it.
+//     A    = q~ k~^T  (causal, s <= t)               tcgen05.mma  M128 N16  K128   (K-major x K-major)
+//     O    = q~ X  +  P v      (P = bf16 causal A)    tcgen05.mma  M128 N128 K128 (SS) + K16 (TS, P in TMEM)
+//     Y    = X + k~^T v                               mma.sync m16n8k16, accumulators = the fp32 master
+//     X'   = exp(b_15 - r + r') (.) Y                 rescaled in registers
+// where X = exp(r) (.) S is the state expressed in the step's reference frame.  The fp32 master lives
+// in the registers of the state warpgroup (with it in TMEM every step would move 128 KB through
+// tcgen05.ld / st for the per-row decay); its bf16 copy -- the MN-major B operand of the next step's
+// q~ X -- is written to shared memory by the pass that rescales it.
 //
-// Warp roles (544 threads), all hand-offs through mbarriers:
-//   warps 0-3   gates: thread = channel; loads g/k/v of a step, builds k~, the q-side factor table
-//               scale*exp(b_t - r) and the per-channel rescale factors into a 4-stage ring
-//   warps 4-7   state: thread = d_k row = TMEM lane; X' = D (.) Y, bf16 copy, final state store
-//   warps 8-11  q-tile builder / P converter / O epilogue for even steps (thread = row for TMEM)
+// Warp roles (512 threads, setmaxnreg 80 / 208 / 112), all hand-offs through mbarriers:
+//   warps 0-1   gates: thread = 2 channels; raw g / k rows arrive by TMA (2-slot ring), v by TMA
+//               straight into its stage; builds k~ (relu folded in for the 7B layer), the q-side
+//               factor table scale*exp(b_t - r) and the per-channel rescale factors, 3-stage ring
+//   warp 2      MMA issuer (one lane);  warp 3 idle
+//   warps 4-7   state: mma.sync Y = X + k~^T v on ldmatrix fragments, rescale, bf16 X to smem,
+//               final state / segment summary store
+//   warps 8-11  q-tile builder (q prefetched one tile ahead, relu folded in) / P converter /
+//               O epilogue (+ g_norm) for even steps (thread = row for TMEM); output rows staged per
+//               warp in smem and stored as 64-byte row segments
 //   warps 12-15 same for odd steps
-//   warp 16     MMA issuer (one lane)
 #include "umma.cuh"
 
 namespace hymeta {

@@ -171,10 +171,14 @@ _WS = {}
 
 
 def _gla_workspace(device, nbytes: int) -> torch.Tensor:
-    """Grow-only fp32 scratch per device (the C ABI never allocates)."""
+    """Grow-only fp32 scratch per device (the C ABI never allocates).  One buffer per device:
+    segmented prefills are single-stream calls.  It must already be large enough when a CUDA graph
+    is captured (a buffer allocated from the graph's private pool must not be cached for eager use)."""
     key = (device.type, device.index)
     w = _WS.get(key)
     if w is None or w.numel() * 4 < nbytes:
+        if torch.cuda.is_current_stream_capturing():
+            raise RuntimeError("gla_prefill workspace must be sized by an eager call before CUDA-graph capture")
         w = torch.empty((nbytes + 3) // 4, dtype=torch.float32, device=device)
         _WS[key] = w
     return w
