@@ -34,10 +34,12 @@ def metatoken_flash_attn_varlen_func(
     cu_seqlens_q=None, cu_seqlens_k=None, max_seqlen_q=None, max_seqlen_k=None,
     num_meta_tokens=128, dropout_p=0.0, softmax_scale=None, causal=False,
     window_size=(-1, -1), alibi_slopes=None, block_tables=None, softcap=0.0,
-    deterministic=False, return_attn_probs=False, attn_mask=None,
+    deterministic=False, return_attn_probs=False, attn_mask=None, out: Optional[torch.Tensor] = None,
 ):
     """Packed varlen prefill (reference fa_kernel_metatoken.py:329-374 -> :198-285).
-    Returns ``[1, (M if q2) + Tq, H, D]`` with the meta-query rows FIRST (:283)."""
+    Returns ``[1, (M if q2) + Tq, H, D]`` with the meta-query rows FIRST (:283).  Extension over the
+    reference signature: ``out`` [(M) + Tq, H, D] is written in place (the backend passes its output
+    tensor, which saves the reference's full copy ``output[:n] = res[0]``, meta_attention.py:920)."""
     _check_unused(dropout_p, alibi_slopes, softcap, attn_mask, return_attn_probs)
     assert causal and window_size[1] in [0, -1]
     if k2 is not None:
@@ -52,7 +54,7 @@ def metatoken_flash_attn_varlen_func(
         max_seqlen_q = q1.shape[0]
     out = ops.swa_meta_prefill_varlen(
         q1, k1, v1, q2, k2, v2, cu_seqlens_q, cu_seqlens_k, int(max_seqlen_q),
-        _window_left(window_size), scale=softmax_scale, block_tables=block_tables)
+        _window_left(window_size), scale=softmax_scale, block_tables=block_tables, out=out)
     return out.unsqueeze(0)
 
 
