@@ -402,7 +402,7 @@ int hymeta_branch_norm_merge(const void* x_attn, const void* x_linear, const flo
  * its own buffer for the peers' slots of that row, sums the means in rank order and finishes the row
  * (its second touch is an L2 hit: x is read from DRAM once).  epoch: any non-zero value that changes by one between consecutive
  * calls on the group (two slot parities); every rank passes the same T, hidden_local and epoch.  All
- * CTAs are co-resident (grid <= SMs x occupancy).  A peer that never arrives traps after ~4M polls. */
+ * CTAs are co-resident (grid <= SMs x occupancy).  A peer that never arrives traps after ~1-2 minutes of polling. */
 size_t hymeta_branch_merge_tp_buffer_bytes(int tp_world, int64_t t_cap);
 int hymeta_branch_norm_merge_tp(const void* x_attn, const void* x_linear, const float* w_attn,
                                 const float* w_linear, void* out, int T, int hidden_local,

@@ -248,7 +248,10 @@ branch_norm_merge_tp_kernel(const __nv_bfloat16* x1, const __nv_bfloat16* x2,
           do {
             asm volatile("ld.volatile.global.v4.u32 {%0,%1,%2,%3}, [%4];"
                          : "=r"(x), "=r"(ex), "=r"(y), "=r"(ey) : "l"(poll + t) : "memory");
-            if (++spins > (1u << 22)) asm volatile("trap;");   // a peer never arrived: fail loudly, do not hang
+            // a peer that never arrives (a rank died, or the ranks disagree on the call sequence) must
+            // not hang the GPU: give up after ~1-2 minutes of polling -- far beyond any legitimate skew
+            // between ranks -- and fail the launch loudly
+            if (++spins > (1u << 27)) asm volatile("trap;");
           } while (ex != epoch || ey != epoch);
           a = __uint_as_float(x); b = __uint_as_float(y);
         }
