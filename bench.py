@@ -427,7 +427,6 @@ def run_gpu(args):
     swa_pf_flops = B * sum(H * 4 * D * min(i + 1, WINDOW_LEFT + 1) for i in range(Tp))
     gla_pf_bytes = T * (H * 2 * D * b2 + Hkv * D * (2 * b2 + 2))
     gla_pf_flops = T * H * (4 * D * D + 2 * 64 * 2 * D)
-    gate_bytes = T * Hkv * D * b2 * 2                      # gk read, g written (relu of q / k is in the GLA kernels)
     kvw_bytes = T * 2 * Hkv * D * b2 * 2
     us_dswa = t_dswa * 1e3 / (Sd * N_SWA_LAYERS)
 
@@ -457,10 +456,8 @@ def run_gpu(args):
                          ms_per_layer_kernel=kms["gla_prefill"], ms_per_layer_module=t_pgla / N_GLA_LAYERS,
                          tensor_tflops=gla_pf_flops / (kms["gla_prefill"] * 1e-3) / 1e12,
                          tok_s_per_layer=T / (t_pgla * 1e-3 / N_GLA_LAYERS),
-                         what="kernel applies relu(q), relu(k) and the fused g_norm epilogue; module adds the 2 KB/token "
-                              "logsigmoid(gk)/16 launch"),
-        "gla_gate": K(kms["gla_gate_7b"] * N_GLA_LAYERS / step_ms, "hbm", gate_bytes, kms["gla_gate_7b"] * 1e-3,
-                      peaks["hbm_gbs"], "GB/s", ms_per_layer_kernel=kms["gla_gate_7b"]),
+                         what="ONE launch per layer on the raw projection rows: relu(q), relu(k), the gate "
+                              "logsigmoid(gk)/16 looked up by the gate warps in a 64 K-entry table, g_norm epilogue"),
         "kv_write": K(kms["kv_write"] * N_SWA_LAYERS / step_ms, "hbm", kvw_bytes, kms["kv_write"] * 1e-3,
                       peaks["hbm_gbs"], "GB/s", ms_per_layer_kernel=kms["kv_write"]),
     }

@@ -184,7 +184,13 @@ int hymeta_gla_gate_7b(const void* q_in, const void* k_in, const void* gk_in, vo
  *                                 prefill kernel takes it together with raw q / k and relu_qk = 1.
  * hymeta_gla_prefill_varlen_fused: hymeta_gla_prefill_varlen_seg_gnorm plus relu_qk (0 / 1): relu is
  *                                 applied to q and k as they are scaled into the MMA operands
- *                                 (relu(x) * e == max(x * e, 0) for e > 0: bit-identical outputs).
+ *                                 (relu(x) * e == max(x * e, 0) for e > 0: bit-identical outputs);
+ *                                 and gate_table (null, or [65536] bf16): `g` then holds the RAW bf16
+ *                                 gk rows and the kernel's gate warps map each through the table --
+ *                                 the 7B gate is a pure function of a 16-bit input; the table is
+ *                                 hymeta_gla_gate_7b_g applied once to all 65536 bit patterns, so the
+ *                                 result is bit-identical to the separate pass and the layer's
+ *                                 prefill is ONE launch.
  * hymeta_gla_decode_gate7b:       hymeta_gla_decode_gnorm plus gate_normalizer: 0 = plain; > 0 = q, k
  *                                 and g are raw q / k / gk rows (g bf16) and relu / logsigmoid /
  *                                 division run in the kernel's operand conversion, bit-identical to
@@ -200,7 +206,8 @@ int hymeta_gla_prefill_varlen_fused(
     int64_t q_sh, int64_t k_st, int64_t k_sh, int64_t v_st, int64_t v_sh, int64_t g_st,
     int64_t g_sh, int64_t o_st, int64_t o_sh, int64_t st_ss, int64_t st_sh, int64_t meta_sh,
     int g_is_fp32, float scale, int write_state, int max_seqlen, int seg_len, void* workspace,
-    size_t workspace_bytes, const void* gnorm_weight, float gnorm_eps, int relu_qk, void* stream);
+    size_t workspace_bytes, const void* gnorm_weight, float gnorm_eps, int relu_qk,
+    const void* gate_table, void* stream);
 int hymeta_gla_decode_gate7b(const void* q, const void* k, const void* v, const void* g, void* o,
                              void* state, const int32_t* slot_idx, int B, int H, int Hk, int Hv,
                              int Hs, int D, int64_t q_sb, int64_t q_sh, int64_t k_sb, int64_t k_sh,

@@ -232,6 +232,11 @@ def test_gate_7b_folded_into_gla_kernels(ops):
         o1 = ops.gla_prefill_varlen(rq[:T], rk[:T], v[:T], rg[:T], s1, cu, sl, md, gnorm_weight=gw)
         o2 = ops.gla_prefill_varlen(q[:T], k[:T], v[:T], rg[:T], s2, cu, sl, md, gnorm_weight=gw, relu_qk=True)
         assert torch.equal(o1, o2) and torch.equal(s1, s2)
+        # the gate looked up by the kernel's gate warps from the table of all 65536 bf16 inputs
+        s3 = state.clone()
+        o3 = ops.gla_prefill_varlen(q[:T], k[:T], v[:T], gk[:T], s3, cu, sl, md, gnorm_weight=gw, relu_qk=True,
+                                    gate_table=ops.gla_gate_7b_table(16.0))
+        assert torch.equal(o1, o3) and torch.equal(s1, s3)
         slots = torch.arange(B, dtype=torch.int32, device=DEV) + 2
         slots[5] = -1
         d1 = ops.gla_decode(rq[T:], rk[T:], v[T:], rg[T:], s1, slots, gnorm_weight=gw)

@@ -32,7 +32,7 @@ SIGNATURES = {
     "hymeta_gla_gate_7b": (_i, [_p] * 6 + [_i] * 4 + [_i64] * 12 + [_f, _p]),
     "hymeta_gla_gate_7b_g": (_i, [_p, _p, _i, _i, _i] + [_i64] * 4 + [_f, _p]),
     "hymeta_gla_prefill_varlen_fused": (_i, [_p] * 10 + [_i] * 7 + [_i64] * 13 +
-                                        [_i, _f, _i, _i, _i, _p, _sz, _p, _f, _i, _p]),
+                                        [_i, _f, _i, _i, _i, _p, _sz, _p, _f, _i, _p, _p]),
     "hymeta_gla_decode_gate7b": (_i, [_p] * 7 + [_i] * 6 + [_i64] * 12 + [_i, _f, _p, _f, _f, _p]),
     "hymeta_kv_write_paged": (_i, [_p] * 5 + [_i] * 4 + [_i64] * 10 + [_p]),
     "hymeta_rope_kv_write_paged": (_i, [_p] * 6 + [_i, _p, _i64] + [_p] * 5 + [_i] * 6 + [_i64] * 20 + [_i, _p]),

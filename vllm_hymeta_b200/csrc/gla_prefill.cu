@@ -73,6 +73,10 @@ struct GlaPrefillParams {
   float gnorm_eps;
   uint32_t relu_lim;              // bf16x2 lower limit applied to q and k: 0 = relu (7B feature map on raw
                                   // projection outputs), 0xff80ff80 (-inf) = identity
+  const uint16_t* gate_table;     // null, or [65536] bf16: g = table[raw bf16 gate bits] -- the 7B gate
+                                  // bf16(bf16(logsigmoid(gk)) / normalizer) is a pure function of a 16-bit
+                                  // input, tabulated once per normalizer by hymeta_gla_gate_7b_g itself
+                                  // (bit-identical by construction; the 128 KB table lives in L1 / L2)
 };
 
 __device__ __forceinline__ uint32_t hmul2_bf16(uint32_t a, uint32_t b) {   // exact products, one rounding each
@@ -217,9 +221,23 @@ gla_prefill_kernel(const GlaPrefillParams p, const __grid_constant__ CUtensorMap
         if (GF32) b[t] = *reinterpret_cast<const float2*>(rawp + so + t * 512);
         else {
           const uint32_t u = *reinterpret_cast<const uint32_t*>(rawp + so + t * 256);
-          b[t] = make_float2(bf16_lo(u), bf16_hi(u));
+          b[t] = make_float2(__uint_as_float(u & 0xffffu), __uint_as_float(u >> 16));   // raw bits for now
         }
         kk[t] = *reinterpret_cast<const uint32_t*>(rawkp + so + t * 256);
+      }
+      if (!GF32) {
+        if (p.gate_table) {   // 32 independent 2-byte gathers per thread and step, hot entries in L1
+#pragma unroll
+          for (int t = 0; t < GC; ++t) {
+            const uint32_t lo = __ldg(p.gate_table + __float_as_uint(b[t].x));
+            const uint32_t hi = __ldg(p.gate_table + __float_as_uint(b[t].y));
+            b[t] = make_float2(__uint_as_float(lo << 16), __uint_as_float(hi << 16));
+          }
+        } else {
+#pragma unroll
+          for (int t = 0; t < GC; ++t)
+            b[t] = make_float2(__uint_as_float(__float_as_uint(b[t].x) << 16), __uint_as_float(__float_as_uint(b[t].y) << 16));
+        }
       }
       float bx = 0.f, by = 0.f;
 #pragma unroll
@@ -677,8 +695,9 @@ extern "C" int hymeta_gla_prefill_varlen_fused(
     int64_t k_st, int64_t k_sh, int64_t v_st, int64_t v_sh, int64_t g_st, int64_t g_sh, int64_t o_st,
     int64_t o_sh, int64_t st_ss, int64_t st_sh, int64_t meta_sh, int g_is_fp32, float scale,
     int write_state, int max_seqlen, int seg_len, void* workspace, size_t workspace_bytes,
-    const void* gnorm_weight, float gnorm_eps, int relu_qk, void* stream) {
+    const void* gnorm_weight, float gnorm_eps, int relu_qk, const void* gate_table, void* stream) {
   if (N == 0) return HYMETA_OK;
+  if (gate_table && g_is_fp32) return HYMETA_ERR_INVALID_ARG;   // the table maps bf16 gate bits
   if (seg_len < 0 || seg_len % GC) return HYMETA_ERR_INVALID_ARG;
   int n_segs = 1;
   if (seg_len > 0 && max_seqlen > seg_len) {
@@ -709,6 +728,7 @@ extern "C" int hymeta_gla_prefill_varlen_fused(
   if (gnorm_weight && ((uintptr_t)gnorm_weight & 15)) return HYMETA_ERR_INVALID_ARG;
   p.gnorm_w = (const __nv_bfloat16*)gnorm_weight; p.gnorm_eps = gnorm_eps;
   p.relu_lim = relu_qk ? 0u : 0xff80ff80u;
+  p.gate_table = (const uint16_t*)gate_table;
   p.seg_len = seg_len; p.n_segs = n_segs; p.pass = 0; p.ws = (float*)workspace;
   // TMA maps: raw g / k rows ([16 tokens][128 channels] boxes) and v (SWIZZLE_128B 64-wide halves)
   const int64_t tvec[] = {k_st, k_sh, g_st * (g_is_fp32 ? 2 : 1), g_sh * (g_is_fp32 ? 2 : 1)};
@@ -771,7 +791,7 @@ extern "C" int hymeta_gla_prefill_varlen_seg_gnorm(
                                          H, Hk, Hv, Hs, D, q_st, q_sh, k_st, k_sh, v_st, v_sh, g_st, g_sh,
                                          o_st, o_sh, st_ss, st_sh, meta_sh, g_is_fp32, scale, write_state,
                                          max_seqlen, seg_len, workspace, workspace_bytes, gnorm_weight,
-                                         gnorm_eps, 0, stream);
+                                         gnorm_eps, 0, nullptr, stream);
 }
 
 extern "C" int hymeta_gla_prefill_varlen_seg(

@@ -4,10 +4,11 @@ method names and argument meaning, on the sm_100a kernels:
 
 * feature map + gate (:251-267)          -> folded into the GLA kernels: they read the
                                             raw ``qkv_proj`` / ``gk_proj`` rows, relu(q) / relu(k)
-                                            on the fly; the decode kernel also computes
-                                            logsigmoid(gk) / 16, prefill takes it from the 2 KB/token
-                                            ``ops.gla_gate_7b_g`` pass (k / v / gk stay at the kv-head
-                                            count: no ``repeat_kv`` x7 materialisation)
+                                            on the fly; the decode kernel computes logsigmoid(gk) / 16
+                                            itself, the prefill kernel's gate warps look it up in a
+                                            64 K-entry table (the gate is a pure function of a bf16
+                                            input); k / v / gk stay at the kv-head count: no
+                                            ``repeat_kv`` x7 materialisation
 * per-request ``fused_chunk_gla`` loop   -> ONE varlen launch over all prefill requests, slot
   (:179-211)                                states read and written in-kernel (no isnan() host sync)
 * decode (:223-235)                      -> ``ops.gla_decode``
@@ -77,11 +78,13 @@ class GatedLinearAttention:
                 mode = torch.where(ctx[:num_prefills] == 0, ops.INIT_ZERO, ops.INIT_SLOT).to(torch.int32)
             else:
                 mode = torch.full((num_prefills,), ops.INIT_SLOT, dtype=torch.int32, device=q.device)
-            g = ops.gla_gate_7b_g(gk[:n_tok], self.gate_logit_normalizer)
-            ops.gla_prefill_varlen(q[:n_tok], k[:n_tok], v[:n_tok], g, kv_cache, cu, slots,
+            # ONE launch: relu(q), relu(k) on the fly, the gate looked up from the 64 K-entry table of
+            # bf16(bf16(logsigmoid(x)) / normalizer) by the kernel's gate warps
+            ops.gla_prefill_varlen(q[:n_tok], k[:n_tok], v[:n_tok], gk[:n_tok], kv_cache, cu, slots,
                                    mode, max_seqlen=getattr(attn_metadata, "max_query_len", None) or n_tok,
                                    out=out[:n_tok], gnorm_weight=self._gnorm_w(q.device),
-                                   gnorm_eps=self.norm_eps, relu_qk=True)
+                                   gnorm_eps=self.norm_eps, relu_qk=True,
+                                   gate_table=ops.gla_gate_7b_table(self.gate_logit_normalizer, q.device))
         if attn_metadata.num_decode_tokens > 0:
             self._decode(q, k, v, gk, kv_cache, state_indices_tensor, attn_metadata,
                          out=out[attn_metadata.num_prefill_tokens:])

@@ -121,11 +121,14 @@ def gla_prefill_varlen(q, k, v, g, state, cu_seqlens, slot_idx, init_mode,
                        write_state: bool = True, max_seqlen: Optional[int] = None,
                        out: Optional[torch.Tensor] = None, seg_len: Optional[int] = None,
                        gnorm_weight: Optional[torch.Tensor] = None,
-                       gnorm_eps: float = 1e-6, relu_qk: bool = False) -> torch.Tensor:
+                       gnorm_eps: float = 1e-6, relu_qk: bool = False,
+                       gate_table: Optional[torch.Tensor] = None) -> torch.Tensor:
     """q [T,H,D]; k,g [T,Hk,D]; v [T,Hv,D]; state [slots,Hs,D,D]; cu_seqlens [N+1], slot_idx [N],
     init_mode [N] int32 device tensors.  Returns o [T,H,D] bf16; writes final states.
     gnorm_weight [D] bf16: the 7B per-head ``g_norm`` RMSNorm applied as the kernel's epilogue.
-    relu_qk: q and k are raw projection rows, relu is applied in the kernel."""
+    relu_qk: q and k are raw projection rows, relu is applied in the kernel.
+    gate_table (``gla_gate_7b_table``): g holds the RAW bf16 gk rows and the kernel maps them through
+    the table -- no separate gate pass."""
     T, H, D = q.shape
     Hk, Hv, Hs = k.shape[1], v.shape[1], state.shape[1]
     if g.shape[1] != Hk:
@@ -154,6 +157,10 @@ def gla_prefill_varlen(q, k, v, g, state, cu_seqlens, slot_idx, init_mode,
         _req(gnorm_weight, "gnorm_weight", torch.bfloat16)
         if gnorm_weight.numel() != D:
             raise ValueError("gnorm_weight must hold head_dim elements")
+    if gate_table is not None:
+        _req(gate_table, "gate_table", torch.bfloat16)
+        if gate_table.numel() != 65536 or not gate_table.is_contiguous() or g.dtype != torch.bfloat16:
+            raise ValueError("gate_table must be a contiguous [65536] bf16 tensor and g the raw bf16 gate rows")
     check(lib().hymeta_gla_prefill_varlen_fused(
         _ptr(q), _ptr(k), _ptr(v), _ptr(g), _ptr(out), _ptr(state), _ptr(meta_state),
         _ptr(cu_seqlens), _ptr(slot_idx), _ptr(init_mode), N, T, H, Hk, Hv, Hs, D,
@@ -162,7 +169,7 @@ def gla_prefill_varlen(q, k, v, g, state, cu_seqlens, slot_idx, init_mode,
         0 if meta_state is None else meta_state.stride(0),
         int(g.dtype == torch.float32), float(scale), int(write_state), msl,
         int(seg_len or 0), _ptr(ws), ws_bytes, _ptr(gnorm_weight), float(gnorm_eps), int(bool(relu_qk)),
-        _stream()), "hymeta_gla_prefill_varlen_seg")
+        _ptr(gate_table), _stream()), "hymeta_gla_prefill_varlen_seg")
     return out
 
 
@@ -273,6 +280,26 @@ def gla_gate_7b_g(gk: torch.Tensor, normalizer: float = 16.0, out: Optional[torc
                                      g_out.stride(0), g_out.stride(1), float(normalizer), _stream()),
           "hymeta_gla_gate_7b_g")
     return g_out
+
+
+_GATE_TABLES = {}
+
+
+def gla_gate_7b_table(normalizer: float = 16.0, device=None) -> torch.Tensor:
+    """[65536] bf16: ``gla_gate_7b_g`` applied to every bf16 bit pattern -- the 7B gate
+    bf16(bf16(logsigmoid(gk)) / normalizer) is a pure function of its 16-bit input, so the GLA prefill
+    kernel's gate warps look it up (``gla_prefill_varlen(gate_table=...)``) instead of a separate pass
+    over the activations.  Built once per (device, normalizer) with the gate kernel itself, hence
+    bit-identical to it."""
+    device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+    key = (device.index, float(normalizer))
+    t = _GATE_TABLES.get(key)
+    if t is None:
+        if torch.cuda.is_current_stream_capturing():
+            raise RuntimeError("build the gate table with an eager call before CUDA-graph capture")
+        bits = torch.arange(65536, dtype=torch.int32, device=device).to(torch.int16).view(torch.bfloat16)
+        t = _GATE_TABLES[key] = gla_gate_7b_g(bits.view(512, 1, 128), normalizer).view(-1).contiguous()
+    return t
 
 
 # ----------------------------------------------------------------------------------- a9
