@@ -211,78 +211,73 @@ __global__ void __launch_bounds__(GD_THREADS, 2) gla_decode_kernel(const GlaDeco
         s_kg[row].y = __float_as_uint(__expf(gv));
       }
     }
-    const uint4 vraw = *reinterpret_cast<const uint4*>(sbase + GD_RAW_V + c * 16);
-    const uint32_t vv[4] = {vraw.x, vraw.y, vraw.z, vraw.w};
+    // Main loop: a lane owns 4 consecutive d_v columns (8 bytes per row) of ALL 16 rows of its warp,
+    // so a warp instruction moves one whole 256-byte state row and the d_k reduction inside a warp
+    // is the lane's own accumulation.  (With 8 columns per lane and the rows split over the two
+    // half-warps, the epilogue needed 64 shuffles per thread -- at one warp-shuffle per clock per SM
+    // that was a third of the per-item time at B = 64 -- and 8 x GT packed accumulators spilled.)
+    const uint2 vraw = *reinterpret_cast<const uint2*>(sbase + GD_RAW_V + lane * 8);
+    const uint32_t vv[2] = {vraw.x, vraw.y};
     __nv_bfloat16* sp = p.state + (int64_t)cur_slot * p.st_ss + (int64_t)cur_i.hs * p.st_sh +
-                        (warp * 16 + rg) * kD + c * 8;
-    const uint32_t st_base = ring + stage * GD_STAGE + (warp * 16 + rg) * 256 + c * 16;
+                        (warp * 16) * kD + lane * 4;
+    const uint32_t st_base = ring + stage * GD_STAGE + (warp * 16) * 256 + lane * 8;
     __syncwarp();
 
-    u64 acc[GT][4];
+    u64 acc[GT][2];
 #pragma unroll
-    for (int hh = 0; hh < GT; ++hh)
-#pragma unroll
-      for (int j = 0; j < 4; ++j) acc[hh][j] = 0ull;
+    for (int hh = 0; hh < GT; ++hh) { acc[hh][0] = 0ull; acc[hh][1] = 0ull; }
 
-    const uint2* kgp = s_kg + warp * 16 + rg;
-    const float* qrow = &s_q[warp * 16 + rg][0];
+    const uint2* kgp = s_kg + warp * 16;
+    const float* qrow = &s_q[warp * 16][0];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {                    // row r = warp*16 + 2i + rg
-      uint4 w4;
-      asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];"
-                   : "=r"(w4.x), "=r"(w4.y), "=r"(w4.z), "=r"(w4.w) : "r"(st_base + i * 512));
-      const uint2 kg = kgp[2 * i];
+    for (int i = 0; i < 16; ++i) {                   // row r = warp*16 + i
+      uint2 w2;
+      asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(w2.x), "=r"(w2.y) : "r"(st_base + i * 256));
+      const uint2 kg = kgp[i];
       const float eg = __uint_as_float(kg.y);
-      const uint32_t w[4] = {w4.x, w4.y, w4.z, w4.w};
-      u64 sn[4];   // new state, fp32 pairs, un-rounded (the output reduces this, my_fused_recurrent.py:75)
+      const uint32_t w[2] = {w2.x, w2.y};
+      u64 sn[2];   // new state, fp32 pairs, un-rounded (the output reduces this, my_fused_recurrent.py:75)
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
+      for (int j = 0; j < 2; ++j) {
         const uint32_t kv = hmul2_bf16(kg.x, vv[j]);            // bf16(k * v), both columns
         sn[j] = ffma2(pack2(eg, eg), pack2(bf16_lo(w[j]), bf16_hi(w[j])),
                       pack2(bf16_lo(kv), bf16_hi(kv)));
       }
       {
-        uint4 st;
+        uint2 st;
         float a, bb;
         unpack2(sn[0], a, bb); st.x = pack_bf16(a, bb);
         unpack2(sn[1], a, bb); st.y = pack_bf16(a, bb);
-        unpack2(sn[2], a, bb); st.z = pack_bf16(a, bb);
-        unpack2(sn[3], a, bb); st.w = pack_bf16(a, bb);
-        stg_v4(sp + i * 2 * kD, st);
+        asm volatile("st.global.L1::no_allocate.v2.u32 [%0], {%1,%2};"
+                     :: "l"(sp + i * kD), "r"(st.x), "r"(st.y) : "memory");
       }
       float qr[8];
       {
-        const float4 t0 = *reinterpret_cast<const float4*>(qrow + i * 16);
+        const float4 t0 = *reinterpret_cast<const float4*>(qrow + i * 8);
         qr[0] = t0.x; qr[1] = t0.y; qr[2] = t0.z; qr[3] = t0.w;
         if (GT > 4) {
-          const float4 t1 = *reinterpret_cast<const float4*>(qrow + i * 16 + 4);
+          const float4 t1 = *reinterpret_cast<const float4*>(qrow + i * 8 + 4);
           qr[4] = t1.x; qr[5] = t1.y; qr[6] = t1.z; qr[7] = t1.w;
         }
       }
 #pragma unroll
       for (int hh = 0; hh < GT; ++hh) {
         const u64 q2 = pack2(qr[hh], qr[hh]);
-#pragma unroll
-        for (int j = 0; j < 4; ++j) acc[hh][j] = ffma2(q2, sn[j], acc[hh][j]);
+        acc[hh][0] = ffma2(q2, sn[0], acc[hh][0]);
+        acc[hh][1] = ffma2(q2, sn[1], acc[hh][1]);
       }
     }
 
-    // reduce over d_k: the two rows of a warp instr by shuffle, then the 8 warps through smem
+    // reduce over d_k across the 8 warps through smem
     // (the scratch aliases this item's state: every thread is done reading it after the barrier)
     __syncthreads();
     float* s_red = reinterpret_cast<float*>(sbase);   // [8][GT][128]
 #pragma unroll
     for (int hh = 0; hh < GT; ++hh) {
-      float a[8];
-#pragma unroll
-      for (int j = 0; j < 4; ++j) unpack2(acc[hh][j], a[2 * j], a[2 * j + 1]);
-#pragma unroll
-      for (int j = 0; j < 8; ++j) a[j] += __shfl_xor_sync(0xffffffffu, a[j], 16);
-      if (lane < 16) {
-        float4* dst = reinterpret_cast<float4*>(&s_red[(warp * GT + hh) * kD + c * 8]);
-        dst[0] = make_float4(a[0], a[1], a[2], a[3]);
-        dst[1] = make_float4(a[4], a[5], a[6], a[7]);
-      }
+      float4 a;
+      unpack2(acc[hh][0], a.x, a.y);
+      unpack2(acc[hh][1], a.z, a.w);
+      *reinterpret_cast<float4*>(&s_red[(warp * GT + hh) * kD + lane * 4]) = a;
     }
     __syncthreads();
     if (GN) {
