@@ -404,9 +404,7 @@ extern "C" int hymeta_gla_decode_gate7b(const void* q, const void* k, const void
   const bool f = g_is_fp32 != 0;
   if (G == 1) launch_gla_decode<1>(p, f, st);
   else if (G <= 4) launch_gla_decode<4>(p, f, st);
-  // G == 7 runs the 8-head instantiation: 7 x 4 packed accumulators spill under the 128-register
-  // cap of 2 CTAs per SM (23 STL / 39 LDL in the loop), 8 x 4 allocate cleanly -- 90 -> 69 us at
-  // B = 1000 with the g_norm epilogue, 9.5 -> 8.8 us at B = 64
+  else if (G == 7) launch_gla_decode<7>(p, f, st);   // spill-free since a lane holds 2 (not 4) packed accumulators per head
   else launch_gla_decode<8>(p, f, st);
   count_launch();
   return check_launch();
