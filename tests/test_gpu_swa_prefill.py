@@ -80,3 +80,19 @@ def test_suffix_queries(ops):
 
 def test_meta_queries_only(ops):
     run_case(ops, [], [], 28, 4, 128, 4095, True, 6)
+
+
+def test_persistent_scheduler_many_items_and_empty_requests(ops):
+    """More work items than CTAs (28 heads x 6 pair levels x 41 requests incl. the meta-query
+    pseudo-request), empty requests in the middle of the batch, one request longer than the rest:
+    every CTA of the persistent kernel walks several items, skips empty ones and hands TMEM / rings
+    from item to item."""
+    lens = [0, 257, 1, 0, 1500, 256, 255, 33, 700, 0] * 4
+    run_case(ops, lens, lens, 28, 4, 128, 300, True, 7)
+
+
+def test_persistent_scheduler_suffix_queries_mixed(ops):
+    """Chunk-shaped work (few queries at the end of long key ranges) next to whole prompts."""
+    q_lens = [16, 300, 1, 64, 5]
+    k_lens = [900, 300, 2000, 64, 700]
+    run_case(ops, q_lens, k_lens, 14, 2, 128, 511, False, 8)
