@@ -292,6 +292,8 @@ def gla_gate_7b_table(normalizer: float = 16.0, device=None) -> torch.Tensor:
     over the activations.  Built once per (device, normalizer) with the gate kernel itself, hence
     bit-identical to it."""
     device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+    if device.index is None:
+        device = torch.device("cuda", torch.cuda.current_device())
     key = (device.index, float(normalizer))
     t = _GATE_TABLES.get(key)
     if t is None:
