@@ -190,7 +190,9 @@ int hymeta_gla_gate_7b(const void* q_in, const void* k_in, const void* gk_in, vo
  *                                 the 7B gate is a pure function of a 16-bit input; the table is
  *                                 hymeta_gla_gate_7b_g applied once to all 65536 bit patterns, so the
  *                                 result is bit-identical to the separate pass and the layer's
- *                                 prefill is ONE launch.
+ *                                 prefill is ONE launch.  sumsq_out (null, or [T, H] fp32): the O
+ *                                 epilogue also emits each bf16 output row's sum of squares (f1: the
+ *                                 branch merge's RMS-norm partials).
  * hymeta_gla_decode_gate7b:       hymeta_gla_decode_gnorm plus gate_normalizer: 0 = plain; > 0 = q, k
  *                                 and g are raw q / k / gk rows (g bf16) and relu / logsigmoid /
  *                                 division run in the kernel's operand conversion, bit-identical to
@@ -207,7 +209,7 @@ int hymeta_gla_prefill_varlen_fused(
     int64_t g_sh, int64_t o_st, int64_t o_sh, int64_t st_ss, int64_t st_sh, int64_t meta_sh,
     int g_is_fp32, float scale, int write_state, int max_seqlen, int seg_len, void* workspace,
     size_t workspace_bytes, const void* gnorm_weight, float gnorm_eps, int relu_qk,
-    const void* gate_table, void* stream);
+    const void* gate_table, float* sumsq_out, void* stream);
 int hymeta_gla_decode_gate7b(const void* q, const void* k, const void* v, const void* g, void* o,
                              void* state, const int32_t* slot_idx, int B, int H, int Hk, int Hv,
                              int Hs, int D, int64_t q_sb, int64_t q_sh, int64_t k_sb, int64_t k_sh,
@@ -416,6 +418,26 @@ int hymeta_branch_norm_merge_tp(const void* x_attn, const void* x_linear, const 
                                 int tp_world, int tp_rank, const uint64_t* peer_buffers,
                                 int64_t t_cap, uint32_t epoch, float eps, int64_t xa_st,
                                 int64_t xl_st, int64_t o_st, void* stream);
+/* Same, with the per-(token, head) sums of squares the attention kernels' epilogues emitted
+ * (hymeta_swa_meta_prefill_varlen_sumsq / hymeta_gla_prefill_varlen_fused: [T, heads_local] fp32, row
+ * stride heads_local): the merge then reads x exactly once -- SURVEY 8f f1 as specified.  Either both
+ * or neither of sumsq_attn / sumsq_linear. */
+int hymeta_branch_norm_merge_tp_sumsq(const void* x_attn, const void* x_linear, const float* w_attn,
+                                      const float* w_linear, void* out, int T, int hidden_local,
+                                      int tp_world, int tp_rank, const uint64_t* peer_buffers,
+                                      int64_t t_cap, uint32_t epoch, float eps, int64_t xa_st,
+                                      int64_t xl_st, int64_t o_st, const float* sumsq_attn,
+                                      const float* sumsq_linear, int heads_local, void* stream);
+/* hymeta_swa_meta_prefill_varlen plus sumsq_out ([rows, H] fp32, rows as `out`; null = plain): each
+ * output row's sum of squares over the head's 128 bf16 values, from the kernel's epilogue. */
+int hymeta_swa_meta_prefill_varlen_sumsq(
+    const void* q1, const void* k1, const void* v1, const void* q2, const void* meta_k,
+    const void* meta_v, void* out, const int32_t* cu_seqlens_q, const int32_t* cu_seqlens_k,
+    const int32_t* block_tables, int64_t bt_stride, int block_size, int N, int Tq, int Tk, int H,
+    int Hkv, int D, int M, int max_seqlen_q, int window_left, float scale, int64_t q_st,
+    int64_t q_sh, int64_t k_st, int64_t k_sh, int64_t v_st, int64_t v_sh, int64_t q2_st,
+    int64_t q2_sh, int64_t mk_st, int64_t mk_sh, int64_t mv_st, int64_t mv_sh, int64_t o_st,
+    int64_t o_sh, int64_t kc_sblk, int64_t vc_sblk, float* sumsq_out, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * f4  Host-side state-slot manager -- replaces the bookkeeping of vLLM 0.10.0's ConstantSizeCache

@@ -42,7 +42,15 @@ def _worker(rank: int, world: int, port: int, q):
             for rep in range(3):                             # epochs advance, both slot parities get used
                 fused = ops.branch_norm_merge(dxa, dxl, dw1, dw2, eps, tp_world=world, exchange=ex)
             nccl = ops.branch_norm_merge(dxa, dxl, dw1, dw2, eps, tp_world=world)
+            # f1 as specified: the per-(token, head) partials the attention epilogues emit feed the merge
+            heads = hl // 128
+            sa = dxa.float().view(T, heads, 128).pow(2).sum(-1).contiguous()
+            sb = dxl.float().view(T, heads, 128).pow(2).sum(-1).contiguous()
+            fused_ss = ops.branch_norm_merge(dxa, dxl, dw1, dw2, eps, tp_world=world, exchange=ex, sumsq=(sa, sb))
             torch.cuda.synchronize()
+            d_ss = (fused_ss.float() - fused.float()).abs()
+            assert (d_ss > 0).float().mean().item() < 0.01 and \
+                (d_ss <= 2.0 ** -6 * fused.float().abs().clamp(min=1.0)).all(), (T, hidden, d_ss.max().item())
             for name, got in (("fused", fused), ("nccl", nccl)):
                 diff = (got.float().cpu() - ref.float()).abs()
                 bad = int((diff > 2.0 ** -6 * ref.float().abs().clamp(min=1.0)).sum())

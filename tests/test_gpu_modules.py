@@ -244,6 +244,36 @@ def test_gate_7b_folded_into_gla_kernels(ops):
         assert torch.equal(d1, d2) and torch.equal(s1, s2)
 
 
+def test_prefill_epilogues_emit_sumsq_partials(ops):
+    """f1: both prefill kernels can emit, per (output row, head), the sum of squares of the bf16 row
+    they store -- the branch merge's RMS-norm partials.  Checked against the same sum taken in torch
+    from the kernels' own outputs (fp32 summation order differs: relative 1e-5)."""
+    H, Hkv, M = 14, 2, 128
+    lens = [300, 70, 513]
+    T = sum(lens)
+    gen = torch.Generator().manual_seed(41)
+    cu = torch.tensor([0, 300, 370, T], dtype=torch.int32, device=DEV)
+    q = torch.randn(T, H, D, generator=gen).bfloat16().to(DEV)
+    k = torch.randn(T, Hkv, D, generator=gen).bfloat16().to(DEV)
+    v = torch.randn(T, Hkv, D, generator=gen).bfloat16().to(DEV)
+    mk = torch.randn(M, Hkv, D, generator=gen).bfloat16().to(DEV)
+    mv = torch.randn(M, Hkv, D, generator=gen).bfloat16().to(DEV)
+    q2 = torch.randn(M, H, D, generator=gen).bfloat16().to(DEV)
+    ss = torch.full((M + T, H), -1.0, dtype=torch.float32, device=DEV)
+    o = ops.swa_meta_prefill_varlen(q, k, v, q2, mk, mv, cu, cu, max(lens), 4095, sumsq_out=ss)
+    ref = o.float().pow(2).sum(-1)
+    assert torch.allclose(ss, ref, rtol=1e-5, atol=1e-6), (ss - ref).abs().max().item()
+    # GLA prefill (70B-style fp32 gates, meta-state init)
+    qg, kg, vg, gg = ogla.synth_gla_inputs(T, H, Hkv, D, "70b", seed=42)
+    state = torch.zeros(4, Hkv, D, D, dtype=torch.bfloat16, device=DEV)
+    ss2 = torch.full((T, H), -1.0, dtype=torch.float32, device=DEV)
+    i32 = lambda x: torch.tensor(x, dtype=torch.int32, device=DEV)
+    og = ops.gla_prefill_varlen(qg.to(DEV), kg.to(DEV), vg.to(DEV), gg.to(DEV), state, cu, i32([0, 1, 2]),
+                                i32([0, 0, 0]), sumsq_out=ss2)
+    ref2 = og.float().pow(2).sum(-1)
+    assert torch.allclose(ss2, ref2, rtol=1e-5, atol=1e-6), (ss2 - ref2).abs().max().item()
+
+
 # ------------------------------------------------------------------------------------- a7-a10 (backend)
 def test_flash_attention_backend_warmup_then_decode(ops):
     from vllm_hymeta_b200.attention.meta_attention import MetaAttentionMetadataBuilder, SeqData

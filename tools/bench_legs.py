@@ -258,16 +258,21 @@ def extra_configs(dev="cuda", world=1, rank=0, tp_group=None, plan=None):
 
     def layer():
         q2, k2, g2 = ops.gla_gate_70b(gq, gk)
-        ops.gla_prefill_varlen(q2, k2, gv, g2, state, cu, slots, mode, meta_state=meta_state, max_seqlen=T, out=o_gla)
+        ops.gla_prefill_varlen(q2, k2, gv, g2, state, cu, slots, mode, meta_state=meta_state, max_seqlen=T, out=o_gla,
+                               sumsq_out=ss_gla)
         ops.rope_kv_write_paged(sq, sk, sv, table, pos, M, kv[0], kv[1], slot_map)
-        ops.swa_meta_prefill_varlen(sq, sk, sv, None, mk, mv, cu, cu, T, 4095, out=o_swa)
+        ops.swa_meta_prefill_varlen(sq, sk, sv, None, mk, mv, cu, cu, T, 4095, out=o_swa, sumsq_out=ss_swa)
         xa, xl = o_swa.view(Tt, h * D), o_gla.view(Tt, h * D)
         if tp > 1 and exchange is not None:   # one kernel: local means -> NVLink peer-memory exchange -> merge (f1)
-            ops.branch_norm_merge(xa, xl, w1, w2, 1e-6, tp_world=tp, out=merged, exchange=exchange)
+            ops.branch_norm_merge(xa, xl, w1, w2, 1e-6, tp_world=tp, out=merged, exchange=exchange,
+                                  sumsq=(ss_swa, ss_gla))
         elif tp > 1:
             ops.branch_norm_merge(xa, xl, w1, w2, 1e-6, tp_world=tp, out=merged, group=tp_group)
         else:
             ops.branch_norm_merge(xa, xl, w1, w2, 1e-6, out=merged)
+    # f1 as specified: the attention epilogues emit the per-(token, head) sums of squares the merge needs
+    ss_swa = torch.empty(Tt, h, dtype=torch.float32, device=dev) if tp > 1 else None
+    ss_gla = torch.empty(Tt, h, dtype=torch.float32, device=dev) if tp > 1 else None
     exchange = None
     if tp > 1:
         # the peer-memory exchange is collective: every rank of the job agrees on whether it came up
@@ -288,7 +293,7 @@ def extra_configs(dev="cuda", world=1, rank=0, tp_group=None, plan=None):
     out["config3_70b_hybrid_layer_32k"] = {
         "plan": f"tp{plan.tp} x dp{plan.dp}", "heads_per_gpu": [h, hkv], "prompts": plan.dp * P, "prompt_len": T,
         "meta_tokens": M, "layer_ms": t * 1e3, "tok_s_per_layer": plan.dp * Tt / t,
-        "exchange": ("none" if tp == 1 else "fused branch-merge kernel: 16 B per token and peer over NVLink peer memory (f1)"
+        "exchange": ("none" if tp == 1 else "fused branch-merge kernel: sum-of-squares partials from the attention epilogues, 16 B per token and peer over NVLink peer memory (f1)"
                      if exchange is not None else "one NCCL all-reduce of 8*T bytes per layer (f1; peer memory unavailable)"),
         "swa_flops_per_gpu": P * h * 4 * D * n_keys}
     del qkv_g, qkv_s, kv, o_gla, o_swa, merged, slot_map

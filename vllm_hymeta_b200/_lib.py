@@ -32,7 +32,7 @@ SIGNATURES = {
     "hymeta_gla_gate_7b": (_i, [_p] * 6 + [_i] * 4 + [_i64] * 12 + [_f, _p]),
     "hymeta_gla_gate_7b_g": (_i, [_p, _p, _i, _i, _i] + [_i64] * 4 + [_f, _p]),
     "hymeta_gla_prefill_varlen_fused": (_i, [_p] * 10 + [_i] * 7 + [_i64] * 13 +
-                                        [_i, _f, _i, _i, _i, _p, _sz, _p, _f, _i, _p, _p]),
+                                        [_i, _f, _i, _i, _i, _p, _sz, _p, _f, _i, _p, _p, _p]),
     "hymeta_gla_decode_gate7b": (_i, [_p] * 7 + [_i] * 6 + [_i64] * 12 + [_i, _f, _p, _f, _f, _p]),
     "hymeta_kv_write_paged": (_i, [_p] * 5 + [_i] * 4 + [_i64] * 10 + [_p]),
     "hymeta_rope_kv_write_paged": (_i, [_p] * 6 + [_i, _p, _i64] + [_p] * 5 + [_i] * 6 + [_i64] * 20 + [_i, _p]),
@@ -50,6 +50,9 @@ SIGNATURES = {
     "hymeta_branch_norm_merge": (_i, [_p] * 6 + [_i, _i, _i, _f, _i64, _i64, _i64, _p]),
     "hymeta_branch_merge_tp_buffer_bytes": (_sz, [_i, _i64]),
     "hymeta_branch_norm_merge_tp": (_i, [_p] * 5 + [_i] * 4 + [_p, _i64, C.c_uint32, _f, _i64, _i64, _i64, _p]),
+    "hymeta_branch_norm_merge_tp_sumsq": (_i, [_p] * 5 + [_i] * 4 + [_p, _i64, C.c_uint32, _f, _i64, _i64, _i64,
+                                              _p, _p, _i, _p]),
+    "hymeta_swa_meta_prefill_varlen_sumsq": (_i, [_p] * 10 + [_i64, _i] + [_i] * 9 + [_f] + [_i64] * 16 + [_p, _p]),
     "hymeta_slot_mgr_create": (_p, [_i]),
     "hymeta_slot_mgr_destroy": (None, [_p]),
     "hymeta_slot_mgr_release": (_i, [_p, _p, _i]),

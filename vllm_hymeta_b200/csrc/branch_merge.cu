@@ -207,7 +207,8 @@ branch_norm_merge_tp_kernel(const __nv_bfloat16* x1, const __nv_bfloat16* x2,
                             const float* __restrict__ w1, const float* __restrict__ w2,
                             __nv_bfloat16* out, int T, int hidden, int world, int rank, uint32_t epoch,
                             int64_t t_cap, const TpPeers peers, float eps, int64_t x1_st, int64_t x2_st,
-                            int64_t o_st) {
+                            int64_t o_st, const float* __restrict__ ss1, const float* __restrict__ ss2,
+                            int heads) {
   const int lane = threadIdx.x & 31, wpb = blockDim.x >> 5;
   const int chunks = hidden / 8;
   const float inv = 1.f / (float)hidden, inv_tp = 1.f / (float)world;
@@ -229,7 +230,17 @@ branch_norm_merge_tp_kernel(const __nv_bfloat16* x1, const __nv_bfloat16* x2,
       m1[j] = m2[j] = 0.f;
       if (t < T) {
         float s1, s2;
-        row_sumsq2(x1 + t * x1_st, x2 + t * x2_st, chunks, lane, s1, s2);
+        if (ss1) {   // per-head partials from the attention kernels' epilogues: x is not read here
+          s1 = s2 = 0.f;
+          for (int h = lane; h < heads; h += 32) { s1 += ss1[(int64_t)t * heads + h]; s2 += ss2[(int64_t)t * heads + h]; }
+#pragma unroll
+          for (int off = 16; off > 0; off >>= 1) {
+            s1 += __shfl_xor_sync(0xffffffffu, s1, off);
+            s2 += __shfl_xor_sync(0xffffffffu, s2, off);
+          }
+        } else {
+          row_sumsq2(x1 + t * x1_st, x2 + t * x2_st, chunks, lane, s1, s2);
+        }
         m1[j] = s1 * inv; m2[j] = s2 * inv;
         if (push)
           asm volatile("st.volatile.global.v4.u32 [%0], {%1,%2,%3,%4};"
@@ -373,12 +384,15 @@ extern "C" size_t hymeta_branch_merge_tp_buffer_bytes(int tp_world, int64_t t_ca
   return (size_t)2 * tp_world * (size_t)t_cap * sizeof(uint4);
 }
 
-extern "C" int hymeta_branch_norm_merge_tp(const void* x_attn, const void* x_linear, const float* w_attn,
+extern "C" int hymeta_branch_norm_merge_tp_sumsq(const void* x_attn, const void* x_linear, const float* w_attn,
                                            const float* w_linear, void* out, int T, int hidden_local,
                                            int tp_world, int tp_rank, const uint64_t* peer_buffers,
                                            int64_t t_cap, uint32_t epoch, float eps, int64_t xa_st,
-                                           int64_t xl_st, int64_t o_st, void* stream) {
+                                           int64_t xl_st, int64_t o_st, const float* sumsq_attn,
+                                           const float* sumsq_linear, int heads_local, void* stream) {
   if (T == 0) return HYMETA_OK;
+  if ((sumsq_attn == nullptr) != (sumsq_linear == nullptr) || (sumsq_attn && heads_local <= 0))
+    return HYMETA_ERR_INVALID_ARG;
   const int rc = check_common(x_attn, x_linear, T, hidden_local, xa_st, xl_st);
   if (rc) return rc;
   if (!w_attn || !w_linear || !out || !peer_buffers || o_st % 8) return HYMETA_ERR_INVALID_ARG;
@@ -400,9 +414,20 @@ extern "C" int hymeta_branch_norm_merge_tp(const void* x_attn, const void* x_lin
     const int grid = want < cap ? want : cap;
     kernel<<<grid, 128, 0, (cudaStream_t)stream>>>(
         (const __nv_bfloat16*)x_attn, (const __nv_bfloat16*)x_linear, w_attn, w_linear, (__nv_bfloat16*)out, T,
-        hidden_local, tp_world, tp_rank, epoch, t_cap, peers, eps, xa_st, xl_st, o_st);
+        hidden_local, tp_world, tp_rank, epoch, t_cap, peers, eps, xa_st, xl_st, o_st, sumsq_attn, sumsq_linear,
+        heads_local);
   };
   go(branch_norm_merge_tp_kernel);
   count_launch();
   return check_launch();
+}
+
+extern "C" int hymeta_branch_norm_merge_tp(const void* x_attn, const void* x_linear, const float* w_attn,
+                                           const float* w_linear, void* out, int T, int hidden_local,
+                                           int tp_world, int tp_rank, const uint64_t* peer_buffers,
+                                           int64_t t_cap, uint32_t epoch, float eps, int64_t xa_st,
+                                           int64_t xl_st, int64_t o_st, void* stream) {
+  return hymeta_branch_norm_merge_tp_sumsq(x_attn, x_linear, w_attn, w_linear, out, T, hidden_local, tp_world,
+                                           tp_rank, peer_buffers, t_cap, epoch, eps, xa_st, xl_st, o_st, nullptr,
+                                           nullptr, 0, stream);
 }

@@ -73,6 +73,8 @@ struct GlaPrefillParams {
   float gnorm_eps;
   uint32_t relu_lim;              // bf16x2 lower limit applied to q and k: 0 = relu (7B feature map on raw
                                   // projection outputs), 0xff80ff80 (-inf) = identity
+  float* sumsq;                   // f1: null, or [T, H] fp32 -- sum of squares of each bf16 output row (the branch
+                                  // merge's RMS-norm partials), emitted by the O epilogue
   const uint16_t* gate_table;     // null, or [65536] bf16: g = table[raw bf16 gate bits] -- the 7B gate
                                   // bf16(bf16(logsigmoid(gk)) / normalizer) is a pure function of a 16-bit
                                   // input, tabulated once per normalizer by hymeta_gla_gate_7b_g itself
@@ -591,6 +593,7 @@ gla_prefill_kernel(const GlaPrefillParams p, const __grid_constant__ CUtensorMap
             rstd = rsqrtf(ss * (1.f / kD) + p.gnorm_eps);
           }
           const uint32_t* gw = reinterpret_cast<const uint32_t*>(smem + GP_GW);
+          float ssq = 0.f;
 #pragma unroll 1
           for (int cc = 0; cc < ((GP_EXP & 1) ? 0 : 4); ++cc) {
             uint32_t ob[16];   // 32 output columns, packed bf16x2
@@ -609,6 +612,13 @@ gla_prefill_kernel(const GlaPrefillParams p, const __grid_constant__ CUtensorMap
                 tmem_ld16(tOw + 32 * cc + 16 * hf, t);
 #pragma unroll
                 for (int j = 0; j < 8; ++j) ob[8 * hf + j] = pack_bf16(t[2 * j], t[2 * j + 1]);
+              }
+            }
+            if (p.sumsq) {
+#pragma unroll
+              for (int j = 0; j < 16; ++j) {
+                ssq = fmaf(bf16_lo(ob[j]), bf16_lo(ob[j]), ssq);
+                ssq = fmaf(bf16_hi(ob[j]), bf16_hi(ob[j]), ssq);
               }
             }
             // 32 rows x 64 bytes staged per warp (chunks XOR-swizzled), read back so that four lanes
@@ -633,6 +643,8 @@ gla_prefill_kernel(const GlaPrefillParams p, const __grid_constant__ CUtensorMap
             }
             __syncwarp();
           }
+          if (p.sumsq && (tq >> 4) < G && r_t < clen)
+            p.sumsq[(int64_t)(tok_begin + i * GC + r_t) * p.H + h0 + (tq >> 4)] = ssq;
         }
         ++cnt;
       }
@@ -695,7 +707,8 @@ extern "C" int hymeta_gla_prefill_varlen_fused(
     int64_t k_st, int64_t k_sh, int64_t v_st, int64_t v_sh, int64_t g_st, int64_t g_sh, int64_t o_st,
     int64_t o_sh, int64_t st_ss, int64_t st_sh, int64_t meta_sh, int g_is_fp32, float scale,
     int write_state, int max_seqlen, int seg_len, void* workspace, size_t workspace_bytes,
-    const void* gnorm_weight, float gnorm_eps, int relu_qk, const void* gate_table, void* stream) {
+    const void* gnorm_weight, float gnorm_eps, int relu_qk, const void* gate_table, float* sumsq_out,
+    void* stream) {
   if (N == 0) return HYMETA_OK;
   if (gate_table && g_is_fp32) return HYMETA_ERR_INVALID_ARG;   // the table maps bf16 gate bits
   if (seg_len < 0 || seg_len % GC) return HYMETA_ERR_INVALID_ARG;
@@ -729,6 +742,7 @@ extern "C" int hymeta_gla_prefill_varlen_fused(
   p.gnorm_w = (const __nv_bfloat16*)gnorm_weight; p.gnorm_eps = gnorm_eps;
   p.relu_lim = relu_qk ? 0u : 0xff80ff80u;
   p.gate_table = (const uint16_t*)gate_table;
+  p.sumsq = sumsq_out;
   p.seg_len = seg_len; p.n_segs = n_segs; p.pass = 0; p.ws = (float*)workspace;
   // TMA maps: raw g / k rows ([16 tokens][128 channels] boxes) and v (SWIZZLE_128B 64-wide halves)
   const int64_t tvec[] = {k_st, k_sh, g_st * (g_is_fp32 ? 2 : 1), g_sh * (g_is_fp32 ? 2 : 1)};
@@ -791,7 +805,7 @@ extern "C" int hymeta_gla_prefill_varlen_seg_gnorm(
                                          H, Hk, Hv, Hs, D, q_st, q_sh, k_st, k_sh, v_st, v_sh, g_st, g_sh,
                                          o_st, o_sh, st_ss, st_sh, meta_sh, g_is_fp32, scale, write_state,
                                          max_seqlen, seg_len, workspace, workspace_bytes, gnorm_weight,
-                                         gnorm_eps, 0, nullptr, stream);
+                                         gnorm_eps, 0, nullptr, nullptr, stream);
 }
 
 extern "C" int hymeta_gla_prefill_varlen_seg(

@@ -80,6 +80,9 @@ struct SwaPrefillParams {
   const int32_t* block_tables;
   int64_t bt_stride;
   int paged, block_size, box_rows;
+  // f1: per (output row, head) sum of squares of the bf16 output row, [rows, H] fp32, or null --
+  // the branch merge's RMS norm partials, emitted here so that the merge need not read x for them
+  float* sumsq;
 };
 
 struct QTile { int on, rows, pmin, pmax, lo, hi; };   // real key-tile range [lo, hi] (empty if hi < lo)
@@ -522,6 +525,7 @@ swa_prefill_kernel(const SwaPrefillParams p, const __grid_constant__ CUtensorMap
         for (int j = 0; j < 128; ++j) o[j] = 0u;
       }
       const float inv = l_run > 0.f ? 1.f / l_run : 0.f;
+      float ssq = 0.f;
 #if PF_OPT_EPI
       {
         // Per warp: 32 rows x 64 columns (4 KB, 16-byte chunks XOR-swizzled by row) staged in smem,
@@ -541,6 +545,14 @@ swa_prefill_kernel(const SwaPrefillParams p, const __grid_constant__ CUtensorMap
             v.y = pack_bf16(__uint_as_float(o[8 * j + 2]) * inv, __uint_as_float(o[8 * j + 3]) * inv);
             v.z = pack_bf16(__uint_as_float(o[8 * j + 4]) * inv, __uint_as_float(o[8 * j + 5]) * inv);
             v.w = pack_bf16(__uint_as_float(o[8 * j + 6]) * inv, __uint_as_float(o[8 * j + 7]) * inv);
+            if (p.sumsq) {   // the norm consumes the bf16 values
+              const uint32_t* w4 = &v.x;
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                ssq = fmaf(bf16_lo(w4[e]), bf16_lo(w4[e]), ssq);
+                ssq = fmaf(bf16_hi(w4[e]), bf16_hi(w4[e]), ssq);
+              }
+            }
             *reinterpret_cast<uint4*>(stg + lane * 128 + ((c ^ (lane & 7)) << 4)) = v;
           }
           __syncwarp();
@@ -567,6 +579,7 @@ swa_prefill_kernel(const SwaPrefillParams p, const __grid_constant__ CUtensorMap
         }
       }
 #endif
+      if (p.sumsq && r < T.rows) p.sumsq[(g.o_row + i * PF_BM + r) * p.H + g.h] = ssq;
       gt += g.n_steps;
     }
   } else {
@@ -587,14 +600,14 @@ extern "C" int hymeta_debug_set_swa_trace(void* buf) {
 }
 #endif
 
-extern "C" int hymeta_swa_meta_prefill_varlen(
+extern "C" int hymeta_swa_meta_prefill_varlen_sumsq(
     const void* q1, const void* k1, const void* v1, const void* q2, const void* meta_k,
     const void* meta_v, void* out, const int32_t* cu_q, const int32_t* cu_k,
     const int32_t* block_tables, int64_t bt_stride, int block_size, int N, int Tq, int Tk, int H,
     int Hkv, int D, int M, int max_seqlen_q, int window_left, float scale, int64_t q_st, int64_t q_sh,
     int64_t k_st, int64_t k_sh, int64_t v_st, int64_t v_sh, int64_t q2_st, int64_t q2_sh,
     int64_t mk_st, int64_t mk_sh, int64_t mv_st, int64_t mv_sh, int64_t o_st, int64_t o_sh,
-    int64_t kc_sblk, int64_t vc_sblk, void* stream) {
+    int64_t kc_sblk, int64_t vc_sblk, float* sumsq_out, void* stream) {
   if (N < 0 || Tq < 0 || Tk < 0 || H <= 0 || Hkv <= 0 || M < 0 || !out) return HYMETA_ERR_INVALID_ARG;
   if (D != kD || H % Hkv) return HYMETA_ERR_UNSUPPORTED;
   const bool paged = block_tables != nullptr;
@@ -656,6 +669,7 @@ extern "C" int hymeta_swa_meta_prefill_varlen(
   p.o_st = o_st; p.o_sh = o_sh;
   p.block_tables = block_tables; p.bt_stride = bt_stride;
   p.paged = paged && real ? 1 : 0; p.block_size = paged ? block_size : 1; p.box_rows = box_rows;
+  p.sumsq = sumsq_out;
 
   static DynSmemAttr attr;
   attr.ensure(swa_prefill_kernel, PF_SMEM);
@@ -667,4 +681,19 @@ extern "C" int hymeta_swa_meta_prefill_varlen(
   swa_prefill_kernel<<<grid, PF_THREADS, PF_SMEM, (cudaStream_t)stream>>>(p, tmQ, tmK, tmV, tmQ2, tmMK, tmMV);
   count_launch();
   return check_launch();
+}
+
+extern "C" int hymeta_swa_meta_prefill_varlen(
+    const void* q1, const void* k1, const void* v1, const void* q2, const void* meta_k,
+    const void* meta_v, void* out, const int32_t* cu_q, const int32_t* cu_k,
+    const int32_t* block_tables, int64_t bt_stride, int block_size, int N, int Tq, int Tk, int H,
+    int Hkv, int D, int M, int max_seqlen_q, int window_left, float scale, int64_t q_st, int64_t q_sh,
+    int64_t k_st, int64_t k_sh, int64_t v_st, int64_t v_sh, int64_t q2_st, int64_t q2_sh,
+    int64_t mk_st, int64_t mk_sh, int64_t mv_st, int64_t mv_sh, int64_t o_st, int64_t o_sh,
+    int64_t kc_sblk, int64_t vc_sblk, void* stream) {
+  return hymeta_swa_meta_prefill_varlen_sumsq(q1, k1, v1, q2, meta_k, meta_v, out, cu_q, cu_k, block_tables,
+                                              bt_stride, block_size, N, Tq, Tk, H, Hkv, D, M, max_seqlen_q,
+                                              window_left, scale, q_st, q_sh, k_st, k_sh, v_st, v_sh, q2_st,
+                                              q2_sh, mk_st, mk_sh, mv_st, mv_sh, o_st, o_sh, kc_sblk, vc_sblk,
+                                              nullptr, stream);
 }

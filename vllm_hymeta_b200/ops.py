@@ -122,13 +122,15 @@ def gla_prefill_varlen(q, k, v, g, state, cu_seqlens, slot_idx, init_mode,
                        out: Optional[torch.Tensor] = None, seg_len: Optional[int] = None,
                        gnorm_weight: Optional[torch.Tensor] = None,
                        gnorm_eps: float = 1e-6, relu_qk: bool = False,
-                       gate_table: Optional[torch.Tensor] = None) -> torch.Tensor:
+                       gate_table: Optional[torch.Tensor] = None,
+                       sumsq_out: Optional[torch.Tensor] = None) -> torch.Tensor:
     """q [T,H,D]; k,g [T,Hk,D]; v [T,Hv,D]; state [slots,Hs,D,D]; cu_seqlens [N+1], slot_idx [N],
     init_mode [N] int32 device tensors.  Returns o [T,H,D] bf16; writes final states.
     gnorm_weight [D] bf16: the 7B per-head ``g_norm`` RMSNorm applied as the kernel's epilogue.
     relu_qk: q and k are raw projection rows, relu is applied in the kernel.
     gate_table (``gla_gate_7b_table``): g holds the RAW bf16 gk rows and the kernel maps them through
-    the table -- no separate gate pass."""
+    the table -- no separate gate pass.  sumsq_out [T,H] fp32: the epilogue also writes each bf16
+    output row's sum of squares (f1: RMS-norm partials for ``branch_norm_merge``)."""
     T, H, D = q.shape
     Hk, Hv, Hs = k.shape[1], v.shape[1], state.shape[1]
     if g.shape[1] != Hk:
@@ -169,8 +171,16 @@ def gla_prefill_varlen(q, k, v, g, state, cu_seqlens, slot_idx, init_mode,
         0 if meta_state is None else meta_state.stride(0),
         int(g.dtype == torch.float32), float(scale), int(write_state), msl,
         int(seg_len or 0), _ptr(ws), ws_bytes, _ptr(gnorm_weight), float(gnorm_eps), int(bool(relu_qk)),
-        _ptr(gate_table), _stream()), "hymeta_gla_prefill_varlen_seg")
+        _ptr(gate_table), _ptr(_sumsq_buf(sumsq_out, T, H)), _stream()), "hymeta_gla_prefill_varlen_seg")
     return out
+
+
+def _sumsq_buf(t: Optional[torch.Tensor], rows: int, heads: int) -> Optional[torch.Tensor]:
+    if t is not None:
+        _req(t, "sumsq_out", torch.float32)
+        if t.shape != (rows, heads) or not t.is_contiguous():
+            raise ValueError(f"sumsq_out must be a contiguous [{rows}, {heads}] fp32 tensor")
+    return t
 
 
 _SM_COUNT = {}
@@ -471,13 +481,16 @@ def branch_norm_merge(x_attn: torch.Tensor, x_linear: torch.Tensor, w_attn: torc
                       w_linear: torch.Tensor, eps: float, tp_world: int = 1,
                       means: Optional[torch.Tensor] = None, group=None,
                       out: Optional[torch.Tensor] = None,
-                      exchange: Optional[BranchMergeExchange] = None) -> torch.Tensor:
+                      exchange: Optional[BranchMergeExchange] = None,
+                      sumsq: Optional[tuple] = None) -> torch.Tensor:
     """``((norm1(out_attn) + norm2(out_linear)) / 2).to(bfloat16)`` of the 70B layer
     (modeling_hymeta.py:909-919, HymetaRMSNormTP :151-173).  x_* [T, hidden/tp] bf16, w_* the
     rank's fp32 weight slice.  tp_world > 1 with ``exchange``: ONE kernel computes the local means,
     exchanges them through NVLink peer memory and merges with the rows still in registers.  Without
     it: ``branch_sumsq`` + ONE NCCL all-reduce of 8*T bytes over ``group`` + the merge kernel (pass
-    ``means`` to supply an already reduced buffer)."""
+    ``means`` to supply an already reduced buffer).  ``sumsq`` = (sumsq_attn, sumsq_linear), the
+    [T, heads_local] fp32 partials the attention kernels' epilogues emitted (``sumsq_out=`` of the
+    prefill ops): with ``exchange`` the merge then reads x exactly once."""
     T, Hd = x_attn.shape
     for n, t in (("x_attn", x_attn), ("x_linear", x_linear)):
         _req(t, n, torch.bfloat16)
@@ -492,10 +505,20 @@ def branch_norm_merge(x_attn: torch.Tensor, x_linear: torch.Tensor, w_attn: torc
             raise ValueError("exchange was built for another group size or a smaller token capacity")
         if out is None:
             out = torch.empty(T, Hd, dtype=torch.bfloat16, device=x_attn.device)
-        check(lib().hymeta_branch_norm_merge_tp(
+        sa = sl = None
+        heads = 0
+        if sumsq is not None:
+            sa, sl = sumsq
+            heads = sa.shape[1]
+            for t in (sa, sl):
+                _req(t, "sumsq", torch.float32)
+                if t.shape != (T, heads) or not t.is_contiguous():
+                    raise ValueError("sumsq tensors must be contiguous [T, heads_local] fp32")
+        check(lib().hymeta_branch_norm_merge_tp_sumsq(
             _ptr(x_attn), _ptr(x_linear), _ptr(w_attn), _ptr(w_linear), _ptr(out), T, Hd, tp_world,
             exchange.rank, exchange.ptrs, exchange.t_cap, exchange.next_epoch(), float(eps),
-            x_attn.stride(0), x_linear.stride(0), out.stride(0), _stream()), "hymeta_branch_norm_merge_tp")
+            x_attn.stride(0), x_linear.stride(0), out.stride(0), _ptr(sa), _ptr(sl), heads, _stream()),
+            "hymeta_branch_norm_merge_tp")
         return out
     if tp_world > 1 and means is None:
         import torch.distributed as dist
@@ -615,10 +638,12 @@ def swa_meta_decode_paged(q, k_cache, v_cache, block_tables, cache_seqlens, meta
 def swa_meta_prefill_varlen(q1, k1, v1, q2, meta_k, meta_v, cu_seqlens_q, cu_seqlens_k,
                             max_seqlen_q: int, window_left: int, scale: Optional[float] = None,
                             block_tables: Optional[torch.Tensor] = None,
-                            out: Optional[torch.Tensor] = None) -> torch.Tensor:
+                            out: Optional[torch.Tensor] = None,
+                            sumsq_out: Optional[torch.Tensor] = None) -> torch.Tensor:
     """q1 [Tq,H,D]; k1,v1 [Tk,Hkv,D] (or paged caches [nb,bs,Hkv,D] with block_tables);
     q2 [M,H,D] or None; meta_k/meta_v [M,Hkv,D] or None.  Returns [(M if q2)+Tq, H, D], meta
-    rows first."""
+    rows first.  sumsq_out [rows,H] fp32: the epilogue also writes each bf16 output row's sum of
+    squares (f1: RMS-norm partials for ``branch_norm_merge``)."""
     Tq, H, D = q1.shape
     paged = block_tables is not None
     Hkv = k1.shape[-2]
@@ -653,7 +678,7 @@ def swa_meta_prefill_varlen(q1, k1, v1, q2, meta_k, meta_v, cu_seqlens_q, cu_seq
         Tk, bs = k1.shape[0], 0
         k_st, k_sh, v_st, v_sh = k1.stride(0), k1.stride(1), v1.stride(0), v1.stride(1)
         kc_sblk = vc_sblk = bt_stride = 0
-    check(lib().hymeta_swa_meta_prefill_varlen(
+    check(lib().hymeta_swa_meta_prefill_varlen_sumsq(
         _ptr(q1), _ptr(k1), _ptr(v1), _ptr(q2), _ptr(meta_k), _ptr(meta_v), _ptr(out),
         _ptr(cu_seqlens_q), _ptr(cu_seqlens_k), _ptr(block_tables), bt_stride, bs,
         N, Tq, Tk, H, Hkv, D, M, int(max_seqlen_q), int(window_left), float(scale),
@@ -661,7 +686,7 @@ def swa_meta_prefill_varlen(q1, k1, v1, q2, meta_k, meta_v, cu_seqlens_q, cu_seq
         q2.stride(0) if q2 is not None else 0, q2.stride(1) if q2 is not None else 0,
         meta_k.stride(0) if M else 0, meta_k.stride(1) if M else 0,
         meta_v.stride(0) if M else 0, meta_v.stride(1) if M else 0,
-        out.stride(0), out.stride(1), kc_sblk, vc_sblk, _stream()),
+        out.stride(0), out.stride(1), kc_sblk, vc_sblk, _ptr(_sumsq_buf(sumsq_out, rows, H)), _stream()),
         "hymeta_swa_meta_prefill_varlen")
     return out
 
