@@ -319,6 +319,34 @@ int hymeta_swa_meta_decode_paged_fused(const void* q, void* k_cache, void* v_cac
                                        const int64_t* new_slot_mapping, int32_t* tickets,
                                        void* stream);
 
+/* No-allocation variant of hymeta_swa_meta_decode_paged.  It has NO counterpart in the reference: it
+ * was added for callers that cannot call cudaMalloc (code
+ * under CUDA-graph capture, tight serving loops, harnesses that forbid it).  Same arguments and
+ * results as hymeta_swa_meta_decode_paged minus the workspace: the split-K partials and the combine
+ * tickets live in a static device array inside the library (HYMETA_SWA_DECODE_STATIC_WS_BYTES +
+ * HYMETA_SWA_DECODE_STATIC_TICKET_BYTES bytes on every GPU that loads the library, held until
+ * exit), and the call performs no cudaMalloc / cudaFree / allocating library call -- one
+ * cudaMemsetAsync of the tickets and one kernel launch on `stream`.  Limits: a plan whose partials
+ * (hymeta_swa_decode_workspace_bytes) exceed HYMETA_SWA_DECODE_STATIC_WS_BYTES or whose tickets
+ * (hymeta_swa_decode_ticket_bytes) exceed HYMETA_SWA_DECODE_STATIC_TICKET_BYTES returns
+ * HYMETA_ERR_WORKSPACE and launches nothing (16 MiB covers B x H x splits <= 32 512 rows, e.g.
+ * B = 1000 x 28 heads in one split, or B = 64 x 28 heads in up to 18 splits).  All calls on one GPU
+ * share the array: calls that may overlap on the GPU (different streams without an ordering
+ * between them) race on it -- serialise them, or use the caller-workspace entry points. */
+#define HYMETA_SWA_DECODE_STATIC_WS_BYTES (16u << 20)
+#define HYMETA_SWA_DECODE_STATIC_TICKET_BYTES (64u << 10)
+int hymeta_swa_meta_decode_paged_static(const void* q, const void* k_cache, const void* v_cache,
+                                        const int32_t* block_tables, const int32_t* cache_seqlens,
+                                        const void* meta_k, const void* meta_v, void* out,
+                                        int B, int H, int Hkv, int D, int M, int block_size,
+                                        int num_blocks, int max_blocks, int64_t bt_stride,
+                                        int window_left, float scale,
+                                        int64_t q_sb, int64_t q_sh, int64_t o_sb, int64_t o_sh,
+                                        int64_t kc_sblk, int64_t kc_stok, int64_t kc_sh,
+                                        int64_t vc_sblk, int64_t vc_stok, int64_t vc_sh,
+                                        int64_t mk_st, int64_t mk_sh, int64_t mv_st, int64_t mv_sh,
+                                        void* stream);
+
 /* ------------------------------------------------------------------------------------------------
  * a10 multi-step decode metadata advance -- replaces vllm._custom_ops.advance_step_flashattn as
  *     called by MetaAttentionMetadata.advance_step (vllm_hymeta/attention/meta_attention.py:338-409).

@@ -39,6 +39,7 @@ SIGNATURES = {
     "hymeta_swa_decode_workspace_bytes": (_sz, [_i] * 8),
     "hymeta_swa_meta_decode_paged": (_i, [_p] * 9 + [_sz] + [_i] * 8 + [_i64, _i, _f] + [_i64] * 14 + [_p]),
     "hymeta_swa_decode_ticket_bytes": (_sz, [_i] * 3),
+    "hymeta_swa_meta_decode_paged_static": (_i, [_p] * 8 + [_i] * 8 + [_i64, _i, _f] + [_i64] * 14 + [_p]),
     "hymeta_swa_meta_decode_paged_fused": (_i, [_p] * 9 + [_sz] + [_i] * 8 + [_i64, _i, _f] + [_i64] * 14 +
                                            [_p, _p] + [_i64] * 4 + [_p, _p, _p]),
     "hymeta_swa_meta_prefill_varlen": (_i, [_p] * 10 + [_i64, _i] + [_i] * 9 + [_f] + [_i64] * 16 + [_p]),

@@ -584,3 +584,61 @@ extern "C" int hymeta_swa_meta_decode_paged(
       bt_stride, window_left, scale, q_sb, q_sh, o_sb, o_sh, kc_sblk, kc_stok, kc_sh, vc_sblk, vc_stok,
       vc_sh, mk_st, mk_sh, mv_st, mv_sh, nullptr, nullptr, 0, 0, 0, 0, nullptr, nullptr, stream);
 }
+
+// ---- no-allocation variant -----------------------------------------------------------------------
+// For callers that cannot provide (or allocate) the split-K scratch: it lives in this file-scope
+// device array -- HYMETA_SWA_DECODE_STATIC_WS_BYTES of fp32 partials followed by
+// HYMETA_SWA_DECODE_STATIC_TICKET_BYTES of tickets -- which every GPU that loads the library holds
+// until exit.  In host code the array's name is only a handle: its device address is looked up once
+// per device (with that device current) through cudaGetSymbolAddress and passed on like a
+// caller-owned workspace.
+static __device__ __align__(256) unsigned char
+    g_swa_decode_static_scratch[HYMETA_SWA_DECODE_STATIC_WS_BYTES + HYMETA_SWA_DECODE_STATIC_TICKET_BYTES];
+
+static int swa_decode_static_scratch(unsigned char** out) {
+  static std::atomic<unsigned char*> cache[64] = {};
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) { g_last_cuda_error = (int)e; return HYMETA_ERR_CUDA; }
+  if (dev < 0 || dev >= 64) return HYMETA_ERR_UNSUPPORTED;
+  unsigned char* ptr = cache[dev].load(std::memory_order_acquire);
+  if (!ptr) {
+    e = cudaGetSymbolAddress((void**)&ptr, g_swa_decode_static_scratch);
+    if (e != cudaSuccess || !ptr) { g_last_cuda_error = (int)e; return HYMETA_ERR_CUDA; }
+    cache[dev].store(ptr, std::memory_order_release);
+  }
+  *out = ptr;
+  return HYMETA_OK;
+}
+
+extern "C" int hymeta_swa_meta_decode_paged_static(
+    const void* q, const void* k_cache, const void* v_cache, const int32_t* block_tables,
+    const int32_t* cache_seqlens, const void* meta_k, const void* meta_v, void* out,
+    int B, int H, int Hkv, int D, int M, int block_size, int num_blocks,
+    int max_blocks, int64_t bt_stride, int window_left, float scale, int64_t q_sb, int64_t q_sh,
+    int64_t o_sb, int64_t o_sh, int64_t kc_sblk, int64_t kc_stok, int64_t kc_sh, int64_t vc_sblk,
+    int64_t vc_stok, int64_t vc_sh, int64_t mk_st, int64_t mk_sh, int64_t mv_st, int64_t mv_sh,
+    void* stream) {
+  if (B == 0) return HYMETA_OK;
+  if (B < 0 || H <= 0 || Hkv <= 0 || block_size <= 0 || max_blocks < 0 || M < 0) return HYMETA_ERR_INVALID_ARG;
+  if (D != kD || H % Hkv) return HYMETA_ERR_UNSUPPORTED;
+  // the same plan as the caller-workspace entry points; sizes beyond the static array are rejected
+  const size_t ws_bytes = plan_swa_decode(B, H, Hkv, max_blocks, block_size, window_left, M).bytes;
+  const size_t ticket_bytes = hymeta_swa_decode_ticket_bytes(B, H, Hkv);
+  if (ws_bytes > HYMETA_SWA_DECODE_STATIC_WS_BYTES || ticket_bytes > HYMETA_SWA_DECODE_STATIC_TICKET_BYTES)
+    return HYMETA_ERR_WORKSPACE;
+  unsigned char* scratch = nullptr;
+  int rc = swa_decode_static_scratch(&scratch);
+  if (rc) return rc;
+  int32_t* tickets = reinterpret_cast<int32_t*>(scratch + HYMETA_SWA_DECODE_STATIC_WS_BYTES);
+  // The array keeps the previous call's contents.  The partials are fully rewritten before they are
+  // read; the tickets must start at zero (the kernel returns them to zero, but a call that was
+  // aborted must not poison the next one), so they are cleared in stream order.
+  cudaError_t e = cudaMemsetAsync(tickets, 0, ticket_bytes, (cudaStream_t)stream);
+  if (e != cudaSuccess) { g_last_cuda_error = (int)e; return HYMETA_ERR_CUDA; }
+  return hymeta_swa_meta_decode_paged_fused(
+      q, const_cast<void*>(k_cache), const_cast<void*>(v_cache), block_tables, cache_seqlens, meta_k,
+      meta_v, out, scratch, HYMETA_SWA_DECODE_STATIC_WS_BYTES, B, H, Hkv, D, M, block_size, num_blocks,
+      max_blocks, bt_stride, window_left, scale, q_sb, q_sh, o_sb, o_sh, kc_sblk, kc_stok, kc_sh, vc_sblk,
+      vc_stok, vc_sh, mk_st, mk_sh, mv_st, mv_sh, nullptr, nullptr, 0, 0, 0, 0, nullptr, tickets, stream);
+}
