@@ -34,8 +34,9 @@
 extern "C" {
 #endif
 
-#define HYMETA_ABI_VERSION 5   /* 3: + rope_kv_write, *_gnorm, branch_*, slot_mgr_*; 4: paged-key prefill,
-                                  new_slot_mapping in the fused decode; 5: 7B gate folded into the GLA kernels (f2) */
+#define HYMETA_ABI_VERSION 6   /* 3: + rope_kv_write, *_gnorm, branch_*, slot_mgr_*; 4: paged-key prefill,
+                                  new_slot_mapping in the fused decode; 5: 7B gate folded into the GLA kernels (f2);
+                                  6: balanced single-pass GLA prefill (HYMETA_GLA_SEG_BALANCED), static-scratch decode */
 
 typedef enum {
   HYMETA_OK = 0,
@@ -111,6 +112,19 @@ int hymeta_gla_prefill_varlen(const void* q, const void* k, const void* v, const
  * hymeta_gla_prefill_workspace_bytes(N, Hs, max_seqlen, seg_len) bytes (16-byte aligned).
  * k/g/v strides must be multiples of 8 elements (TMA). */
 size_t hymeta_gla_prefill_workspace_bytes(int N, int Hs, int max_seqlen, int seg_len);
+
+/* Balanced single-pass form for MORE chains than SMs (N * Hs > SM count; BASELINE config 2: 256 chains
+ * on 148 SMs): pass seg_len = HYMETA_GLA_SEG_BALANCED to the _seg / _seg_gnorm / _fused entry points
+ * with a workspace of hymeta_gla_prefill_balanced_workspace_bytes(N, Hs) bytes (16-byte aligned).  A
+ * one-CTA plan kernel lays the chains end to end in 16-token steps and cuts the line into one equal
+ * range per SM; a chain that straddles a cut hands its fp32 state (and the decay it still owes) from
+ * one CTA to the next through the workspace (release / acquire flag), so every SM walks the same
+ * number of steps instead of whole chains in waves.  Each token is still read once and the state
+ * recurrence is evaluated in the same order with the same roundings: results are bit-identical to
+ * the single-pass form.  When a chain is longer than an SM's share (nothing to balance) or there
+ * are no more chains than SMs, the plan says so and the launch runs one chain per CTA. */
+#define HYMETA_GLA_SEG_BALANCED (-1)
+size_t hymeta_gla_prefill_balanced_workspace_bytes(int N, int Hs);
 int hymeta_gla_prefill_varlen_seg(const void* q, const void* k, const void* v, const void* g,
                                   void* o, void* state, const void* meta_state,
                                   const int32_t* cu_seqlens, const int32_t* slot_idx,

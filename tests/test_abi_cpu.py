@@ -30,7 +30,7 @@ def test_header_symbols_exported(built):
 
 def test_version_and_status_strings(built):
     h = built.lib()
-    assert h.hymeta_abi_version() == 5
+    assert h.hymeta_abi_version() == 6
     assert h.hymeta_status_string(0) == b"ok"
     for code in (-1, -2, -3, -4, -5):
         assert h.hymeta_status_string(code) not in (b"ok", b"unknown status")

@@ -134,3 +134,61 @@ def test_seg_len_heuristic():
     assert o.gla_prefill_seg_len(4, 300) == 0               # too short to cut
     s = o.gla_prefill_seg_len(1, 32768)
     assert s > 0 and s % 16 == 0 and 32768 // s >= 64
+
+
+# ------------------------------------------------------------------- balanced single-pass form
+def _balanced_vs_single(ops, lens, H, Hkv, Hs, model, seed, with_sumsq=False):
+    """seg_len = GLA_SEG_BALANCED must reproduce the single-pass launch bit for bit: the chains are
+    only re-distributed over the SMs, a cut hands the fp32 state (and its pending decay) over."""
+    D, T, N = 128, sum(lens), len(lens)
+    q, k, v, g = ogla.synth_gla_inputs(T, H, Hkv, D, model, seed=seed)
+    if Hs != Hkv:
+        k, v, g = (x.repeat_interleave(Hs // Hkv, 1).contiguous() for x in (k, v, g))
+    gen = torch.Generator().manual_seed(seed + 5)
+    nslots = N + 2
+    state = (torch.randn(nslots, Hs, D, D, generator=gen) * 0.2).bfloat16()
+    meta = (torch.randn(Hs, D, D, generator=gen) * 0.2).bfloat16().to(DEV)
+    slots = torch.randperm(nslots, generator=gen)[:N].tolist()
+    slots[3] = -1                                            # a PAD request
+    modes = [i % 3 for i in range(N)]
+    cu = [0]
+    for L in lens:
+        cu.append(cu[-1] + L)
+    i32 = lambda x: torch.tensor(x, dtype=torch.int32, device=DEV)
+    dq, dk, dv, dg = (x.to(DEV) for x in (q, k, v, g))
+    res = []
+    for seg_len in (0, ops.GLA_SEG_BALANCED):
+        st = state.to(DEV)
+        ss = torch.full((T, H), -1.0, device=DEV) if with_sumsq else None
+        o = torch.full((T, H, D), float("nan"), device=DEV, dtype=torch.bfloat16)
+        ops.gla_prefill_varlen(dq, dk, dv, dg, st, i32(cu), i32(slots), i32(modes), meta,
+                               max_seqlen=max(lens), seg_len=seg_len, out=o, sumsq_out=ss)
+        torch.cuda.synchronize()
+        res.append((o, st, ss))
+    (o0, s0, q0), (o1, s1, q1) = res
+    assert torch.isfinite(o0.float()).all()
+    assert torch.equal(o1, o0), f"outputs differ: {(o1.float() - o0.float()).abs().max().item()}"
+    assert torch.equal(s1, s0), "final states differ"
+    if with_sumsq:
+        assert torch.equal(q1, q0)
+    return o0
+
+
+def test_balanced_equals_single_pass_more_chains_than_sms(ops):
+    gen = torch.Generator().manual_seed(3)
+    # 90 requests x 4 state heads = 360 chains on 148 SMs; ragged tails, a 1-token and two empty requests
+    lens = torch.randint(48, 330, (90,), generator=gen).tolist()
+    lens[0], lens[7], lens[20], lens[89] = 1, 0, 16, 0
+    _balanced_vs_single(ops, lens, 28, 4, 4, "7b", 21, with_sumsq=True)
+    _balanced_vs_single(ops, lens, 28, 4, 4, "70b", 22)
+
+
+def test_balanced_one_state_per_q_head(ops):
+    lens = [130, 64, 257, 300, 90, 111, 200, 31]              # x 28 heads = 224 chains, G = 1
+    _balanced_vs_single(ops, lens, 28, 4, 28, "70b", 23)
+
+
+def test_balanced_falls_back_when_a_chain_exceeds_an_sm_share(ops):
+    lens = [40] * 60 + [4000]                                 # 244 chains, one far longer than total / 148
+    _balanced_vs_single(ops, lens, 28, 4, 4, "7b", 24)
+    _balanced_vs_single(ops, [100, 50, 60, 70], 28, 4, 4, "7b", 25)   # fewer chains than SMs: plain grid

@@ -24,6 +24,7 @@ SIGNATURES = {
     "hymeta_gla_decode": (_i, [_p] * 7 + [_i] * 6 + [_i64] * 12 + [_i, _f, _p]),
     "hymeta_gla_prefill_varlen": (_i, [_p] * 10 + [_i] * 7 + [_i64] * 13 + [_i, _f, _i, _i, _p]),
     "hymeta_gla_prefill_workspace_bytes": (_sz, [_i] * 4),
+    "hymeta_gla_prefill_balanced_workspace_bytes": (_sz, [_i] * 2),
     "hymeta_gla_prefill_varlen_seg": (_i, [_p] * 10 + [_i] * 7 + [_i64] * 13 + [_i, _f, _i, _i, _i, _p, _sz, _p]),
     "hymeta_gla_decode_gnorm": (_i, [_p] * 7 + [_i] * 6 + [_i64] * 12 + [_i, _f, _p, _f, _p]),
     "hymeta_gla_prefill_varlen_seg_gnorm": (_i, [_p] * 10 + [_i] * 7 + [_i64] * 13 +
@@ -83,7 +84,7 @@ def lib() -> C.CDLL:
         for name, (res, args) in SIGNATURES.items():
             fn = getattr(h, name)      # AttributeError if the library lacks a declared symbol
             fn.restype, fn.argtypes = res, args
-        if h.hymeta_abi_version() != 5:
+        if h.hymeta_abi_version() != 6:
             raise ImportError("hymeta_b200 ABI version mismatch")
         _lib = h
     return _lib

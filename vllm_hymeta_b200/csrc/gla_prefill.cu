@@ -58,6 +58,17 @@ constexpr int GP_SMEM = GP_GW + 256;
 constexpr int GP_THREADS = 512;
 constexpr int GP_WS_ELEMS = kD * kD + kD;      // per (chain, segment): state [128][128] + decay [128]
 
+// One unit of a CTA's work: a run of whole steps of one (sequence, state-head) chain.  A launch over
+// the (Hs, N, segments) grid gives every CTA the one piece its block index names; the balanced
+// single-pass form (gla_prefill_plan_kernel below) gives each CTA a list.
+struct __align__(16) GlaPiece {
+  int32_t tok_begin, len;   // first token row and token count
+  int32_t hs, in_kind;      // state head; start state: 0 zero, 1 slot in_idx, 2 meta state, 3 fp32 buffer in_idx
+  int32_t in_idx, out_kind; // end state: 0 dropped, 1 slot out_idx (bf16), 2 fp32 buffer out_idx
+  int32_t out_idx, pad;
+};
+constexpr int GP_PLAN_HDR = 4;                  // plan header ints: {cut mode, ctas, ticket, steps per CTA}
+
 struct GlaPrefillParams {
   const __nv_bfloat16 *q, *k, *v;
   const void* g;
@@ -75,6 +86,12 @@ struct GlaPrefillParams {
                                   // projection outputs), 0xff80ff80 (-inf) = identity
   float* sumsq;                   // f1: null, or [T, H] fp32 -- sum of squares of each bf16 output row (the branch
                                   // merge's RMS-norm partials), emitted by the O epilogue
+  // balanced single-pass form (all null otherwise): plan header, per-CTA piece ranges and step
+  // totals, piece table, hand-off flags of the fp32 buffers in ws (one per cut)
+  int32_t* plan;
+  const int32_t *cta_off, *cta_steps;
+  const GlaPiece* pieces;
+  int32_t* flags;
   const uint16_t* gate_table;     // null, or [65536] bf16: g = table[raw bf16 gate bits] -- the 7B gate
                                   // bf16(bf16(logsigmoid(gk)) / normalizer) is a pure function of a 16-bit
                                   // input, tabulated once per normalizer by hymeta_gla_gate_7b_g itself
@@ -113,42 +130,76 @@ gla_prefill_kernel(const GlaPrefillParams p, const __grid_constant__ CUtensorMap
   extern __shared__ __align__(1024) uint8_t smem[];
   const int tid = threadIdx.x, lane = tid & 31;
   const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);   // warp-uniform for the compiler
-  const int hs = blockIdx.x, n = blockIdx.y;
-  const int G = p.H / p.Hs, h0 = hs * G, hk = hs / (p.Hs / p.Hk), hv = hs / (p.Hs / p.Hv);
-  const int seq_begin = p.cu[n], seq_len = p.cu[n + 1] - seq_begin;
-  const int slot = p.slot[n], mode = p.init_mode[n];
-  // segment [seg0, seg0 + len) of the sequence (the whole sequence when seg_len == 0)
-  const int seg = blockIdx.z, seg0 = seg * p.seg_len;
+  const int G = p.H / p.Hs;
   const bool summary = p.pass == 1;
-  if (seg > 0 && seg0 >= seq_len) return;
-  const bool last_seg = p.seg_len == 0 || seg0 + p.seg_len >= seq_len;
-  if (summary && last_seg) return;               // nothing follows: no summary needed
-  const int tok_begin = seq_begin + seg0, len = last_seg ? seq_len - seg0 : p.seg_len;
-  const int n_steps = (len + GC - 1) / GC;
-  float* ws_out = summary ? p.ws + ((int64_t)(n * p.Hs + hs) * p.n_segs + seg) * GP_WS_ELEMS : nullptr;
-  const float* ws_in = (p.pass == 3 && seg > 0)
-      ? p.ws + ((int64_t)(n * p.Hs + hs) * p.n_segs + seg - 1) * GP_WS_ELEMS : nullptr;
-
-  const __nv_bfloat16* init_src = nullptr;
-  if (!summary && seg == 0) {
-    if (mode == 1 && slot >= 0) init_src = p.state + (int64_t)slot * p.st_ss + (int64_t)hs * p.st_sh;
-    else if (mode == 2 && p.meta_state) init_src = p.meta_state + (int64_t)hs * p.meta_sh;
-  }
-  __nv_bfloat16* final_dst = (!summary && last_seg && p.write_state && slot >= 0)
-      ? p.state + (int64_t)slot * p.st_ss + (int64_t)hs * p.st_sh : nullptr;
-
-  if (n_steps == 0) {   // empty sequence: the slot receives the initial state unchanged
-    if (final_dst && final_dst != init_src && warp >= 4 && warp < 8) {
-      const int d = tid - 128;
-#pragma unroll
-      for (int c = 0; c < 16; ++c) {
-        uint4 t = make_uint4(0, 0, 0, 0);
-        if (init_src) t = ldg_v4(init_src + d * kD + 8 * c);
-        stg_v4(final_dst + d * kD + 8 * c, t);
-      }
+  // ---- this CTA's work list -------------------------------------------------------------------
+  GlaPiece own;                    // the block index's piece (grid launches) / first piece of the list
+  own.pad = 0;
+  int pi0 = 0, n_pieces = 1, cta_steps = 0;
+  const bool table = p.plan != nullptr && p.plan[0] != 0;
+  if (table) {
+    // logical CTA index = arrival order, so the CTA a hand-off waits for has always started
+    int* slot_l = reinterpret_cast<int*>(smem + GP_BAR + 208);
+    if (tid == 0) *slot_l = atomicAdd(p.plan + 2, 1);
+    __syncthreads();
+    const int logical = *slot_l;
+    if (logical >= p.plan[1]) return;
+    pi0 = p.cta_off[logical];
+    n_pieces = p.cta_off[logical + 1] - pi0;
+    cta_steps = p.cta_steps[logical];
+    if (n_pieces == 0) return;
+    own = p.pieces[pi0];
+  } else {
+    const int hs = blockIdx.x, n = blockIdx.y;
+    const int seq_begin = p.cu[n], seq_len = p.cu[n + 1] - seq_begin;
+    const int slot = p.slot[n], mode = p.init_mode[n];
+    // segment [seg0, seg0 + len) of the sequence (the whole sequence when seg_len == 0)
+    const int seg = blockIdx.z, seg0 = seg * p.seg_len;
+    if (seg > 0 && seg0 >= seq_len) return;
+    const bool last_seg = p.seg_len == 0 || seg0 + p.seg_len >= seq_len;
+    if (summary && last_seg) return;               // nothing follows: no summary needed
+    const int ws_idx = (n * p.Hs + hs) * p.n_segs + seg;
+    own.tok_begin = seq_begin + seg0;
+    own.len = last_seg ? seq_len - seg0 : p.seg_len;
+    own.hs = hs;
+    own.in_kind = 0; own.in_idx = 0;
+    if (p.pass == 3 && seg > 0) { own.in_kind = 3; own.in_idx = ws_idx - 1; }
+    else if (!summary && seg == 0) {
+      if (mode == 1 && slot >= 0) { own.in_kind = 1; own.in_idx = slot; }
+      else if (mode == 2 && p.meta_state) own.in_kind = 2;
     }
-    return;
+    own.out_kind = 0; own.out_idx = 0;
+    if (summary) { own.out_kind = 2; own.out_idx = ws_idx; }
+    else if (last_seg && p.write_state && slot >= 0) { own.out_kind = 1; own.out_idx = slot; }
+    cta_steps = (own.len + GC - 1) / GC;
+    if (cta_steps == 0) {   // empty sequence: the slot receives the initial state unchanged
+      if (own.out_kind == 1 && warp >= 4 && warp < 8) {
+        const __nv_bfloat16* init_src = nullptr;
+        if (own.in_kind == 1) init_src = p.state + (int64_t)slot * p.st_ss + (int64_t)hs * p.st_sh;
+        else if (own.in_kind == 2) init_src = p.meta_state + (int64_t)hs * p.meta_sh;
+        __nv_bfloat16* final_dst = p.state + (int64_t)slot * p.st_ss + (int64_t)hs * p.st_sh;
+        if (final_dst != init_src) {
+          const int d = tid - 128;
+#pragma unroll
+          for (int c = 0; c < 16; ++c) {
+            uint4 t = make_uint4(0, 0, 0, 0);
+            if (init_src) t = ldg_v4(init_src + d * kD + 8 * c);
+            stg_v4(final_dst + d * kD + 8 * c, t);
+          }
+        }
+      }
+      return;
+    }
   }
+  auto piece = [&](int k) -> GlaPiece {
+    if (!table || k == 0) return own;
+    const int4* src = reinterpret_cast<const int4*>(p.pieces + pi0 + k);
+    const int4 a = __ldg(src), b = __ldg(src + 1);
+    GlaPiece r;
+    r.tok_begin = a.x; r.len = a.y; r.hs = a.z; r.in_kind = a.w;
+    r.in_idx = b.x; r.out_kind = b.y; r.out_idx = b.z; r.pad = 0;
+    return r;
+  };
 
   const uint32_t sbase = smem_u32(smem);
   const uint32_t sQ = sbase + GP_SQ, sS = sbase + GP_SS, sT = sbase + GP_ST;
@@ -194,19 +245,35 @@ gla_prefill_kernel(const GlaPrefillParams p, const __grid_constant__ CUtensorMap
     constexpr uint32_t RAW_BYTES = GC * kD * (GB + 2);
     const uint8_t* rawp = smem + GP_RAW + c * GB;
     const uint8_t* rawkp = smem + GP_RAW + GP_RAW_K + c * 2;
-    auto fetch = [&](int i) {
-      if (i < n_steps && tid == 0) {
-        const uint32_t bar = bar_raw + 8 * (i % GP_RS), dst = sbase + GP_RAW + (i % GP_RS) * GP_RAW_STAGE;
-        mbar_expect_tx(bar, RAW_BYTES);
-        tma_load_3d(dst, &tmG, bar, 0, hk, tok_begin + i * GC);
-        tma_load_3d(dst + GP_RAW_K, &tmK, bar, 0, hk, tok_begin + i * GC);
+    // the raw ring runs GP_RS steps ahead of the stage being built, across piece boundaries: thread 0
+    // walks the work list a second time with its own cursor
+    int f_pi = 0, f_i = 0, f_g = 0, f_steps = (own.len + GC - 1) / GC, f_tok = own.tok_begin,
+        f_hk = own.hs / (p.Hs / p.Hk);
+    auto fetch = [&]() {
+      if (tid != 0) return;
+      while (f_pi < n_pieces && f_i >= f_steps) {
+        if (++f_pi >= n_pieces) break;
+        const GlaPiece pc = piece(f_pi);
+        f_i = 0; f_steps = (pc.len + GC - 1) / GC; f_tok = pc.tok_begin; f_hk = pc.hs / (p.Hs / p.Hk);
       }
+      if (f_pi >= n_pieces) return;
+      const uint32_t bar = bar_raw + 8 * (f_g % GP_RS), dst = sbase + GP_RAW + (f_g % GP_RS) * GP_RAW_STAGE;
+      mbar_expect_tx(bar, RAW_BYTES);
+      tma_load_3d(dst, &tmG, bar, 0, f_hk, f_tok + f_i * GC);
+      tma_load_3d(dst + GP_RAW_K, &tmK, bar, 0, f_hk, f_tok + f_i * GC);
+      ++f_i; ++f_g;
     };
     if (tid == 0) { tma_prefetch_desc(&tmG); tma_prefetch_desc(&tmK); tma_prefetch_desc(&tmV); }
 #pragma unroll
-    for (int i = 0; i < GP_RS; ++i) fetch(i);
-    for (int i = 0; i < n_steps; ++i) {
-      const int st = i % GP_KS, clen = len - i * GC;
+    for (int i = 0; i < GP_RS; ++i) fetch();
+    int gbase = 0;
+    for (int pi = 0; pi < n_pieces; ++pi) {
+     const GlaPiece pc = piece(pi);
+     const int n_steps = (pc.len + GC - 1) / GC, len = pc.len, tok_begin = pc.tok_begin;
+     const int hv = pc.hs / (p.Hs / p.Hv);
+     for (int li = 0; li < n_steps; ++li) {
+      const int i = gbase + li;                     // step index of the CTA: ring slots and phases
+      const int st = i % GP_KS, clen = len - li * GC;
       const uint32_t so = (uint32_t)((i % GP_RS) * GP_RAW_STAGE);
       uint8_t* stage = smem + GP_ST + st * GP_STAGE;
       if (tid == 0) GP_TRACE(i, 15);
@@ -258,15 +325,15 @@ gla_prefill_kernel(const GlaPrefillParams p, const __grid_constant__ CUtensorMap
         if (tid == 0) {
           const uint32_t dst = sT + st * GP_STAGE + GP_ST_V;
           mbar_expect_tx_only(bar_kf + 8 * st, GC * kD * 2);
-          tma_load_3d(dst, &tmV, bar_kf + 8 * st, 0, hv, tok_begin + i * GC);
-          tma_load_3d(dst + 2048, &tmV, bar_kf + 8 * st, 64, hv, tok_begin + i * GC);
+          tma_load_3d(dst, &tmV, bar_kf + 8 * st, 0, hv, tok_begin + li * GC);
+          tma_load_3d(dst + 2048, &tmV, bar_kf + 8 * st, 64, hv, tok_begin + li * GC);
         }
       } else {   // ragged last step: copy by hand, zero rows past the sequence end
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
           const int id = tid + 64 * j, t = id >> 4, vc = id & 15;
           uint4 x = make_uint4(0, 0, 0, 0);
-          if (t < clen) x = ldg_nc_v4(p.v + (int64_t)(tok_begin + i * GC + t) * p.v_st + (int64_t)hv * p.v_sh + vc * 8);
+          if (t < clen) x = ldg_nc_v4(p.v + (int64_t)(tok_begin + li * GC + t) * p.v_st + (int64_t)hv * p.v_sh + vc * 8);
           *reinterpret_cast<uint4*>(stage + GP_ST_V + (vc >> 3) * 2048 + sw128_chunk(t, vc & 7)) = x;
         }
       }
@@ -293,14 +360,17 @@ gla_prefill_kernel(const GlaPrefillParams p, const __grid_constant__ CUtensorMap
       // barrier right after the loads is NOT enough -- the compiler schedules their first use
       // behind it, and under LSU pressure the last rows were read after the refill).
       asm volatile("bar.sync 1, 64;" ::: "memory");   // both gate warps are done with the raw slot
-      fetch(i + GP_RS);
+      fetch();
       if (tid == 0) GP_TRACE(i, 0);
+     }
+     gbase += n_steps;
     }
    } else if (warp == 3) {
     // idle: g / k / v arrive by TMA
    } else {
     // ================================================================== MMA issuer
-    if (!summary && elect_one_sync()) {
+    if (!summary && cta_steps > 0 && elect_one_sync()) {
+      const int n_steps = cta_steps;                 // the issuer sees one stream of steps
       const uint32_t idesc_a = umma_idesc_bf16(128, 16, 0, 0);
       const uint32_t idesc_o = umma_idesc_bf16(128, 128, 0, 1);
       // descriptors differ from these templates only in the 16-byte-granular start address
@@ -371,23 +441,8 @@ gla_prefill_kernel(const GlaPrefillParams p, const __grid_constant__ CUtensorMap
     const int ws = warp - 4, gid = lane >> 2, tig = lane & 3;
     const int row0 = 32 * ws + gid;                 // rows row0 + 8j, j = 0..3 (m-tile j>>1, half j&1)
     float S[2][16][4];
-    float Ptot[4] = {1.f, 1.f, 1.f, 1.f};            // total decay of the segment (summary pass)
-#pragma unroll
-    for (int mt = 0; mt < 2; ++mt)
-#pragma unroll
-      for (int nt = 0; nt < 16; ++nt)
-#pragma unroll
-        for (int hf = 0; hf < 2; ++hf) {
-          const int off = (row0 + 16 * mt + 8 * hf) * kD + 8 * nt + 2 * tig;
-          if (ws_in) {
-            const float2 f = *reinterpret_cast<const float2*>(ws_in + off);
-            S[mt][nt][2 * hf] = f.x; S[mt][nt][2 * hf + 1] = f.y;
-          } else {
-            uint32_t u = 0;
-            if (init_src) u = *reinterpret_cast<const uint32_t*>(init_src + off);
-            S[mt][nt][2 * hf] = bf16_lo(u); S[mt][nt][2 * hf + 1] = bf16_hi(u);
-          }
-        }
+    float Ptot[4];                                   // total decay of the segment (summary pass)
+    float Din[4];                                    // decay still owed by a state handed over at a cut
     // ldmatrix row addresses inside a stage (k~ / v tiles: [2 halves][16 tokens][64] SWIZZLE_128B)
     const int lt = (lane & 7) + 8 * ((lane >> 4) & 1);          // A: token row, d_k block (lane>>3)&1
     const uint32_t a_row = (uint32_t)(lt * 128), a_x = (uint32_t)(lt & 7);
@@ -395,8 +450,58 @@ gla_prefill_kernel(const GlaPrefillParams p, const __grid_constant__ CUtensorMap
     const int bt = (lane & 7) + 8 * ((lane >> 3) & 1);          // B: token row, d_v block pair lane>>4
     const uint32_t b_row = (uint32_t)(bt * 128), b_x = (uint32_t)(bt & 7);
     const float* sD0 = reinterpret_cast<const float*>(smem + GP_ST + GP_ST_D);
-    for (int i = -1; i < n_steps; ++i) {
-      const bool first = i < 0, last = i + 1 == n_steps;
+    int gbase = 0;
+    for (int pi = 0; pi < n_pieces; ++pi) {
+     const GlaPiece pc = piece(pi);
+     const int n_steps = (pc.len + GC - 1) / GC;
+     // ---- start state of the piece
+     {
+      const __nv_bfloat16* init_src = nullptr;
+      const float* ws_in = nullptr;
+      if (pc.in_kind == 1) init_src = p.state + (int64_t)pc.in_idx * p.st_ss + (int64_t)pc.hs * p.st_sh;
+      else if (pc.in_kind == 2) init_src = p.meta_state + (int64_t)pc.hs * p.meta_sh;
+      else if (pc.in_kind == 3) {
+        ws_in = p.ws + (int64_t)pc.in_idx * GP_WS_ELEMS;
+        if (p.flags) {   // handed over by the CTA that owns the head of this chain (it runs it first)
+          if (tid == 128) {
+            int v;
+            do {
+              asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p.flags + pc.in_idx) : "memory");
+            } while (v == 0);
+          }
+          asm volatile("bar.sync 2, 128;" ::: "memory");
+        }
+      }
+#pragma unroll
+      for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+        for (int nt = 0; nt < 16; ++nt)
+#pragma unroll
+          for (int hf = 0; hf < 2; ++hf) {
+            const int off = (row0 + 16 * mt + 8 * hf) * kD + 8 * nt + 2 * tig;
+            if (ws_in) {
+              const float2 f = __ldcg(reinterpret_cast<const float2*>(ws_in + off));
+              S[mt][nt][2 * hf] = f.x; S[mt][nt][2 * hf + 1] = f.y;
+            } else {
+              uint32_t u = 0;
+              if (init_src) u = *reinterpret_cast<const uint32_t*>(init_src + off);
+              S[mt][nt][2 * hf] = bf16_lo(u); S[mt][nt][2 * hf + 1] = bf16_hi(u);
+            }
+          }
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        Ptot[j] = 1.f;
+        // at a cut the state travels WITHOUT its last step's decay, which is folded into the first
+        // rescale here exactly as the uncut chain folds it: S * (d_i * e_{i+1}), bit for bit
+        Din[j] = (ws_in && p.flags) ? __ldcg(ws_in + kD * kD + row0 + 8 * j) : 1.f;
+      }
+     }
+     __nv_bfloat16* final_dst = pc.out_kind == 1
+         ? p.state + (int64_t)pc.out_idx * p.st_ss + (int64_t)pc.hs * p.st_sh : nullptr;
+     float* ws_out = pc.out_kind == 2 ? p.ws + (int64_t)pc.out_idx * GP_WS_ELEMS : nullptr;
+     for (int li = -1; li < n_steps; ++li) {
+      const int i = gbase + li;                     // step index of the CTA (ring slots and phases)
+      const bool first = li < 0, last = li + 1 == n_steps;
       if (!first && !(GP_EXP & 16)) {
         const uint32_t stg = sT + (i % GP_KS) * GP_STAGE;      // kf(i) was awaited in pass i-1
         uint32_t af[2][4];
@@ -421,7 +526,7 @@ gla_prefill_kernel(const GlaPrefillParams p, const __grid_constant__ CUtensorMap
       }
       float D[4];
 #pragma unroll
-      for (int j = 0; j < 4; ++j) D[j] = first ? 1.f : sD0[(i % GP_KS) * (GP_STAGE / 4) + row0 + 8 * j];
+      for (int j = 0; j < 4; ++j) D[j] = first ? Din[j] : sD0[(i % GP_KS) * (GP_STAGE / 4) + row0 + 8 * j];
       if (!last) {
         const int sn = (i + 1) % GP_KS;
         mbar_wait(bar_kf + 8 * sn, ((i + 1) / GP_KS) & 1);
@@ -429,31 +534,51 @@ gla_prefill_kernel(const GlaPrefillParams p, const __grid_constant__ CUtensorMap
         for (int j = 0; j < 4; ++j) D[j] *= sD0[sn * (GP_STAGE / 4) + kD + row0 + 8 * j];
       }
       if (!first) mbar_arrive(bar_ke + 8 * (i % GP_KS));        // k~, v, D of step i consumed
+      const bool handoff = last && ws_out && p.flags;           // cut: the decay travels beside the state
+      if (!handoff) {
 #pragma unroll
-      for (int mt = 0; mt < 2; ++mt)
+        for (int mt = 0; mt < 2; ++mt)
 #pragma unroll
-        for (int nt = 0; nt < 16; ++nt) {
-          S[mt][nt][0] *= D[2 * mt]; S[mt][nt][1] *= D[2 * mt];
-          S[mt][nt][2] *= D[2 * mt + 1]; S[mt][nt][3] *= D[2 * mt + 1];
-        }
+          for (int nt = 0; nt < 16; ++nt) {
+            S[mt][nt][0] *= D[2 * mt]; S[mt][nt][1] *= D[2 * mt];
+            S[mt][nt][2] *= D[2 * mt + 1]; S[mt][nt][3] *= D[2 * mt + 1];
+          }
+      }
 #pragma unroll
-      for (int j = 0; j < 4; ++j) Ptot[j] *= D[j];
-      if (summary) {
-        if (last) {   // local end state (zero start) and total decay of this segment
+      for (int j = 0; j < 4; ++j) Ptot[j] = handoff ? D[j] : Ptot[j] * D[j];
+      if (last) {
+        if (ws_out) {   // fp32 end state and decay: a segment summary, or the hand-off at a cut
 #pragma unroll
           for (int mt = 0; mt < 2; ++mt)
 #pragma unroll
             for (int nt = 0; nt < 16; ++nt)
 #pragma unroll
               for (int hf = 0; hf < 2; ++hf)
-                *reinterpret_cast<float2*>(ws_out + (row0 + 16 * mt + 8 * hf) * kD + 8 * nt + 2 * tig) =
-                    make_float2(S[mt][nt][2 * hf], S[mt][nt][2 * hf + 1]);
+                __stcg(reinterpret_cast<float2*>(ws_out + (row0 + 16 * mt + 8 * hf) * kD + 8 * nt + 2 * tig),
+                       make_float2(S[mt][nt][2 * hf], S[mt][nt][2 * hf + 1]));
           if (tig == 0) {
 #pragma unroll
-            for (int j = 0; j < 4; ++j) ws_out[kD * kD + row0 + 8 * j] = Ptot[j];
+            for (int j = 0; j < 4; ++j) __stcg(ws_out + kD * kD + row0 + 8 * j, Ptot[j]);
           }
+          if (p.flags) {
+            __threadfence();
+            asm volatile("bar.sync 2, 128;" ::: "memory");
+            if (tid == 128) {
+              const int one = 1;
+              asm volatile("st.release.gpu.global.s32 [%0], %1;" :: "l"(p.flags + pc.out_idx), "r"(one) : "memory");
+            }
+          }
+        } else if (final_dst) {
+#pragma unroll
+          for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+            for (int nt = 0; nt < 16; ++nt)
+#pragma unroll
+              for (int hf = 0; hf < 2; ++hf)
+                *reinterpret_cast<uint32_t*>(final_dst + (row0 + 16 * mt + 8 * hf) * kD + 8 * nt + 2 * tig) =
+                    pack_bf16(S[mt][nt][2 * hf], S[mt][nt][2 * hf + 1]);
         }
-      } else if (!last) {
+      } else if (!summary) {
         // X_{i+1} -> buffer (i+1)&1, last read by q~ X of step i-1
         if (i >= 1) mbar_wait(bar_xf + 8 * ((i + 1) & 1), ((i - 1) >> 1) & 1);
         // rows row0 + 8j all have (row & 7) == gid: eight slot bases, everything else is immediate
@@ -472,17 +597,10 @@ gla_prefill_kernel(const GlaPrefillParams p, const __grid_constant__ CUtensorMap
         }
         fence_proxy_async_smem();
         mbar_arrive(bar_x + 8 * ((i + 1) & 1));   // one barrier per buffer: the state may run a full buffer ahead
-        if (tid == 128 && i >= 0) GP_TRACE(i, 3);
-      } else if (final_dst) {
-#pragma unroll
-        for (int mt = 0; mt < 2; ++mt)
-#pragma unroll
-          for (int nt = 0; nt < 16; ++nt)
-#pragma unroll
-            for (int hf = 0; hf < 2; ++hf)
-              *reinterpret_cast<uint32_t*>(final_dst + (row0 + 16 * mt + 8 * hf) * kD + 8 * nt + 2 * tig) =
-                  pack_bf16(S[mt][nt][2 * hf], S[mt][nt][2 * hf + 1]);
+        if (tid == 128 && li >= 0) GP_TRACE(i, 3);
       }
+     }
+     gbase += n_steps;
     }
   } else {
     setmaxnreg_dec<112>();
@@ -496,12 +614,24 @@ gla_prefill_kernel(const GlaPrefillParams p, const __grid_constant__ CUtensorMap
     // q~ row (hh*16 + t) of 16-byte chunk qc: byte offsets of tokens qt0 / qt0+8 for head slot 0
     uint8_t* sQw = smem + GP_SQ + w * 32768 + (qc >> 3) * 16384;
     const uint32_t qo0 = (uint32_t)(qt0 * 128 + (((qc ^ qt0) & 7) << 4)), qo1 = qo0 + 1024;   // (qt0+8)&7 == qt0&7
-    const __nv_bfloat16* qp = p.q + (int64_t)(tok_begin + qt0) * p.q_st + (int64_t)h0 * p.q_sh + qc * 8;
-    const int q_steps = summary ? 0 : n_steps;      // the summary pass has no queries
+    const __nv_bfloat16* qp = p.q + (int64_t)qt0 * p.q_st + qc * 8;
+    const int q_steps = summary ? 0 : cta_steps;    // the summary pass has no queries
+    // cursor over the work list, positioned on the tile being prefetched (two steps ahead)
+    int n_pi = 0, n_base = 0, n_cnt = (own.len + GC - 1) / GC, n_tok = own.tok_begin, n_len = own.len,
+        n_h0 = own.hs * G;
+    auto seek = [&](int g) {
+      while (n_pi < n_pieces && g >= n_base + n_cnt) {
+        n_base += n_cnt;
+        if (++n_pi >= n_pieces) break;
+        const GlaPiece pc = piece(n_pi);
+        n_cnt = (pc.len + GC - 1) / GC; n_tok = pc.tok_begin; n_len = pc.len; n_h0 = pc.hs * G;
+      }
+    };
+    int clen = 0, tok0 = 0, h0 = 0;                 // step i: valid tokens, first token row, first q head
     uint4 qv[16];
     int cnt = 0;
     for (int i = w - 2; i < q_steps; i += 2) {
-      const int clen = len - i * GC;
+      int nx_clen = 0, nx_tok0 = 0, nx_h0 = 0;
       if (i >= 0) {
         const int st = i % GP_KS;
         // ---- build q~ from the registers prefetched one tile ahead (buffer w is free: this
@@ -533,8 +663,10 @@ gla_prefill_kernel(const GlaPrefillParams p, const __grid_constant__ CUtensorMap
         if (tq == 0) GP_TRACE(i, 5);
       }
       if (i + 2 < q_steps) {                        // next tile: in flight under the P conversion and epilogue
-        const int rem = len - (i + 2) * GC - qt0;   // token qt0 + 8e valid iff 8e < rem
-        const __nv_bfloat16* src = qp + (int64_t)(i + 2) * GC * p.q_st;
+        seek(i + 2);
+        nx_clen = n_len - (i + 2 - n_base) * GC; nx_tok0 = n_tok + (i + 2 - n_base) * GC; nx_h0 = n_h0;
+        const int rem = nx_clen - qt0;              // token qt0 + 8e valid iff 8e < rem
+        const __nv_bfloat16* src = qp + (int64_t)nx_tok0 * p.q_st + (int64_t)nx_h0 * p.q_sh;
 #pragma unroll
         for (int it = 0; it < 16; ++it) {
           qv[it] = make_uint4(0, 0, 0, 0);
@@ -638,16 +770,17 @@ gla_prefill_kernel(const GlaPrefillParams p, const __grid_constant__ CUtensorMap
                 const int rq = (warp & 3) * 32 + row, hh2 = rq >> 4, t2 = rq & 15;
                 const uint4 o4 = *reinterpret_cast<const uint4*>(stg + row * 64 + (((c ^ (row >> 1)) & 3) << 4));
                 if (hh2 < G && t2 < clen)
-                  stg_v4(p.o + (int64_t)(tok_begin + i * GC + t2) * p.o_st + (int64_t)(h0 + hh2) * p.o_sh + 32 * cc + 8 * c, o4);
+                  stg_v4(p.o + (int64_t)(tok0 + t2) * p.o_st + (int64_t)(h0 + hh2) * p.o_sh + 32 * cc + 8 * c, o4);
               }
             }
             __syncwarp();
           }
           if (p.sumsq && (tq >> 4) < G && r_t < clen)
-            p.sumsq[(int64_t)(tok_begin + i * GC + r_t) * p.H + h0 + (tq >> 4)] = ssq;
+            p.sumsq[(int64_t)(tok0 + r_t) * p.H + h0 + (tq >> 4)] = ssq;
         }
         ++cnt;
       }
+      clen = nx_clen; tok0 = nx_tok0; h0 = nx_h0;
     }
   }
   tc_fence_before();
@@ -684,6 +817,102 @@ __global__ void __launch_bounds__(256) gla_prefill_scan_kernel(const GlaPrefillP
   }
 }
 
+// Work plan of the balanced single-pass form (one CTA, every launch).  The (sequence, state-head)
+// chains are laid end to end on a line of 16-token steps and the line is cut into `ncta` equal
+// ranges, one per SM, so chains > SMs no longer run as whole waves (256 chains on 148 SMs: 1024 ->
+// 886 steps per SM).  A chain that straddles a cut becomes two pieces: its head A in CTA j, its tail
+// B in CTA j+1, the fp32 state handed over through buffer j of the workspace.  Every CTA walks its
+// range BACKWARDS -- A first, whole chains, B last: A has no dependency, and B starts no earlier than
+// (range - |B|) >= |A| steps into its CTA, when A is long done.  That needs range >= longest chain;
+// otherwise (a few very long chains among short ones) the plan says so and the launch runs one
+// chain per CTA in block-index order.
+__global__ void __launch_bounds__(1024) gla_prefill_plan_kernel(
+    const GlaPrefillParams p, int ncta, int32_t* cs, int32_t* cta_off, int32_t* cta_steps, GlaPiece* pieces) {
+  __shared__ int s_sum[1024], s_max[1024], s_cnt[1024];
+  const int tid = threadIdx.x, N = p.N, Hs = p.Hs;
+  const int per = (N + 1023) / 1024, n0 = min(tid * per, N), n1 = min(n0 + per, N);
+  int sum = 0, mx = 0;
+  for (int n = n0; n < n1; ++n) {
+    const int st = (p.cu[n + 1] - p.cu[n] + GC - 1) / GC;
+    sum += st; mx = max(mx, st);
+  }
+  s_sum[tid] = sum; s_max[tid] = mx;
+  __syncthreads();
+  for (int d = 1; d < 1024; d <<= 1) {   // inclusive scan of the per-thread step sums, running maximum
+    const int a = tid >= d ? s_sum[tid - d] : 0, b = tid >= d ? s_max[tid - d] : 0;
+    __syncthreads();
+    s_sum[tid] += a; s_max[tid] = max(s_max[tid], b);
+    __syncthreads();
+  }
+  int run = s_sum[tid] - sum;
+  for (int n = n0; n < n1; ++n) {
+    cs[n] = run;
+    run += (p.cu[n + 1] - p.cu[n] + GC - 1) / GC;
+  }
+  if (tid == 1023) cs[N] = s_sum[1023];
+  const int chains = N * Hs, total = Hs * s_sum[1023], longest = s_max[1023];
+  const int R = (total + ncta - 1) / ncta;
+  const bool cut = chains > ncta && total > 0 && R >= longest;
+  if (tid == 0) { p.plan[0] = cut ? 1 : 0; p.plan[1] = ncta; p.plan[2] = 0; p.plan[3] = R; }
+  for (int j = tid; j < ncta; j += 1024) p.flags[j] = 0;
+  __syncthreads();
+  if (!cut) return;
+  // thread j plans range [j R, (j+1) R): pass 0 counts its pieces, pass 1 writes them back to front
+  // (an empty chain is a point of the line: it goes to the range that holds the point and only
+  // moves its start state to its slot)
+  const int lo = tid * R, hi = tid == ncta - 1 ? 0x7fffffff : lo + R;
+  int c0 = 0;
+  if (tid < ncta) {
+    int a = 0, b = chains;             // first chain whose end is >= lo
+    while (a < b) {
+      const int m = (a + b) >> 1, n = m / Hs, sn = cs[n + 1] - cs[n];
+      if (Hs * cs[n] + (m - n * Hs + 1) * sn >= lo) b = m; else a = m + 1;
+    }
+    c0 = a;
+  }
+  int off = 0;
+  for (int pass = 0; pass < 2; ++pass) {
+    int cnt = 0;
+    if (tid < ncta) {
+      for (int c = c0; c < chains; ++c) {
+        const int n = c / Hs, hsx = c - n * Hs, sn = cs[n + 1] - cs[n];
+        const int P = Hs * cs[n] + hsx * sn, E = P + sn;
+        if (P >= hi) break;
+        if (sn > 0 ? E <= lo : P < lo) continue;
+        if (pass) {
+          const int a = max(P, lo), b = min(E, hi);
+          const bool starts = a == P, ends = b == E;
+          const int slot = p.slot[n], mode = p.init_mode[n], seq_len = p.cu[n + 1] - p.cu[n];
+          GlaPiece pc;
+          pc.tok_begin = p.cu[n] + (a - P) * GC;
+          pc.len = ends ? seq_len - (a - P) * GC : (b - a) * GC;
+          pc.hs = hsx;
+          pc.in_kind = 0; pc.in_idx = 0;
+          if (!starts) { pc.in_kind = 3; pc.in_idx = tid - 1; }
+          else if (mode == 1 && slot >= 0) { pc.in_kind = 1; pc.in_idx = slot; }
+          else if (mode == 2 && p.meta_state) pc.in_kind = 2;
+          pc.out_kind = 0; pc.out_idx = 0;
+          if (!ends) { pc.out_kind = 2; pc.out_idx = tid; }
+          else if (p.write_state && slot >= 0) { pc.out_kind = 1; pc.out_idx = slot; }
+          pc.pad = 0;
+          pieces[off + s_cnt[tid] - 1 - cnt] = pc;
+        }
+        ++cnt;
+      }
+    }
+    if (pass == 0) {
+      s_cnt[tid] = cnt;
+      __syncthreads();
+      for (int j = 0; j < tid && j < ncta; ++j) off += s_cnt[j];
+      if (tid < ncta) {
+        cta_off[tid] = off;
+        cta_steps[tid] = max(0, min(hi, total) - min(lo, total));
+        if (tid == ncta - 1) cta_off[ncta] = off + cnt;
+      }
+    }
+  }
+}
+
 }  // namespace hymeta
 
 using namespace hymeta;
@@ -700,6 +929,18 @@ extern "C" size_t hymeta_gla_prefill_workspace_bytes(int N, int Hs, int max_seql
   return (size_t)N * Hs * n_segs * GP_WS_ELEMS * sizeof(float);
 }
 
+// Balanced single-pass form (seg_len == HYMETA_GLA_SEG_BALANCED): workspace = one fp32 hand-off
+// buffer per SM, then the plan (header, per-CTA ranges, step totals, flags, step prefix, pieces).
+static size_t balanced_ints(int N, int ncta) {
+  return ((size_t)GP_PLAN_HDR + (ncta + 1) + ncta + ncta + (N + 1) + 3) & ~(size_t)3;
+}
+extern "C" size_t hymeta_gla_prefill_balanced_workspace_bytes(int N, int Hs) {
+  if (N <= 0 || Hs <= 0) return 0;
+  const int ncta = sm_count();
+  return (size_t)ncta * GP_WS_ELEMS * sizeof(float) + balanced_ints(N, ncta) * sizeof(int32_t) +
+         ((size_t)N * Hs + ncta) * sizeof(GlaPiece);
+}
+
 extern "C" int hymeta_gla_prefill_varlen_fused(
     const void* q, const void* k, const void* v, const void* g, void* o, void* state,
     const void* meta_state, const int32_t* cu_seqlens, const int32_t* slot_idx,
@@ -711,6 +952,13 @@ extern "C" int hymeta_gla_prefill_varlen_fused(
     void* stream) {
   if (N == 0) return HYMETA_OK;
   if (gate_table && g_is_fp32) return HYMETA_ERR_INVALID_ARG;   // the table maps bf16 gate bits
+  const bool balanced = seg_len == HYMETA_GLA_SEG_BALANCED;
+  if (balanced) {
+    if (N < 0 || Hs <= 0) return HYMETA_ERR_INVALID_ARG;
+    if (!workspace || ((uintptr_t)workspace % 16)) return HYMETA_ERR_INVALID_ARG;
+    if (workspace_bytes < hymeta_gla_prefill_balanced_workspace_bytes(N, Hs)) return HYMETA_ERR_WORKSPACE;
+    seg_len = 0;
+  }
   if (seg_len < 0 || seg_len % GC) return HYMETA_ERR_INVALID_ARG;
   int n_segs = 1;
   if (seg_len > 0 && max_seqlen > seg_len) {
@@ -744,6 +992,18 @@ extern "C" int hymeta_gla_prefill_varlen_fused(
   p.gate_table = (const uint16_t*)gate_table;
   p.sumsq = sumsq_out;
   p.seg_len = seg_len; p.n_segs = n_segs; p.pass = 0; p.ws = (float*)workspace;
+  p.plan = nullptr; p.cta_off = p.cta_steps = nullptr; p.pieces = nullptr; p.flags = nullptr;
+  int32_t* plan_cs = nullptr;
+  const int ncta = sm_count();
+  if (balanced) {
+    int32_t* ints = reinterpret_cast<int32_t*>((float*)workspace + (size_t)ncta * GP_WS_ELEMS);
+    p.plan = ints;
+    p.cta_off = ints + GP_PLAN_HDR;
+    p.cta_steps = ints + GP_PLAN_HDR + ncta + 1;
+    p.flags = ints + GP_PLAN_HDR + 2 * ncta + 1;
+    plan_cs = ints + GP_PLAN_HDR + 3 * ncta + 1;
+    p.pieces = reinterpret_cast<const GlaPiece*>(ints + balanced_ints(N, ncta));
+  }
   // TMA maps: raw g / k rows ([16 tokens][128 channels] boxes) and v (SWIZZLE_128B 64-wide halves)
   const int64_t tvec[] = {k_st, k_sh, g_st * (g_is_fp32 ? 2 : 1), g_sh * (g_is_fp32 ? 2 : 1)};
   for (int64_t s : tvec)
@@ -782,7 +1042,13 @@ extern "C" int hymeta_gla_prefill_varlen_fused(
     }
     count_launch();
   };
-  if (n_segs == 1) launch(0, 1);
+  if (balanced) {
+    gla_prefill_plan_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(
+        p, ncta, plan_cs, const_cast<int32_t*>(p.cta_off), const_cast<int32_t*>(p.cta_steps),
+        const_cast<GlaPiece*>(p.pieces));
+    count_launch();
+    launch(0, 1);
+  } else if (n_segs == 1) launch(0, 1);
   else {
     // (1) per-segment summaries from a zero start, (2) scan into segment start states, (3) outputs
     launch(1, n_segs - 1);

@@ -151,7 +151,13 @@ def gla_prefill_varlen(q, k, v, g, state, cu_seqlens, slot_idx, init_mode,
     if seg_len is None:
         seg_len = gla_prefill_seg_len(N * Hs, msl, q.device)
     ws, ws_bytes = None, 0
-    if seg_len:
+    if seg_len == GLA_SEG_BALANCED:
+        ws_bytes = lib().hymeta_gla_prefill_balanced_workspace_bytes(N, Hs)
+        if ws_bytes:
+            ws = _gla_workspace(q.device, ws_bytes)
+        else:
+            seg_len = 0
+    elif seg_len:
         ws_bytes = lib().hymeta_gla_prefill_workspace_bytes(N, Hs, msl, seg_len)
         if ws_bytes:
             ws = _gla_workspace(q.device, ws_bytes)
@@ -185,6 +191,7 @@ def _sumsq_buf(t: Optional[torch.Tensor], rows: int, heads: int) -> Optional[tor
 
 _SM_COUNT = {}
 _WS = {}
+GLA_SEG_BALANCED = -1      # HYMETA_GLA_SEG_BALANCED: equal step ranges per SM, chains cut where they straddle
 
 
 def _gla_workspace(device, nbytes: int) -> torch.Tensor:
