@@ -1,0 +1,30 @@
+import sys, torch
+sys.path.insert(0, "/root/repo")
+from vllm_hymeta_b200 import ops
+dev = "cuda"
+N, T, H, Hkv, D = 64, 8192, 28, 4, 128
+q = torch.randn(N * T, H, D, device=dev).bfloat16()
+k = torch.randn(N * T, Hkv, D, device=dev).bfloat16()
+v = torch.randn(N * T, Hkv, D, device=dev).bfloat16()
+g = (torch.nn.functional.logsigmoid(torch.randn(N * T, Hkv, D, device=dev)) / 16).bfloat16()
+state = torch.zeros(N, Hkv, D, D, device=dev, dtype=torch.bfloat16)
+cu = torch.arange(0, (N + 1) * T, T, device=dev, dtype=torch.int32)
+slots = torch.arange(N, device=dev, dtype=torch.int32)
+modes = torch.zeros(N, device=dev, dtype=torch.int32)
+out = torch.empty_like(q)
+gw = torch.ones(D, device=dev, dtype=torch.bfloat16)
+outs = {}
+for name, kw in (("plain", {}), ("gn", dict(gnorm_weight=gw, relu_qk=True))):
+    for seg in (0, -1):
+        fn = lambda: ops.gla_prefill_varlen(q, k, v, g, state, cu, slots, modes, max_seqlen=T, seg_len=seg, out=out, **kw)
+        for _ in range(2): fn()
+        torch.cuda.synchronize()
+        ts = []
+        for _ in range(7):
+            s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            s.record(); fn(); e.record(); torch.cuda.synchronize()
+            ts.append(s.elapsed_time(e))
+        ts.sort()
+        outs[(name, seg)] = out.clone()
+        print(f"{name} seg_len={seg}: {ts[len(ts)//2]:.3f} ms (min {ts[0]:.3f})", flush=True)
+    print(name, "equal:", torch.equal(outs[(name, 0)], outs[(name, -1)]))

@@ -69,6 +69,7 @@ struct __align__(16) GlaPiece {
 };
 constexpr int GP_PLAN_HDR = 4;                  // plan header ints: {cut mode, ctas, ticket, steps per CTA}
 
+
 struct GlaPrefillParams {
   const __nv_bfloat16 *q, *k, *v;
   const void* g;
@@ -206,11 +207,12 @@ gla_prefill_kernel(const GlaPrefillParams p, const __grid_constant__ CUtensorMap
   const uint32_t bars = sbase + GP_BAR;
   const uint32_t bar_kf = bars, bar_ke = bar_kf + 8 * GP_KS, bar_qf = bar_ke + 8 * GP_KS,
                  bar_a = bar_qf + 16, bar_p = bar_a + 16, bar_o = bar_p + 16, bar_x = bar_o + 16,
-                 bar_xf = bar_x + 16, bar_raw = bar_xf + 16;
+                 bar_xf = bar_x + 16, bar_raw = bar_xf + 16, bar_fin = bar_raw + 8 * GP_RS;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + GP_BAR + 200);
 
-  if (tid == 0) {
-    if (sbase & 1023) asm volatile("trap;");
+  auto init_bars = [&](bool again) {
+    if (again)   // a piece is over: every phase has completed, no asynchronous arrival is pending
+      for (uint32_t b = bar_kf; b <= bar_fin; b += 8) asm volatile("mbarrier.inval.shared::cta.b64 [%0];" :: "r"(b) : "memory");
     for (int s = 0; s < GP_KS; ++s) { mbar_init(bar_kf + 8 * s, 64); mbar_init(bar_ke + 8 * s, summary ? 128 : 257); }
     for (int i = 0; i < 2; ++i) {
       mbar_init(bar_qf + 8 * i, 128); mbar_init(bar_a + 8 * i, 1);
@@ -218,7 +220,21 @@ gla_prefill_kernel(const GlaPrefillParams p, const __grid_constant__ CUtensorMap
     }
     mbar_init(bar_x, 128); mbar_init(bar_x + 8, 128); mbar_init(bar_xf, 1); mbar_init(bar_xf + 8, 1);
     for (int s = 0; s < GP_RS; ++s) mbar_init(bar_raw + 8 * s, 1);
+    mbar_init(bar_fin, 1);
     fence_mbar_init();
+  };
+  // Between the pieces of a work list the pipeline drains and restarts from step 0 (a few steps of
+  // ramp per piece, ~1 % at config 2): every role's loops stay those of a single chain.
+  auto piece_end = [&]() {
+    tc_fence_before();
+    asm volatile("bar.sync 0;" ::: "memory");     // every role is done with the piece
+    if (tid == 0) init_bars(true);
+    asm volatile("bar.sync 0;" ::: "memory");
+    tc_fence_after();
+  };
+  if (tid == 0) {
+    if (sbase & 1023) asm volatile("trap;");
+    init_bars(false);
   }
   if (GN && tid >= 64 && tid < 80)   // g_norm weight -> smem once (read as broadcast words by every row owner)
     *reinterpret_cast<uint4*>(smem + GP_GW + (tid - 64) * 16) = ldg_nc_v4(p.gnorm_w + (tid - 64) * 8);
@@ -245,35 +261,23 @@ gla_prefill_kernel(const GlaPrefillParams p, const __grid_constant__ CUtensorMap
     constexpr uint32_t RAW_BYTES = GC * kD * (GB + 2);
     const uint8_t* rawp = smem + GP_RAW + c * GB;
     const uint8_t* rawkp = smem + GP_RAW + GP_RAW_K + c * 2;
-    // the raw ring runs GP_RS steps ahead of the stage being built, across piece boundaries: thread 0
-    // walks the work list a second time with its own cursor
-    int f_pi = 0, f_i = 0, f_g = 0, f_steps = (own.len + GC - 1) / GC, f_tok = own.tok_begin,
-        f_hk = own.hs / (p.Hs / p.Hk);
-    auto fetch = [&]() {
-      if (tid != 0) return;
-      while (f_pi < n_pieces && f_i >= f_steps) {
-        if (++f_pi >= n_pieces) break;
-        const GlaPiece pc = piece(f_pi);
-        f_i = 0; f_steps = (pc.len + GC - 1) / GC; f_tok = pc.tok_begin; f_hk = pc.hs / (p.Hs / p.Hk);
-      }
-      if (f_pi >= n_pieces) return;
-      const uint32_t bar = bar_raw + 8 * (f_g % GP_RS), dst = sbase + GP_RAW + (f_g % GP_RS) * GP_RAW_STAGE;
-      mbar_expect_tx(bar, RAW_BYTES);
-      tma_load_3d(dst, &tmG, bar, 0, f_hk, f_tok + f_i * GC);
-      tma_load_3d(dst + GP_RAW_K, &tmK, bar, 0, f_hk, f_tok + f_i * GC);
-      ++f_i; ++f_g;
-    };
     if (tid == 0) { tma_prefetch_desc(&tmG); tma_prefetch_desc(&tmK); tma_prefetch_desc(&tmV); }
-#pragma unroll
-    for (int i = 0; i < GP_RS; ++i) fetch();
-    int gbase = 0;
     for (int pi = 0; pi < n_pieces; ++pi) {
-     const GlaPiece pc = piece(pi);
-     const int n_steps = (pc.len + GC - 1) / GC, len = pc.len, tok_begin = pc.tok_begin;
-     const int hv = pc.hs / (p.Hs / p.Hv);
-     for (int li = 0; li < n_steps; ++li) {
-      const int i = gbase + li;                     // step index of the CTA: ring slots and phases
-      const int st = i % GP_KS, clen = len - li * GC;
+    const GlaPiece pc = piece(pi);
+    const int n_steps = (pc.len + GC - 1) / GC, len = pc.len, tok_begin = pc.tok_begin;
+    const int hk = pc.hs / (p.Hs / p.Hk), hv = pc.hs / (p.Hs / p.Hv);
+    auto fetch = [&](int i) {
+      if (i < n_steps && tid == 0) {
+        const uint32_t bar = bar_raw + 8 * (i % GP_RS), dst = sbase + GP_RAW + (i % GP_RS) * GP_RAW_STAGE;
+        mbar_expect_tx(bar, RAW_BYTES);
+        tma_load_3d(dst, &tmG, bar, 0, hk, tok_begin + i * GC);
+        tma_load_3d(dst + GP_RAW_K, &tmK, bar, 0, hk, tok_begin + i * GC);
+      }
+    };
+#pragma unroll
+    for (int i = 0; i < GP_RS; ++i) fetch(i);
+    for (int i = 0; i < n_steps; ++i) {
+      const int st = i % GP_KS, clen = len - i * GC;
       const uint32_t so = (uint32_t)((i % GP_RS) * GP_RAW_STAGE);
       uint8_t* stage = smem + GP_ST + st * GP_STAGE;
       if (tid == 0) GP_TRACE(i, 15);
@@ -325,15 +329,15 @@ gla_prefill_kernel(const GlaPrefillParams p, const __grid_constant__ CUtensorMap
         if (tid == 0) {
           const uint32_t dst = sT + st * GP_STAGE + GP_ST_V;
           mbar_expect_tx_only(bar_kf + 8 * st, GC * kD * 2);
-          tma_load_3d(dst, &tmV, bar_kf + 8 * st, 0, hv, tok_begin + li * GC);
-          tma_load_3d(dst + 2048, &tmV, bar_kf + 8 * st, 64, hv, tok_begin + li * GC);
+          tma_load_3d(dst, &tmV, bar_kf + 8 * st, 0, hv, tok_begin + i * GC);
+          tma_load_3d(dst + 2048, &tmV, bar_kf + 8 * st, 64, hv, tok_begin + i * GC);
         }
       } else {   // ragged last step: copy by hand, zero rows past the sequence end
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
           const int id = tid + 64 * j, t = id >> 4, vc = id & 15;
           uint4 x = make_uint4(0, 0, 0, 0);
-          if (t < clen) x = ldg_nc_v4(p.v + (int64_t)(tok_begin + li * GC + t) * p.v_st + (int64_t)hv * p.v_sh + vc * 8);
+          if (t < clen) x = ldg_nc_v4(p.v + (int64_t)(tok_begin + i * GC + t) * p.v_st + (int64_t)hv * p.v_sh + vc * 8);
           *reinterpret_cast<uint4*>(stage + GP_ST_V + (vc >> 3) * 2048 + sw128_chunk(t, vc & 7)) = x;
         }
       }
@@ -360,17 +364,19 @@ gla_prefill_kernel(const GlaPrefillParams p, const __grid_constant__ CUtensorMap
       // barrier right after the loads is NOT enough -- the compiler schedules their first use
       // behind it, and under LSU pressure the last rows were read after the refill).
       asm volatile("bar.sync 1, 64;" ::: "memory");   // both gate warps are done with the raw slot
-      fetch();
+      fetch(i + GP_RS);
       if (tid == 0) GP_TRACE(i, 0);
-     }
-     gbase += n_steps;
+    }
+    piece_end();
     }
    } else if (warp == 3) {
     // idle: g / k / v arrive by TMA
+    for (int pi = 0; pi < n_pieces; ++pi) piece_end();
    } else {
     // ================================================================== MMA issuer
-    if (!summary && cta_steps > 0 && elect_one_sync()) {
-      const int n_steps = cta_steps;                 // the issuer sees one stream of steps
+    for (int pi = 0; pi < n_pieces; ++pi) {
+    const int n_steps = (piece(pi).len + GC - 1) / GC;
+    if (!summary && n_steps > 0 && elect_one_sync()) {
       const uint32_t idesc_a = umma_idesc_bf16(128, 16, 0, 0);
       const uint32_t idesc_o = umma_idesc_bf16(128, 128, 0, 1);
       // descriptors differ from these templates only in the 16-byte-granular start address
@@ -428,8 +434,14 @@ gla_prefill_kernel(const GlaPrefillParams p, const __grid_constant__ CUtensorMap
         }
         GP_TRACE(i, 13);
       }
+      // every MMA of the piece has completed (and with it every commit it was to signal) before the
+      // barriers are torn down
+      umma_commit(bar_fin);
+      mbar_wait(bar_fin, 0);
     }
     __syncwarp();
+    piece_end();
+    }
    }
   } else if (warp < 8) {
     setmaxnreg_inc<208>();
@@ -440,9 +452,6 @@ gla_prefill_kernel(const GlaPrefillParams p, const __grid_constant__ CUtensorMap
     // The chain needs only the gate ring and a free X buffer, so it runs ahead of the MMA issuer.
     const int ws = warp - 4, gid = lane >> 2, tig = lane & 3;
     const int row0 = 32 * ws + gid;                 // rows row0 + 8j, j = 0..3 (m-tile j>>1, half j&1)
-    float S[2][16][4];
-    float Ptot[4];                                   // total decay of the segment (summary pass)
-    float Din[4];                                    // decay still owed by a state handed over at a cut
     // ldmatrix row addresses inside a stage (k~ / v tiles: [2 halves][16 tokens][64] SWIZZLE_128B)
     const int lt = (lane & 7) + 8 * ((lane >> 4) & 1);          // A: token row, d_k block (lane>>3)&1
     const uint32_t a_row = (uint32_t)(lt * 128), a_x = (uint32_t)(lt & 7);
@@ -450,58 +459,56 @@ gla_prefill_kernel(const GlaPrefillParams p, const __grid_constant__ CUtensorMap
     const int bt = (lane & 7) + 8 * ((lane >> 3) & 1);          // B: token row, d_v block pair lane>>4
     const uint32_t b_row = (uint32_t)(bt * 128), b_x = (uint32_t)(bt & 7);
     const float* sD0 = reinterpret_cast<const float*>(smem + GP_ST + GP_ST_D);
-    int gbase = 0;
+    float S[2][16][4];
     for (int pi = 0; pi < n_pieces; ++pi) {
-     const GlaPiece pc = piece(pi);
-     const int n_steps = (pc.len + GC - 1) / GC;
-     // ---- start state of the piece
-     {
-      const __nv_bfloat16* init_src = nullptr;
-      const float* ws_in = nullptr;
-      if (pc.in_kind == 1) init_src = p.state + (int64_t)pc.in_idx * p.st_ss + (int64_t)pc.hs * p.st_sh;
-      else if (pc.in_kind == 2) init_src = p.meta_state + (int64_t)pc.hs * p.meta_sh;
-      else if (pc.in_kind == 3) {
-        ws_in = p.ws + (int64_t)pc.in_idx * GP_WS_ELEMS;
-        if (p.flags) {   // handed over by the CTA that owns the head of this chain (it runs it first)
-          if (tid == 128) {
-            int v;
-            do {
-              asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p.flags + pc.in_idx) : "memory");
-            } while (v == 0);
-          }
-          asm volatile("bar.sync 2, 128;" ::: "memory");
+    const GlaPiece pc = piece(pi);
+    const int n_steps = (pc.len + GC - 1) / GC;
+    // ---- start state of the piece
+    const __nv_bfloat16* init_src = nullptr;
+    const float* ws_in = nullptr;
+    if (pc.in_kind == 1) init_src = p.state + (int64_t)pc.in_idx * p.st_ss + (int64_t)pc.hs * p.st_sh;
+    else if (pc.in_kind == 2) init_src = p.meta_state + (int64_t)pc.hs * p.meta_sh;
+    else if (pc.in_kind == 3) {
+      ws_in = p.ws + (int64_t)pc.in_idx * GP_WS_ELEMS;
+      if (p.flags) {   // handed over by the CTA that owns the head of this chain (it ran it first)
+        if (tid == 128) {
+          int v;
+          do {
+            asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p.flags + pc.in_idx) : "memory");
+          } while (v == 0);
         }
+        asm volatile("bar.sync 2, 128;" ::: "memory");
       }
+    }
+    __nv_bfloat16* final_dst = pc.out_kind == 1
+        ? p.state + (int64_t)pc.out_idx * p.st_ss + (int64_t)pc.hs * p.st_sh : nullptr;
+    float* ws_out = pc.out_kind == 2 ? p.ws + (int64_t)pc.out_idx * GP_WS_ELEMS : nullptr;
+    float Ptot[4], Din[4];   // total decay of the segment (summary pass); decay owed by a handed-over state
 #pragma unroll
-      for (int mt = 0; mt < 2; ++mt)
+    for (int mt = 0; mt < 2; ++mt)
 #pragma unroll
-        for (int nt = 0; nt < 16; ++nt)
+      for (int nt = 0; nt < 16; ++nt)
 #pragma unroll
-          for (int hf = 0; hf < 2; ++hf) {
-            const int off = (row0 + 16 * mt + 8 * hf) * kD + 8 * nt + 2 * tig;
-            if (ws_in) {
-              const float2 f = __ldcg(reinterpret_cast<const float2*>(ws_in + off));
-              S[mt][nt][2 * hf] = f.x; S[mt][nt][2 * hf + 1] = f.y;
-            } else {
-              uint32_t u = 0;
-              if (init_src) u = *reinterpret_cast<const uint32_t*>(init_src + off);
-              S[mt][nt][2 * hf] = bf16_lo(u); S[mt][nt][2 * hf + 1] = bf16_hi(u);
-            }
+        for (int hf = 0; hf < 2; ++hf) {
+          const int off = (row0 + 16 * mt + 8 * hf) * kD + 8 * nt + 2 * tig;
+          if (ws_in) {
+            const float2 f = __ldcg(reinterpret_cast<const float2*>(ws_in + off));
+            S[mt][nt][2 * hf] = f.x; S[mt][nt][2 * hf + 1] = f.y;
+          } else {
+            uint32_t u = 0;
+            if (init_src) u = *reinterpret_cast<const uint32_t*>(init_src + off);
+            S[mt][nt][2 * hf] = bf16_lo(u); S[mt][nt][2 * hf + 1] = bf16_hi(u);
           }
+        }
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        Ptot[j] = 1.f;
-        // at a cut the state travels WITHOUT its last step's decay, which is folded into the first
-        // rescale here exactly as the uncut chain folds it: S * (d_i * e_{i+1}), bit for bit
-        Din[j] = (ws_in && p.flags) ? __ldcg(ws_in + kD * kD + row0 + 8 * j) : 1.f;
-      }
-     }
-     __nv_bfloat16* final_dst = pc.out_kind == 1
-         ? p.state + (int64_t)pc.out_idx * p.st_ss + (int64_t)pc.hs * p.st_sh : nullptr;
-     float* ws_out = pc.out_kind == 2 ? p.ws + (int64_t)pc.out_idx * GP_WS_ELEMS : nullptr;
-     for (int li = -1; li < n_steps; ++li) {
-      const int i = gbase + li;                     // step index of the CTA (ring slots and phases)
-      const bool first = li < 0, last = li + 1 == n_steps;
+    for (int j = 0; j < 4; ++j) {
+      Ptot[j] = 1.f;
+      // at a cut the state travels WITHOUT its last step's decay, which is folded into the first
+      // rescale here exactly as the uncut chain folds it: S * (d_i * e_{i+1}), bit for bit
+      Din[j] = (ws_in && p.flags) ? __ldcg(ws_in + kD * kD + row0 + 8 * j) : 1.f;
+    }
+    for (int i = -1; i < n_steps; ++i) {
+      const bool first = i < 0, last = i + 1 == n_steps;
       if (!first && !(GP_EXP & 16)) {
         const uint32_t stg = sT + (i % GP_KS) * GP_STAGE;      // kf(i) was awaited in pass i-1
         uint32_t af[2][4];
@@ -546,39 +553,22 @@ gla_prefill_kernel(const GlaPrefillParams p, const __grid_constant__ CUtensorMap
       }
 #pragma unroll
       for (int j = 0; j < 4; ++j) Ptot[j] = handoff ? D[j] : Ptot[j] * D[j];
-      if (last) {
-        if (ws_out) {   // fp32 end state and decay: a segment summary, or the hand-off at a cut
+      if (summary) {
+        if (last) {   // local end state (zero start) and total decay of this segment
 #pragma unroll
           for (int mt = 0; mt < 2; ++mt)
 #pragma unroll
             for (int nt = 0; nt < 16; ++nt)
 #pragma unroll
               for (int hf = 0; hf < 2; ++hf)
-                __stcg(reinterpret_cast<float2*>(ws_out + (row0 + 16 * mt + 8 * hf) * kD + 8 * nt + 2 * tig),
-                       make_float2(S[mt][nt][2 * hf], S[mt][nt][2 * hf + 1]));
+                *reinterpret_cast<float2*>(ws_out + (row0 + 16 * mt + 8 * hf) * kD + 8 * nt + 2 * tig) =
+                    make_float2(S[mt][nt][2 * hf], S[mt][nt][2 * hf + 1]);
           if (tig == 0) {
 #pragma unroll
-            for (int j = 0; j < 4; ++j) __stcg(ws_out + kD * kD + row0 + 8 * j, Ptot[j]);
+            for (int j = 0; j < 4; ++j) ws_out[kD * kD + row0 + 8 * j] = Ptot[j];
           }
-          if (p.flags) {
-            __threadfence();
-            asm volatile("bar.sync 2, 128;" ::: "memory");
-            if (tid == 128) {
-              const int one = 1;
-              asm volatile("st.release.gpu.global.s32 [%0], %1;" :: "l"(p.flags + pc.out_idx), "r"(one) : "memory");
-            }
-          }
-        } else if (final_dst) {
-#pragma unroll
-          for (int mt = 0; mt < 2; ++mt)
-#pragma unroll
-            for (int nt = 0; nt < 16; ++nt)
-#pragma unroll
-              for (int hf = 0; hf < 2; ++hf)
-                *reinterpret_cast<uint32_t*>(final_dst + (row0 + 16 * mt + 8 * hf) * kD + 8 * nt + 2 * tig) =
-                    pack_bf16(S[mt][nt][2 * hf], S[mt][nt][2 * hf + 1]);
         }
-      } else if (!summary) {
+      } else if (!last) {
         // X_{i+1} -> buffer (i+1)&1, last read by q~ X of step i-1
         if (i >= 1) mbar_wait(bar_xf + 8 * ((i + 1) & 1), ((i - 1) >> 1) & 1);
         // rows row0 + 8j all have (row & 7) == gid: eight slot bases, everything else is immediate
@@ -597,10 +587,38 @@ gla_prefill_kernel(const GlaPrefillParams p, const __grid_constant__ CUtensorMap
         }
         fence_proxy_async_smem();
         mbar_arrive(bar_x + 8 * ((i + 1) & 1));   // one barrier per buffer: the state may run a full buffer ahead
-        if (tid == 128 && li >= 0) GP_TRACE(i, 3);
+        if (tid == 128 && i >= 0) GP_TRACE(i, 3);
+      } else if (ws_out) {   // cut: fp32 state (without the last decay) and that decay, then the flag
+#pragma unroll
+        for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+          for (int nt = 0; nt < 16; ++nt)
+#pragma unroll
+            for (int hf = 0; hf < 2; ++hf)
+              __stcg(reinterpret_cast<float2*>(ws_out + (row0 + 16 * mt + 8 * hf) * kD + 8 * nt + 2 * tig),
+                     make_float2(S[mt][nt][2 * hf], S[mt][nt][2 * hf + 1]));
+        if (tig == 0) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) __stcg(ws_out + kD * kD + row0 + 8 * j, Ptot[j]);
+        }
+        __threadfence();
+        asm volatile("bar.sync 2, 128;" ::: "memory");
+        if (tid == 128) {
+          const int one = 1;
+          asm volatile("st.release.gpu.global.s32 [%0], %1;" :: "l"(p.flags + pc.out_idx), "r"(one) : "memory");
+        }
+      } else if (final_dst) {
+#pragma unroll
+        for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+          for (int nt = 0; nt < 16; ++nt)
+#pragma unroll
+            for (int hf = 0; hf < 2; ++hf)
+              *reinterpret_cast<uint32_t*>(final_dst + (row0 + 16 * mt + 8 * hf) * kD + 8 * nt + 2 * tig) =
+                  pack_bf16(S[mt][nt][2 * hf], S[mt][nt][2 * hf + 1]);
       }
-     }
-     gbase += n_steps;
+    }
+    piece_end();
     }
   } else {
     setmaxnreg_dec<112>();
@@ -614,24 +632,15 @@ gla_prefill_kernel(const GlaPrefillParams p, const __grid_constant__ CUtensorMap
     // q~ row (hh*16 + t) of 16-byte chunk qc: byte offsets of tokens qt0 / qt0+8 for head slot 0
     uint8_t* sQw = smem + GP_SQ + w * 32768 + (qc >> 3) * 16384;
     const uint32_t qo0 = (uint32_t)(qt0 * 128 + (((qc ^ qt0) & 7) << 4)), qo1 = qo0 + 1024;   // (qt0+8)&7 == qt0&7
-    const __nv_bfloat16* qp = p.q + (int64_t)qt0 * p.q_st + qc * 8;
-    const int q_steps = summary ? 0 : cta_steps;    // the summary pass has no queries
-    // cursor over the work list, positioned on the tile being prefetched (two steps ahead)
-    int n_pi = 0, n_base = 0, n_cnt = (own.len + GC - 1) / GC, n_tok = own.tok_begin, n_len = own.len,
-        n_h0 = own.hs * G;
-    auto seek = [&](int g) {
-      while (n_pi < n_pieces && g >= n_base + n_cnt) {
-        n_base += n_cnt;
-        if (++n_pi >= n_pieces) break;
-        const GlaPiece pc = piece(n_pi);
-        n_cnt = (pc.len + GC - 1) / GC; n_tok = pc.tok_begin; n_len = pc.len; n_h0 = pc.hs * G;
-      }
-    };
-    int clen = 0, tok0 = 0, h0 = 0;                 // step i: valid tokens, first token row, first q head
     uint4 qv[16];
+    for (int pi = 0; pi < n_pieces; ++pi) {
+    const GlaPiece pc = piece(pi);
+    const int n_steps = (pc.len + GC - 1) / GC, len = pc.len, tok_begin = pc.tok_begin, h0 = pc.hs * G;
+    const __nv_bfloat16* qp = p.q + (int64_t)(tok_begin + qt0) * p.q_st + (int64_t)h0 * p.q_sh + qc * 8;
+    const int q_steps = summary ? 0 : n_steps;      // the summary pass has no queries
     int cnt = 0;
     for (int i = w - 2; i < q_steps; i += 2) {
-      int nx_clen = 0, nx_tok0 = 0, nx_h0 = 0;
+      const int clen = len - i * GC;
       if (i >= 0) {
         const int st = i % GP_KS;
         // ---- build q~ from the registers prefetched one tile ahead (buffer w is free: this
@@ -663,10 +672,8 @@ gla_prefill_kernel(const GlaPrefillParams p, const __grid_constant__ CUtensorMap
         if (tq == 0) GP_TRACE(i, 5);
       }
       if (i + 2 < q_steps) {                        // next tile: in flight under the P conversion and epilogue
-        seek(i + 2);
-        nx_clen = n_len - (i + 2 - n_base) * GC; nx_tok0 = n_tok + (i + 2 - n_base) * GC; nx_h0 = n_h0;
-        const int rem = nx_clen - qt0;              // token qt0 + 8e valid iff 8e < rem
-        const __nv_bfloat16* src = qp + (int64_t)nx_tok0 * p.q_st + (int64_t)nx_h0 * p.q_sh;
+        const int rem = len - (i + 2) * GC - qt0;   // token qt0 + 8e valid iff 8e < rem
+        const __nv_bfloat16* src = qp + (int64_t)(i + 2) * GC * p.q_st;
 #pragma unroll
         for (int it = 0; it < 16; ++it) {
           qv[it] = make_uint4(0, 0, 0, 0);
@@ -770,17 +777,18 @@ gla_prefill_kernel(const GlaPrefillParams p, const __grid_constant__ CUtensorMap
                 const int rq = (warp & 3) * 32 + row, hh2 = rq >> 4, t2 = rq & 15;
                 const uint4 o4 = *reinterpret_cast<const uint4*>(stg + row * 64 + (((c ^ (row >> 1)) & 3) << 4));
                 if (hh2 < G && t2 < clen)
-                  stg_v4(p.o + (int64_t)(tok0 + t2) * p.o_st + (int64_t)(h0 + hh2) * p.o_sh + 32 * cc + 8 * c, o4);
+                  stg_v4(p.o + (int64_t)(tok_begin + i * GC + t2) * p.o_st + (int64_t)(h0 + hh2) * p.o_sh + 32 * cc + 8 * c, o4);
               }
             }
             __syncwarp();
           }
           if (p.sumsq && (tq >> 4) < G && r_t < clen)
-            p.sumsq[(int64_t)(tok0 + r_t) * p.H + h0 + (tq >> 4)] = ssq;
+            p.sumsq[(int64_t)(tok_begin + i * GC + r_t) * p.H + h0 + (tq >> 4)] = ssq;
         }
         ++cnt;
       }
-      clen = nx_clen; tok0 = nx_tok0; h0 = nx_h0;
+    }
+    piece_end();
     }
   }
   tc_fence_before();

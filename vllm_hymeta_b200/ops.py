@@ -129,7 +129,9 @@ def gla_prefill_varlen(q, k, v, g, state, cu_seqlens, slot_idx, init_mode,
     gnorm_weight [D] bf16: the 7B per-head ``g_norm`` RMSNorm applied as the kernel's epilogue.
     relu_qk: q and k are raw projection rows, relu is applied in the kernel.
     gate_table (``gla_gate_7b_table``): g holds the RAW bf16 gk rows and the kernel maps them through
-    the table -- no separate gate pass.  sumsq_out [T,H] fp32: the epilogue also writes each bf16
+    the table -- no separate gate pass.  seg_len: None = automatic (sequence-parallel segments for few
+    long chains, ``GLA_SEG_BALANCED`` when there are more chains than SMs, else one chain per CTA), 0 =
+    one chain per CTA, > 0 = segment length.  sumsq_out [T,H] fp32: the epilogue also writes each bf16
     output row's sum of squares (f1: RMS-norm partials for ``branch_norm_merge``)."""
     T, H, D = q.shape
     Hk, Hv, Hs = k.shape[1], v.shape[1], state.shape[1]
@@ -150,6 +152,10 @@ def gla_prefill_varlen(q, k, v, g, state, cu_seqlens, slot_idx, init_mode,
     msl = int(max_seqlen if max_seqlen is not None else T)
     if seg_len is None:
         seg_len = gla_prefill_seg_len(N * Hs, msl, q.device)
+        if seg_len == 0 and N * Hs > _sm_count(q.device):
+            # more chains than SMs: equal step ranges per SM instead of whole chains in waves (the
+            # device-side plan keeps the plain grid when one chain exceeds an SM's share)
+            seg_len = GLA_SEG_BALANCED
     ws, ws_bytes = None, 0
     if seg_len == GLA_SEG_BALANCED:
         ws_bytes = lib().hymeta_gla_prefill_balanced_workspace_bytes(N, Hs)
@@ -208,6 +214,14 @@ def _gla_workspace(device, nbytes: int) -> torch.Tensor:
     return w
 
 
+def _sm_count(device=None) -> int:
+    dev = torch.cuda.current_device() if device is None or device.index is None else device.index
+    sms = _SM_COUNT.get(dev)
+    if sms is None:
+        sms = _SM_COUNT[dev] = torch.cuda.get_device_properties(dev).multi_processor_count
+    return sms
+
+
 def gla_prefill_seg_len(chains: int, max_seqlen: int, device=None, min_seg: int = 256) -> int:
     """Segment length for the sequence-parallel prefill, or 0 for the single-pass form.  One CTA per
     SM walks one chain, so the launch is quantised in waves of ``sms`` CTAs: candidates are the
@@ -215,10 +229,7 @@ def gla_prefill_seg_len(chains: int, max_seqlen: int, device=None, min_seg: int 
     (tools/sweep_gla_segs.py) the three-pass form costs ~1.5x its ideal w * T / n_segs (the summary
     pass re-reads k/v/g), so it is taken only when that still beats ceil(chains / sms) full-length
     waves -- never for whole waves of full sequences (config 2), always for few long chains."""
-    dev = torch.cuda.current_device() if device is None or device.index is None else device.index
-    sms = _SM_COUNT.get(dev)
-    if sms is None:
-        sms = _SM_COUNT[dev] = torch.cuda.get_device_properties(dev).multi_processor_count
+    sms = _sm_count(device)
     if chains <= 0 or max_seqlen < 2 * min_seg:
         return 0
     best_cost, best_ns = float(-(-chains // sms)), 1          # single pass: full-length waves
