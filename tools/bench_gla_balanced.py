@@ -1,3 +1,7 @@
+#!/usr/bin/env python3
+"""GLA prefill at the config-2 shape (64 x 8192, 28/4 heads): one chain per CTA (seg_len 0) against the
+balanced work lists (seg_len -1), plain and with the 7B relu + g_norm epilogue; checks that the two
+forms produce the same bits.  HYMETA_B200_LIB=<A/B library> selects another build of the kernels."""
 import sys, torch
 sys.path.insert(0, "/root/repo")
 from vllm_hymeta_b200 import ops

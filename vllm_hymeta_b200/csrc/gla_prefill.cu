@@ -35,6 +35,11 @@ constexpr int GC = 16;                          // tokens per step
 #ifndef GP_KS_
 #define GP_KS_ 3
 #endif
+#ifndef GP_GN_UNROLL
+#define GP_GN_UNROLL 4   // g_norm pass 1: 4 chunks in flight (A/B on B200: 1 -> 2.55, 2 -> 2.50, 4 -> 2.47, 8 -> 2.54 ms)
+#endif
+#define GP_STR_(x) #x
+#define GP_STR(x) GP_STR_(x)
 #ifndef GP_EXP
 #define GP_EXP 0   // timing / bisection experiments of tools/trace_gla_prefill.py (bit mask); 0 in the product build
 #endif
@@ -715,7 +720,7 @@ gla_prefill_kernel(const GlaPrefillParams p, const __grid_constant__ CUtensorMap
           float rstd = 0.f;
           if (GN) {
             float ss = 0.f;
-#pragma unroll 1
+_Pragma(GP_STR(unroll GP_GN_UNROLL))
             for (int cc = 0; cc < 8; ++cc) {   // 16 columns at a time: the q prefetch holds 64 registers here
               float t[16];
               tmem_ld16(tOw + 16 * cc, t);
