@@ -39,6 +39,8 @@ def main():
     ap.add_argument("--Hkv", type=int, default=4)
     ap.add_argument("--first", type=int, default=40)
     ap.add_argument("--count", type=int, default=6)
+    ap.add_argument("--fused", type=int, default=0,
+                    help="1: raw bf16 gate rows through the 7B gate table; 2: + relu + g_norm epilogue")
     ap.add_argument("--exp", type=int, default=0, help="GP_EXP timing-experiment mask (results are wrong)")
     a = ap.parse_args()
     global TRACE_LIB
@@ -68,11 +70,17 @@ def main():
     h = _lib.lib()
     h.hymeta_debug_set_gla_trace.restype = C.c_int
     h.hymeta_debug_set_gla_trace.argtypes = [C.c_void_p]
+    kw = {}
+    if a.fused >= 1:
+        g = torch.randn(N * T, Hkv, D, device=dev).bfloat16()          # raw gk projection rows
+        kw["gate_table"] = ops.gla_gate_7b_table(16.0, q.device)
+    if a.fused >= 2:
+        kw.update(relu_qk=True, gnorm_weight=torch.ones(D, device=dev, dtype=torch.bfloat16))
     for _ in range(2):
-        ops.gla_prefill_varlen(q, k, v, g, state, cu, slots, modes, max_seqlen=T)
+        ops.gla_prefill_varlen(q, k, v, g, state, cu, slots, modes, max_seqlen=T, **kw)
     torch.cuda.synchronize()
     assert h.hymeta_debug_set_gla_trace(trace.data_ptr()) == 0
-    ops.gla_prefill_varlen(q, k, v, g, state, cu, slots, modes, max_seqlen=T)
+    ops.gla_prefill_varlen(q, k, v, g, state, cu, slots, modes, max_seqlen=T, **kw)
     torch.cuda.synchronize()
     h.hymeta_debug_set_gla_trace(None)
     tr = trace.cpu().view(4096, 16)[:steps]
