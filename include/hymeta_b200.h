@@ -470,6 +470,18 @@ int hymeta_branch_norm_merge_tp_sumsq(const void* x_attn, const void* x_linear, 
                                       int64_t t_cap, uint32_t epoch, float eps, int64_t xa_st,
                                       int64_t xl_st, int64_t o_st, const float* sumsq_attn,
                                       const float* sumsq_linear, int heads_local, void* stream);
+/* CUDA-graph form of hymeta_branch_norm_merge_tp_sumsq: a replayed graph cannot carry a fresh by-value
+ * epoch, so the epoch lives in device memory.  epoch_state: two uint32 {last epoch, CTAs done}, 8-byte
+ * aligned, zero before the first call, owned by the exchange (one per peer_buffers set) and touched by
+ * nothing else; every CTA derives the call's epoch from it and the last CTA to finish advances it.
+ * Every rank must issue (or replay) the same sequence of calls on the group; do not mix this entry
+ * point and the by-value one on the same buffers. */
+int hymeta_branch_norm_merge_tp_graph(const void* x_attn, const void* x_linear, const float* w_attn,
+                                      const float* w_linear, void* out, int T, int hidden_local,
+                                      int tp_world, int tp_rank, const uint64_t* peer_buffers,
+                                      int64_t t_cap, uint32_t* epoch_state, float eps, int64_t xa_st,
+                                      int64_t xl_st, int64_t o_st, const float* sumsq_attn,
+                                      const float* sumsq_linear, int heads_local, void* stream);
 /* hymeta_swa_meta_prefill_varlen plus sumsq_out ([rows, H] fp32, rows as `out`; null = plain): each
  * output row's sum of squares over the head's 128 bf16 values, from the kernel's epilogue. */
 int hymeta_swa_meta_prefill_varlen_sumsq(

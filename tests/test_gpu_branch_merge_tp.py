@@ -22,7 +22,8 @@ def _worker(rank: int, world: int, port: int, q):
         dist.init_process_group("nccl", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world,
                                 device_id=torch.device("cuda", rank))
         eps = 1e-6
-        ex = ops.BranchMergeExchange(None, t_cap=4096)
+        ex = ops.BranchMergeExchange(None, t_cap=4096)                      # epoch in device memory
+        ex_host = ops.BranchMergeExchange(None, t_cap=4096, device_epoch=False)   # epoch by value
         worst = 0.0
         for T, hidden in ((1, 3584), (257, 3584), (4096, 3584), (64, 2048)):
             gen = torch.Generator().manual_seed(T)           # same data on every rank
@@ -42,6 +43,9 @@ def _worker(rank: int, world: int, port: int, q):
             for rep in range(3):                             # epochs advance, both slot parities get used
                 fused = ops.branch_norm_merge(dxa, dxl, dw1, dw2, eps, tp_world=world, exchange=ex)
             nccl = ops.branch_norm_merge(dxa, dxl, dw1, dw2, eps, tp_world=world)
+            for rep in range(2):
+                fused_host = ops.branch_norm_merge(dxa, dxl, dw1, dw2, eps, tp_world=world, exchange=ex_host)
+            assert torch.equal(fused_host, fused), (T, hidden)
             # f1 as specified: the per-(token, head) partials the attention epilogues emit feed the merge
             heads = hl // 128
             sa = dxa.float().view(T, heads, 128).pow(2).sum(-1).contiguous()
@@ -59,6 +63,36 @@ def _worker(rank: int, world: int, port: int, q):
             # world 2: a + b in either order is the same float, so the two forms agree bit for bit
             if world == 2:
                 assert torch.equal(fused, nccl), (T, hidden)
+        # ---- CUDA graph: the captured launch is replayed with new inputs, the kernel advances its
+        #      own epoch; eager calls in between keep the same epoch sequence on both ranks
+        T, hl = 64, 3584 // world
+        gen = torch.Generator().manual_seed(99)
+        xs = [(torch.randn(T, 3584, generator=gen) * (1 + i)).bfloat16()[:, rank * hl:(rank + 1) * hl].cuda().contiguous()
+              for i in range(4)]
+        wa = (1 + 0.1 * torch.randn(3584, generator=gen))[rank * hl:(rank + 1) * hl].cuda().contiguous()
+        wb = (1 + 0.1 * torch.randn(3584, generator=gen))[rank * hl:(rank + 1) * hl].cuda().contiguous()
+        sa, sb = torch.empty_like(xs[0]), torch.empty_like(xs[0])
+        gout = torch.empty_like(xs[0])
+        sa.copy_(xs[0]); sb.copy_(xs[1])
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            ops.branch_norm_merge(sa, sb, wa, wb, eps, tp_world=world, exchange=ex, out=gout)   # warm-up
+        torch.cuda.current_stream().wait_stream(side)
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            ops.branch_norm_merge(sa, sb, wa, wb, eps, tp_world=world, exchange=ex, out=gout)
+            ops.branch_norm_merge(gout, sb, wa, wb, eps, tp_world=world, exchange=ex, out=gout)  # two calls per replay
+        for i in range(5):
+            a, b = xs[i % 4], xs[(i + 1) % 4]
+            sa.copy_(a); sb.copy_(b)
+            graph.replay()
+            want = ops.branch_norm_merge(a, b, wa, wb, eps, tp_world=world)          # NCCL form, eager
+            want = ops.branch_norm_merge(want, b, wa, wb, eps, tp_world=world)
+            if i % 2:
+                ops.branch_norm_merge(a, b, wa, wb, eps, tp_world=world, exchange=ex)  # eager call between replays
+            torch.cuda.synchronize()
+            assert torch.equal(gout, want), ("graph replay", i)
         dist.barrier()
         dist.destroy_process_group()
         q.put((rank, "ok", worst))

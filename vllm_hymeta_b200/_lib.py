@@ -54,6 +54,8 @@ SIGNATURES = {
     "hymeta_branch_norm_merge_tp": (_i, [_p] * 5 + [_i] * 4 + [_p, _i64, C.c_uint32, _f, _i64, _i64, _i64, _p]),
     "hymeta_branch_norm_merge_tp_sumsq": (_i, [_p] * 5 + [_i] * 4 + [_p, _i64, C.c_uint32, _f, _i64, _i64, _i64,
                                               _p, _p, _i, _p]),
+    "hymeta_branch_norm_merge_tp_graph": (_i, [_p] * 5 + [_i] * 4 + [_p, _i64, _p, _f, _i64, _i64, _i64,
+                                              _p, _p, _i, _p]),
     "hymeta_swa_meta_prefill_varlen_sumsq": (_i, [_p] * 10 + [_i64, _i] + [_i] * 9 + [_f] + [_i64] * 16 + [_p, _p]),
     "hymeta_slot_mgr_create": (_p, [_i]),
     "hymeta_slot_mgr_destroy": (None, [_p]),

@@ -208,8 +208,15 @@ branch_norm_merge_tp_kernel(const __nv_bfloat16* x1, const __nv_bfloat16* x2,
                             __nv_bfloat16* out, int T, int hidden, int world, int rank, uint32_t epoch,
                             int64_t t_cap, const TpPeers peers, float eps, int64_t x1_st, int64_t x2_st,
                             int64_t o_st, const float* __restrict__ ss1, const float* __restrict__ ss2,
-                            int heads) {
+                            int heads, uint32_t* epoch_state) {
   const int lane = threadIdx.x & 31, wpb = blockDim.x >> 5;
+  if (epoch_state) {
+    // Device-side epoch (CUDA-graph replays carry no fresh by-value argument): {last epoch, CTAs done}.
+    // Every CTA of this launch reads the same last epoch -- it is advanced by the LAST CTA to finish.
+    uint32_t cur;
+    asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(cur) : "l"(epoch_state) : "memory");
+    epoch = cur % 0x7fffffffu + 1u;              // never 0 (the zero fill of the slots)
+  }
   const int chunks = hidden / 8;
   const float inv = 1.f / (float)hidden, inv_tp = 1.f / (float)world;
   const int64_t par = (int64_t)(epoch & 1u) * world;
@@ -317,6 +324,16 @@ branch_norm_merge_tp_kernel(const __nv_bfloat16* x1, const __nv_bfloat16* x2,
       }
     }
   }
+  if (epoch_state) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      __threadfence();
+      if (atomicAdd(epoch_state + 1, 1u) == gridDim.x - 1) {
+        epoch_state[1] = 0;
+        asm volatile("st.volatile.global.u32 [%0], %1;" :: "l"(epoch_state), "r"(epoch) : "memory");
+      }
+    }
+  }
 }
 
 static int check_common(const void* x1, const void* x2, int T, int hidden, int64_t x1_st,
@@ -384,13 +401,18 @@ extern "C" size_t hymeta_branch_merge_tp_buffer_bytes(int tp_world, int64_t t_ca
   return (size_t)2 * tp_world * (size_t)t_cap * sizeof(uint4);
 }
 
-extern "C" int hymeta_branch_norm_merge_tp_sumsq(const void* x_attn, const void* x_linear, const float* w_attn,
-                                           const float* w_linear, void* out, int T, int hidden_local,
-                                           int tp_world, int tp_rank, const uint64_t* peer_buffers,
-                                           int64_t t_cap, uint32_t epoch, float eps, int64_t xa_st,
-                                           int64_t xl_st, int64_t o_st, const float* sumsq_attn,
-                                           const float* sumsq_linear, int heads_local, void* stream) {
+static int branch_norm_merge_tp_impl(const void* x_attn, const void* x_linear, const float* w_attn,
+                                     const float* w_linear, void* out, int T, int hidden_local,
+                                     int tp_world, int tp_rank, const uint64_t* peer_buffers,
+                                     int64_t t_cap, uint32_t epoch, uint32_t* epoch_state, float eps,
+                                     int64_t xa_st, int64_t xl_st, int64_t o_st, const float* sumsq_attn,
+                                     const float* sumsq_linear, int heads_local, void* stream) {
+  // T == 0 launches nothing on any rank (every rank passes the same T), so the epochs stay aligned
   if (T == 0) return HYMETA_OK;
+  if (epoch_state) {
+    if ((uintptr_t)epoch_state & 7) return HYMETA_ERR_INVALID_ARG;
+    epoch = 1;   // placeholder: the kernel derives the epoch from epoch_state
+  }
   if ((sumsq_attn == nullptr) != (sumsq_linear == nullptr) || (sumsq_attn && heads_local <= 0))
     return HYMETA_ERR_INVALID_ARG;
   const int rc = check_common(x_attn, x_linear, T, hidden_local, xa_st, xl_st);
@@ -415,11 +437,34 @@ extern "C" int hymeta_branch_norm_merge_tp_sumsq(const void* x_attn, const void*
     kernel<<<grid, 128, 0, (cudaStream_t)stream>>>(
         (const __nv_bfloat16*)x_attn, (const __nv_bfloat16*)x_linear, w_attn, w_linear, (__nv_bfloat16*)out, T,
         hidden_local, tp_world, tp_rank, epoch, t_cap, peers, eps, xa_st, xl_st, o_st, sumsq_attn, sumsq_linear,
-        heads_local);
+        heads_local, epoch_state);
   };
   go(branch_norm_merge_tp_kernel);
   count_launch();
   return check_launch();
+}
+
+extern "C" int hymeta_branch_norm_merge_tp_sumsq(const void* x_attn, const void* x_linear, const float* w_attn,
+                                           const float* w_linear, void* out, int T, int hidden_local,
+                                           int tp_world, int tp_rank, const uint64_t* peer_buffers,
+                                           int64_t t_cap, uint32_t epoch, float eps, int64_t xa_st,
+                                           int64_t xl_st, int64_t o_st, const float* sumsq_attn,
+                                           const float* sumsq_linear, int heads_local, void* stream) {
+  return branch_norm_merge_tp_impl(x_attn, x_linear, w_attn, w_linear, out, T, hidden_local, tp_world, tp_rank,
+                                   peer_buffers, t_cap, epoch, nullptr, eps, xa_st, xl_st, o_st, sumsq_attn,
+                                   sumsq_linear, heads_local, stream);
+}
+
+extern "C" int hymeta_branch_norm_merge_tp_graph(const void* x_attn, const void* x_linear, const float* w_attn,
+                                           const float* w_linear, void* out, int T, int hidden_local,
+                                           int tp_world, int tp_rank, const uint64_t* peer_buffers,
+                                           int64_t t_cap, uint32_t* epoch_state, float eps, int64_t xa_st,
+                                           int64_t xl_st, int64_t o_st, const float* sumsq_attn,
+                                           const float* sumsq_linear, int heads_local, void* stream) {
+  if (!epoch_state) return HYMETA_ERR_INVALID_ARG;
+  return branch_norm_merge_tp_impl(x_attn, x_linear, w_attn, w_linear, out, T, hidden_local, tp_world, tp_rank,
+                                   peer_buffers, t_cap, 0, epoch_state, eps, xa_st, xl_st, o_st, sumsq_attn,
+                                   sumsq_linear, heads_local, stream);
 }
 
 extern "C" int hymeta_branch_norm_merge_tp(const void* x_attn, const void* x_linear, const float* w_attn,

@@ -469,9 +469,12 @@ class BranchMergeExchange:
     of the TP group, allocated as torch symmetric memory (CUDA peer mapping over NVLink) and handed
     to ``hymeta_branch_norm_merge_tp`` as raw addresses.  Create it once per group (collective call:
     every rank of ``group`` must construct it with the same ``t_cap``); each ``branch_norm_merge(...,
-    exchange=ex)`` call advances the epoch, so every rank must make the same sequence of calls."""
+    exchange=ex)`` call advances the epoch, so every rank must make the same sequence of calls.
+    ``device_epoch`` (default): the epoch lives in device memory and the kernel advances it itself, so
+    the call can be captured in a CUDA graph and replayed (every rank replays the same graphs in the
+    same order); False: the host counts and passes the epoch by value (eager launches only)."""
 
-    def __init__(self, group, t_cap: int, device=None):
+    def __init__(self, group, t_cap: int, device=None, device_epoch: bool = True):
         import torch.distributed as dist
         import torch.distributed._symmetric_memory as symm_mem
         self.group = group if group is not None else dist.group.WORLD
@@ -488,6 +491,8 @@ class BranchMergeExchange:
         torch.cuda.synchronize(device)
         dist.barrier(self.group)        # every buffer is zeroed before any peer may write into it
         self.epoch = 0
+        # {last epoch, CTAs done}: read and advanced by the kernel (hymeta_branch_norm_merge_tp_graph)
+        self.epoch_state = torch.zeros(2, dtype=torch.int32, device=device) if device_epoch else None
 
     def next_epoch(self) -> int:
         self.epoch = self.epoch % 0x7fffffff + 1      # never 0 (the zero fill), +1 per call
@@ -532,6 +537,13 @@ def branch_norm_merge(x_attn: torch.Tensor, x_linear: torch.Tensor, w_attn: torc
                 _req(t, "sumsq", torch.float32)
                 if t.shape != (T, heads) or not t.is_contiguous():
                     raise ValueError("sumsq tensors must be contiguous [T, heads_local] fp32")
+        if exchange.epoch_state is not None:
+            check(lib().hymeta_branch_norm_merge_tp_graph(
+                _ptr(x_attn), _ptr(x_linear), _ptr(w_attn), _ptr(w_linear), _ptr(out), T, Hd, tp_world,
+                exchange.rank, exchange.ptrs, exchange.t_cap, _ptr(exchange.epoch_state), float(eps),
+                x_attn.stride(0), x_linear.stride(0), out.stride(0), _ptr(sa), _ptr(sl), heads, _stream()),
+                "hymeta_branch_norm_merge_tp_graph")
+            return out
         check(lib().hymeta_branch_norm_merge_tp_sumsq(
             _ptr(x_attn), _ptr(x_linear), _ptr(w_attn), _ptr(w_linear), _ptr(out), T, Hd, tp_world,
             exchange.rank, exchange.ptrs, exchange.t_cap, exchange.next_epoch(), float(eps),
