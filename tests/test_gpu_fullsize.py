@@ -196,3 +196,9 @@ def test_config2_full_batch_prefill_64x8192_sampled_rows(ops):
         rows = [0, 1, 15, 16, 63, 64, 1000, 4096, 8191]
         assert_close(o[r][rows], ro[rows], f"config-2 GLA prefill seq {n} sampled rows")
         assert_close(state[int(slots[n])], rS[:: H // Hkv], f"config-2 GLA final state seq {n}")
+    # the launch above ran the balanced work lists (256 chains > 148 SMs, chains cut across SMs); one
+    # chain per CTA must give the same bits for every row and every state
+    state1 = torch.zeros_like(state)
+    o1 = ops.gla_prefill_varlen(qg, kg, v, g, state1, cu, slots, _i32([0] * N), max_seqlen=L, seg_len=0)
+    torch.cuda.synchronize()
+    assert torch.equal(o1, o) and torch.equal(state1, state)
