@@ -18,7 +18,11 @@ modes = torch.zeros(N, device=dev, dtype=torch.int32)
 out = torch.empty_like(q)
 gw = torch.ones(D, device=dev, dtype=torch.bfloat16)
 outs = {}
-for name, kw in (("plain", {}), ("gn", dict(gnorm_weight=gw, relu_qk=True))):
+graw = torch.randn(N * T, Hkv, D, device=dev).bfloat16()      # raw gk rows for the gate-table form
+gfull = g
+for name, kw in (("plain", {}), ("gn", dict(gnorm_weight=gw, relu_qk=True)),
+                 ("fused", dict(gnorm_weight=gw, relu_qk=True, gate_table=ops.gla_gate_7b_table(16.0, q.device)))):
+    g = graw if name == "fused" else gfull
     for seg in (0, -1):
         fn = lambda: ops.gla_prefill_varlen(q, k, v, g, state, cu, slots, modes, max_seqlen=T, seg_len=seg, out=out, **kw)
         for _ in range(2): fn()
