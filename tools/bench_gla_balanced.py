@@ -6,7 +6,8 @@ import sys, torch
 sys.path.insert(0, "/root/repo")
 from vllm_hymeta_b200 import ops
 dev = "cuda"
-N, T, H, Hkv, D = 64, 8192, 28, 4, 128
+N, T = (int(sys.argv[1]), int(sys.argv[2])) if len(sys.argv) > 2 else (64, 8192)   # requests x prompt length
+H, Hkv, D = 28, 4, 128
 q = torch.randn(N * T, H, D, device=dev).bfloat16()
 k = torch.randn(N * T, Hkv, D, device=dev).bfloat16()
 v = torch.randn(N * T, Hkv, D, device=dev).bfloat16()
