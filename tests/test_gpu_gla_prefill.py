@@ -134,6 +134,12 @@ def test_seg_len_heuristic():
     assert o.gla_prefill_seg_len(4, 300) == 0               # too short to cut
     s = o.gla_prefill_seg_len(1, 32768)
     assert s > 0 and s % 16 == 0 and 32768 // s >= 64
+    # balanced work lists: only where the partial last wave outweighs the per-piece restart
+    assert o.gla_prefill_balanced_pays(256, 8192, 148)      # config 2: 1.73 waves
+    assert o.gla_prefill_balanced_pays(160, 8192, 148)
+    assert not o.gla_prefill_balanced_pays(148, 8192, 148)  # one full wave
+    assert not o.gla_prefill_balanced_pays(296, 8192, 148)  # two full waves
+    assert not o.gla_prefill_balanced_pays(4000, 256, 148)  # many short chains: the grid wins
 
 
 # ------------------------------------------------------------------- balanced single-pass form
@@ -192,3 +198,11 @@ def test_balanced_falls_back_when_a_chain_exceeds_an_sm_share(ops):
     lens = [40] * 60 + [4000]                                 # 244 chains, one far longer than total / 148
     _balanced_vs_single(ops, lens, 28, 4, 4, "7b", 24)
     _balanced_vs_single(ops, [100, 50, 60, 70], 28, 4, 4, "7b", 25)   # fewer chains than SMs: plain grid
+
+
+def test_balanced_many_short_requests(ops):
+    """More requests than plan threads (N > 1024) and far more chains than SMs: every SM's list holds
+    dozens of pieces, most of them whole chains of a few steps, some empty."""
+    gen = torch.Generator().manual_seed(5)
+    lens = torch.randint(0, 70, (1500,), generator=gen).tolist()
+    _balanced_vs_single(ops, lens, 8, 2, 2, "70b", 26)

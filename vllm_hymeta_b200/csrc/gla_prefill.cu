@@ -142,7 +142,7 @@ gla_prefill_kernel(const GlaPrefillParams p, const __grid_constant__ CUtensorMap
   GlaPiece own;                    // the block index's piece (grid launches) / first piece of the list
   own.pad = 0;
   int pi0 = 0, n_pieces = 1, cta_steps = 0;
-  const bool table = p.plan != nullptr && p.plan[0] != 0;
+  const bool table = p.plan != nullptr;   // balanced launch: `ctas` CTAs, each with a list from the plan kernel
   if (table) {
     // logical CTA index = arrival order, so the CTA a hand-off waits for has always started
     int* slot_l = reinterpret_cast<int*>(smem + GP_BAR + 208);
@@ -837,8 +837,8 @@ __global__ void __launch_bounds__(256) gla_prefill_scan_kernel(const GlaPrefillP
 // B in CTA j+1, the fp32 state handed over through buffer j of the workspace.  Every CTA walks its
 // range BACKWARDS -- A first, whole chains, B last: A has no dependency, and B starts no earlier than
 // (range - |B|) >= |A| steps into its CTA, when A is long done.  That needs range >= longest chain;
-// otherwise (a few very long chains among short ones) the plan says so and the launch runs one
-// chain per CTA in block-index order.
+// otherwise (a few very long chains among short ones, or no more chains than SMs) whole chains are
+// dealt round-robin.  Either way the main kernel is launched with one persistent CTA per SM.
 __global__ void __launch_bounds__(1024) gla_prefill_plan_kernel(
     const GlaPrefillParams p, int ncta, int32_t* cs, int32_t* cta_off, int32_t* cta_steps, GlaPiece* pieces) {
   __shared__ int s_sum[1024], s_max[1024], s_cnt[1024];
@@ -869,7 +869,30 @@ __global__ void __launch_bounds__(1024) gla_prefill_plan_kernel(
   if (tid == 0) { p.plan[0] = cut ? 1 : 0; p.plan[1] = ncta; p.plan[2] = 0; p.plan[3] = R; }
   for (int j = tid; j < ncta; j += 1024) p.flags[j] = 0;
   __syncthreads();
-  if (!cut) return;
+  if (!cut) {
+    // nothing to balance by cutting: whole chains, dealt round-robin (CTA j: chains j, j + ncta, ...)
+    if (tid < ncta) {
+      int off = 0, steps = 0;
+      for (int j = 0; j < tid; ++j) off += j < chains ? (chains - j + ncta - 1) / ncta : 0;
+      int k = 0;
+      for (int c = tid; c < chains; c += ncta, ++k) {
+        const int n = c / Hs, slot = p.slot[n], mode = p.init_mode[n];
+        GlaPiece pc;
+        pc.tok_begin = p.cu[n]; pc.len = p.cu[n + 1] - p.cu[n]; pc.hs = c - n * Hs;
+        pc.in_kind = 0; pc.in_idx = 0;
+        if (mode == 1 && slot >= 0) { pc.in_kind = 1; pc.in_idx = slot; }
+        else if (mode == 2 && p.meta_state) pc.in_kind = 2;
+        pc.out_kind = 0; pc.out_idx = 0;
+        if (p.write_state && slot >= 0) { pc.out_kind = 1; pc.out_idx = slot; }
+        pc.pad = 0;
+        pieces[off + k] = pc;
+        steps += cs[n + 1] - cs[n];
+      }
+      cta_off[tid] = off; cta_steps[tid] = steps;
+      if (tid == ncta - 1) cta_off[ncta] = off + k;
+    }
+    return;
+  }
   // thread j plans range [j R, (j+1) R): pass 0 counts its pieces, pass 1 writes them back to front
   // (an empty chain is a point of the line: it goes to the range that holds the point and only
   // moves its start state to its slot)
@@ -1044,6 +1067,7 @@ extern "C" int hymeta_gla_prefill_varlen_fused(
   auto launch = [&](int pass, int segs) {
     p.pass = pass;
     dim3 grid(Hs, N, segs);
+    if (balanced) grid = dim3(ncta, 1, 1);
     cudaStream_t st = (cudaStream_t)stream;
     const bool gn = p.gnorm_w != nullptr && pass != 1;   // the summary pass emits no outputs
     if (g_is_fp32) {
@@ -1060,7 +1084,7 @@ extern "C" int hymeta_gla_prefill_varlen_fused(
         p, ncta, plan_cs, const_cast<int32_t*>(p.cta_off), const_cast<int32_t*>(p.cta_steps),
         const_cast<GlaPiece*>(p.pieces));
     count_launch();
-    launch(0, 1);
+    launch(0, 1);                                  // one persistent CTA per SM, whatever the plan says
   } else if (n_segs == 1) launch(0, 1);
   else {
     // (1) per-segment summaries from a zero start, (2) scan into segment start states, (3) outputs

@@ -152,9 +152,7 @@ def gla_prefill_varlen(q, k, v, g, state, cu_seqlens, slot_idx, init_mode,
     msl = int(max_seqlen if max_seqlen is not None else T)
     if seg_len is None:
         seg_len = gla_prefill_seg_len(N * Hs, msl, q.device)
-        if seg_len == 0 and N * Hs > _sm_count(q.device):
-            # more chains than SMs: equal step ranges per SM instead of whole chains in waves (the
-            # device-side plan keeps the plain grid when one chain exceeds an SM's share)
+        if seg_len == 0 and gla_prefill_balanced_pays(N * Hs, msl, _sm_count(q.device)):
             seg_len = GLA_SEG_BALANCED
     ws, ws_bytes = None, 0
     if seg_len == GLA_SEG_BALANCED:
@@ -220,6 +218,22 @@ def _sm_count(device=None) -> int:
     if sms is None:
         sms = _SM_COUNT[dev] = torch.cuda.get_device_properties(dev).multi_processor_count
     return sms
+
+
+def gla_prefill_balanced_pays(chains: int, max_seqlen: int, sms: int) -> bool:
+    """Whether the balanced work lists (equal step ranges per SM, chains cut where they straddle) beat
+    one chain per CTA.  They remove the partial last wave -- ceil(w) / w - 1 with w = chains / SMs
+    waves -- and pay ~4 steps of pipeline drain + restart per piece plus ~6 % for the static split
+    (a hardware-scheduled grid evens out SM-to-SM speed differences, fixed lists cannot).  Measured
+    on B200 (tools/bench_gla_balanced.py; chains x steps): 160 x 512 -41 %, 256 x 512 -9 %,
+    400 x 256 -5 %, 1200 x 128 -5 %, 1024 x 64 +13 %, 4000 x 16 +25 %.  The host only knows the
+    longest sequence, so the estimate takes every chain at that length."""
+    if chains <= sms or max_seqlen <= 0:
+        return False
+    steps = -(-max_seqlen // 16)
+    w = chains / sms
+    gain = -(-chains // sms) / w - 1.0
+    return gain > 4.0 / steps + 0.06 + 0.02
 
 
 def gla_prefill_seg_len(chains: int, max_seqlen: int, device=None, min_seg: int = 256) -> int:
