@@ -12,6 +12,11 @@ q = torch.randn(N * T, H, D, device=dev).bfloat16()
 k = torch.randn(N * T, Hkv, D, device=dev).bfloat16()
 v = torch.randn(N * T, Hkv, D, device=dev).bfloat16()
 g = (torch.nn.functional.logsigmoid(torch.randn(N * T, Hkv, D, device=dev)) / 16).bfloat16()
+if len(sys.argv) > 3 and sys.argv[3] == "strided":   # q / k / v as views of one qkv projection output, as the module passes them
+    qkv = torch.cat([q.view(N * T, -1), k.view(N * T, -1), v.view(N * T, -1)], 1)
+    q = qkv[:, :H * D].view(N * T, H, D)
+    k = qkv[:, H * D:(H + Hkv) * D].view(N * T, Hkv, D)
+    v = qkv[:, (H + Hkv) * D:].view(N * T, Hkv, D)
 state = torch.zeros(N, Hkv, D, D, device=dev, dtype=torch.bfloat16)
 cu = torch.arange(0, (N + 1) * T, T, device=dev, dtype=torch.int32)
 slots = torch.arange(N, device=dev, dtype=torch.int32)
