@@ -361,3 +361,18 @@ def test_v1_metadata_builder_bit_exact():
     with pytest.raises(ValueError):
         MetaAttentionV1Impl(28, 64, 0.1, 4)
     assert MetaAttentionV1Impl(28, 128, 0.1, 4, sliding_window=4096).window_left == 4095
+
+
+def test_gla_prefill_scheduling_policy_is_pure_host_logic():
+    """Which GLA prefill form a launch takes is decided on the host from (chains, longest sequence,
+    SM count) alone -- no device query, no sync: balanced work lists only where a partial last wave
+    costs more than the per-piece pipeline restart."""
+    from vllm_hymeta_b200 import ops
+    assert ops.gla_prefill_balanced_pays(256, 8192, 148)        # BASELINE config 2: 1.73 waves of 512 steps
+    assert ops.gla_prefill_balanced_pays(160, 8192, 148)
+    assert ops.gla_prefill_balanced_pays(400, 4096, 148)
+    assert not ops.gla_prefill_balanced_pays(148, 8192, 148)    # exactly one wave
+    assert not ops.gla_prefill_balanced_pays(8, 32768, 148)     # few long chains: the segmented form's case
+    assert not ops.gla_prefill_balanced_pays(1024, 1024, 148)   # 6.9 waves of short chains
+    assert not ops.gla_prefill_balanced_pays(4000, 256, 148)
+    assert not ops.gla_prefill_balanced_pays(256, 0, 148)
